@@ -1,0 +1,158 @@
+"""ctypes binding of libguava_rasterizer_b200.so (C ABI: include/guava_rasterizer.h).
+
+There is no CPU or PyTorch fallback: if the shared object is missing or a
+required symbol is absent, loading raises and every product entry point fails.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_float, c_int, c_longlong,
+                    c_size_t, c_ulonglong, c_void_p)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "lib", "libguava_rasterizer_b200.so")
+
+ALLOC_FN = CFUNCTYPE(c_void_p, c_void_p, c_size_t)
+
+EXPORTS = (
+    "guava_rasterizer_forward",
+    "guava_rasterizer_backward",
+    "guava_rasterizer_mark_visible",
+    "guava_rasterizer_forward_batch",
+    "guava_rasterizer_backward_batch",
+    "guava_buffer_layout",
+    "guava_set_option",
+    "guava_get_option",
+    "guava_launch_count",
+    "guava_stage_time",
+    "guava_stage_time_reset",
+    "guava_last_error",
+    "guava_version",
+)
+
+GUAVA_OK = 0
+GUAVA_ERR_INVALID_ARGUMENT = 1
+GUAVA_ERR_CUDA = 2
+GUAVA_ERR_ALLOC = 3
+GUAVA_ERR_UNSUPPORTED = 4
+
+
+class Layout(Structure):
+    _fields_ = [(n, c_size_t) for n in (
+        "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched",
+        "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "num_rendered",
+        "binning_bytes", "point_list", "keys_unsorted", "keys_sorted")]
+
+
+class GuavaLibraryError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(SO_PATH):
+        raise GuavaLibraryError(
+            f"{SO_PATH} is missing: the CUDA library has not been built "
+            "(run `python guava_renderer_b200/build.py`). There is no CPU fallback.")
+    lib = ctypes.CDLL(SO_PATH)
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise GuavaLibraryError(f"{SO_PATH} does not export {name}")
+    P = c_void_p
+    lib.guava_rasterizer_forward.restype = c_int
+    lib.guava_rasterizer_forward.argtypes = [
+        ALLOC_FN, P, ALLOC_FN, P, ALLOC_FN, P,
+        c_int, c_int, c_int, P, c_int, c_int,
+        P, P, P, P, P, c_float, P, P, P, P, P,
+        c_float, c_float, c_int, P, P, c_int, P, c_int, P, POINTER(c_int)]
+    lib.guava_rasterizer_backward.restype = c_int
+    lib.guava_rasterizer_backward.argtypes = [
+        c_int, c_int, c_int, c_int, P, c_int, c_int,
+        P, P, P, P, P, c_float, P, P, P, P, P, c_float, c_float,
+        P, P, P, P, P, P,
+        P, P, P, P, P, P, P, P, P, P,
+        c_int, c_int, P]
+    lib.guava_rasterizer_mark_visible.restype = c_int
+    lib.guava_rasterizer_mark_visible.argtypes = [c_int, P, P, P, P, P]
+    lib.guava_rasterizer_forward_batch.restype = c_int
+    lib.guava_rasterizer_forward_batch.argtypes = [
+        ALLOC_FN, P, ALLOC_FN, P, ALLOC_FN, P,
+        c_int, c_int, P, c_int, c_int,
+        P, c_size_t, P, c_size_t, P, c_size_t, P, c_size_t, c_float, P, c_size_t,
+        P, P, P, P, P, c_int, P, c_int, P, POINTER(c_int)]
+    lib.guava_rasterizer_backward_batch.restype = c_int
+    lib.guava_rasterizer_backward_batch.argtypes = [
+        c_int, c_int, c_int, P, c_int, c_int,
+        P, c_size_t, P, c_size_t, P, c_size_t, P, c_size_t, c_float, P, c_size_t,
+        P, P, P, P, P, P, P, P, P,
+        P, P, P, P, P, P, P, P, P,
+        c_int, c_int, P]
+    lib.guava_buffer_layout.restype = c_int
+    lib.guava_buffer_layout.argtypes = [c_int, c_int, c_int, c_int, c_size_t, POINTER(Layout)]
+    lib.guava_set_option.restype = c_int
+    lib.guava_set_option.argtypes = [c_char_p, c_longlong]
+    lib.guava_get_option.restype = c_longlong
+    lib.guava_get_option.argtypes = [c_char_p]
+    lib.guava_launch_count.restype = c_ulonglong
+    lib.guava_stage_time.restype = c_int
+    lib.guava_stage_time.argtypes = [c_char_p, POINTER(ctypes.c_double), POINTER(c_ulonglong)]
+    lib.guava_stage_time_reset.restype = None
+    lib.guava_last_error.restype = c_char_p
+    lib.guava_version.restype = c_char_p
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().guava_last_error().decode("utf-8", "replace")
+
+
+def set_option(name: str, value: int) -> None:
+    rc = load().guava_set_option(name.encode(), int(value))
+    if rc != GUAVA_OK:
+        raise ValueError(f"unknown option {name!r}")
+
+
+def get_option(name: str) -> int:
+    return int(load().guava_get_option(name.encode()))
+
+
+def launch_count() -> int:
+    return int(load().guava_launch_count())
+
+
+STAGES = ("preprocess", "tile_scan", "scatter", "tile_sort", "render_forward", "render_backward",
+          "preprocess_backward")
+
+
+def stage_times() -> dict:
+    """{stage: (total_ms, calls)} accumulated while option "profile_stages" is on."""
+    lib = load()
+    out = {}
+    for s in STAGES:
+        ms, n = ctypes.c_double(0), c_ulonglong(0)
+        lib.guava_stage_time(s.encode(), ctypes.byref(ms), ctypes.byref(n))
+        out[s] = (ms.value, int(n.value))
+    return out
+
+
+def stage_times_reset() -> None:
+    load().guava_stage_time_reset()
+
+
+def version() -> str:
+    return load().guava_version().decode()
+
+
+def buffer_layout(V: int, P: int, W: int, H: int, capacity: int = 0) -> Layout:
+    L = Layout()
+    rc = load().guava_buffer_layout(V, P, W, H, capacity, ctypes.byref(L))
+    if rc != GUAVA_OK:
+        raise ValueError(last_error())
+    return L

@@ -1,0 +1,577 @@
+// C ABI (include/guava_rasterizer.h) and host-side orchestration.
+//
+// Replaces DGR32/cuda_rasterizer/rasterizer_impl.cu:141-450
+// (CudaRasterizer::Rasterizer::{markVisible, forward, backward}).
+//
+// Launch chain of one forward call (single view or V batched views):
+//   memset(tile counters) -> preprocess(+count) -> tile scan -> scatter ->
+//   tile sort (3 size classes) -> composite
+// There is no device->host dependency inside the chain.  The reference blocks
+// on a cudaMemcpy of num_rendered (rasterizer_impl.cu:284) before it can size
+// the binning buffer; here the buffer is sized from a running capacity estimate,
+// the whole chain is enqueued, and only then the host reads num_rendered from a
+// pinned word the scan kernel wrote (by then long finished).  If the estimate
+// was too small the kernels skipped themselves (overflow flag) and the tail of
+// the chain is re-enqueued with the exact size.
+#include "internal.cuh"
+#include "../../include/guava_rasterizer.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+namespace guava {
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+static thread_local std::string t_last_error;
+static std::atomic<long long> g_opt_emit_sorted_keys{0};
+static std::atomic<long long> g_opt_exact_binning{0};
+static std::atomic<long long> g_opt_capacity_hint{0};
+static std::atomic<long long> g_opt_async_forward{0};
+
+static int fail(int code, const std::string& msg)
+{
+    t_last_error = msg;
+    return code;
+}
+
+#define GUAVA_CUDA(expr)                                                                        \
+    do {                                                                                        \
+        cudaError_t e__ = (expr);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return fail(GUAVA_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));   \
+    } while (0)
+
+// reference: CHECK_CUDA (auxiliary.h:178-185): in debug mode synchronise after
+// every stage and report the failing stage
+#define GUAVA_STAGE(what, debug)                                                                \
+    do {                                                                                        \
+        cudaError_t e__ = cudaGetLastError();                                                   \
+        if (e__ == cudaSuccess && (debug)) e__ = cudaStreamSynchronize(stream);                 \
+        if (e__ != cudaSuccess)                                                                 \
+            return fail(GUAVA_ERR_CUDA, std::string("[CUDA ERROR] in ") + what + ": " +         \
+                                            cudaGetErrorString(e__));                           \
+    } while (0)
+
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// ------------------------------------------------------------ stage profiling
+// Option "profile_stages": bracket every kernel of a call with CUDA events on the
+// launching stream and accumulate per-stage device time (read back with
+// guava_stage_time).  Used by bench.py for the roofline object; off by default.
+static std::atomic<long long> g_opt_profile_stages{0};
+static const char* const kStageNames[] = {"preprocess", "tile_scan", "scatter", "tile_sort", "render_forward",
+                                          "render_backward", "preprocess_backward"};
+constexpr int kNumStages = 7;
+static double g_stage_ms[kNumStages];
+static unsigned long long g_stage_calls[kNumStages];
+static std::mutex g_stage_mu;
+
+struct StageTimer {
+    bool on;
+    cudaStream_t stream;
+    struct Rec { int stage; cudaEvent_t a, b; };
+    Rec recs[16];
+    int n = 0;
+    StageTimer(cudaStream_t s) : on(g_opt_profile_stages.load() != 0), stream(s) {}
+    void begin(int stage)
+    {
+        if (!on || n >= 16) return;
+        recs[n].stage = stage;
+        cudaEventCreate(&recs[n].a);
+        cudaEventCreate(&recs[n].b);
+        cudaEventRecord(recs[n].a, stream);
+    }
+    void end()
+    {
+        if (!on || n >= 16) return;
+        cudaEventRecord(recs[n].b, stream);
+        n++;
+    }
+    ~StageTimer()
+    {
+        if (!on || n == 0) return;
+        cudaEventSynchronize(recs[n - 1].b);
+        std::lock_guard<std::mutex> lk(g_stage_mu);
+        for (int i = 0; i < n; i++) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, recs[i].a, recs[i].b) == cudaSuccess) {
+                g_stage_ms[recs[i].stage] += ms;
+                g_stage_calls[recs[i].stage] += 1;
+            }
+            cudaEventDestroy(recs[i].a);
+            cudaEventDestroy(recs[i].b);
+        }
+    }
+};
+
+static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emit_keys, guava_layout* L)
+{
+    const size_t n = (size_t)V * P;
+    const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const size_t tiles = (size_t)V * gx * gy;
+    const size_t npix = (size_t)V * H * W;
+    size_t o = 0;
+    L->splat_rec = o;     o = align_up(o + n * sizeof(SplatRec));
+    L->depths = o;        o = align_up(o + n * 4);
+    L->rects = o;         o = align_up(o + n * 8);
+    L->tiles_touched = o; o = align_up(o + n * 4);
+    L->geom_bytes = o;
+    o = 0;
+    L->final_T = o;      o = align_up(o + npix * 4);
+    L->n_contrib = o;    o = align_up(o + npix * 4);
+    L->ranges = o;       o = align_up(o + tiles * 8);
+    L->tile_cursor = o;  o = align_up(o + tiles * 4);
+    L->num_rendered = o; o = align_up(o + 16);
+    L->image_bytes = o;
+    o = 0;
+    L->point_list = o;    o = align_up(o + capacity * 4);
+    L->keys_unsorted = o; o = align_up(o + capacity * 8);
+    L->keys_sorted = o;   o = align_up(o + (emit_keys ? capacity * 8 : 0));
+    L->binning_bytes = o;
+}
+
+// ------------------------------------------------ num_rendered readback slots
+struct HostSlots {
+    uint32_t* host = nullptr;   // pinned, mapped
+    uint32_t* dev = nullptr;
+    std::atomic<unsigned> next{0};
+    static constexpr unsigned N = 256;
+};
+static HostSlots g_slots;
+static std::once_flag g_slots_once;
+static cudaError_t g_slots_err = cudaSuccess;
+
+static cudaError_t ensure_slots()
+{
+    std::call_once(g_slots_once, [] {
+        void* h = nullptr;
+        g_slots_err = cudaHostAlloc(&h, HostSlots::N * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
+        if (g_slots_err != cudaSuccess) return;
+        g_slots.host = (uint32_t*)h;
+        void* d = nullptr;
+        g_slots_err = cudaHostGetDevicePointer(&d, h, 0);
+        g_slots.dev = (uint32_t*)d;
+    });
+    return g_slots_err;
+}
+
+// --------------------------------------------------------- capacity estimates
+struct CapEntry { size_t n; int W, H; size_t cap; };
+static CapEntry g_caps[16];
+static unsigned g_caps_next = 0;
+static std::mutex g_caps_mu;
+
+static size_t capacity_estimate(size_t n, int W, int H)
+{
+    const long long forced = g_opt_capacity_hint.load();
+    if (forced > 0) return (size_t)forced;
+    std::lock_guard<std::mutex> lk(g_caps_mu);
+    for (auto& e : g_caps)
+        if (e.n == n && e.W == W && e.H == H && e.cap) return e.cap;
+    size_t c = 16 * n;
+    if (c < (1u << 20)) c = 1u << 20;
+    return c;
+}
+static void capacity_record(size_t n, int W, int H, size_t R)
+{
+    std::lock_guard<std::mutex> lk(g_caps_mu);
+    const size_t want = R + R / 4 + 4096;
+    for (auto& e : g_caps)
+        if (e.n == n && e.W == W && e.H == H && e.cap) {
+            // grow immediately, shrink slowly
+            e.cap = want > e.cap ? want : (e.cap * 15 + want) / 16;
+            return;
+        }
+    g_caps[g_caps_next++ % 16] = CapEntry{n, W, H, want};
+}
+
+__global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
+                                    uint32_t* __restrict__ num_rendered, unsigned long long capacity)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) cursor[i] = ranges[i].x;
+    if (i == 0) num_rendered[1] = ((unsigned long long)num_rendered[0] > capacity) ? 1u : 0u;
+}
+
+// ------------------------------------------------------------------- forward
+static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
+                        guava_alloc_fn binningBuffer, void* binning_user,
+                        guava_alloc_fn imageBuffer, void* image_user,
+                        Inputs in, float* out_color, float* out_invdepth, int* radii,
+                        int debug, cudaStream_t stream, int* num_rendered)
+{
+    if (num_rendered) *num_rendered = 0;
+    if (in.V < 0 || in.P < 0 || in.W <= 0 || in.H <= 0)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if ((size_t)in.V * in.P == 0) return GUAVA_OK;   // rasterize_points.cu:88: outputs stay as allocated
+    if (in.colors == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "For non-RGB, provide precomputed Gaussian colors!");
+    if (in.means3D == nullptr || in.opacities == nullptr || in.viewmatrix == nullptr || in.projmatrix == nullptr ||
+        in.background == nullptr || out_color == nullptr || radii == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (in.cov3D_precomp == nullptr && (in.scales == nullptr || in.rotations == nullptr))
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "need scales+rotations or cov3D_precomp");
+    if (((uintptr_t)in.colors & 15) || ((in.colors_vs * sizeof(float)) & 15))
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "colors_precomp must be 16-byte aligned");
+    in.gx = (in.W + TILE_X - 1) / TILE_X;
+    in.gy = (in.H + TILE_Y - 1) / TILE_Y;
+    in.tiles = in.gx * in.gy;
+    if (in.gx > 65535 || in.gy > 65535) return fail(GUAVA_ERR_INVALID_ARGUMENT, "image too large");
+
+    const size_t n = (size_t)in.V * in.P;
+    const bool emit_keys = g_opt_emit_sorted_keys.load() != 0;
+    const bool exact = g_opt_exact_binning.load() != 0;
+    const bool async_fwd = g_opt_async_forward.load() != 0 && !exact;
+    GUAVA_CUDA(ensure_slots());
+
+    guava_layout L;
+    size_t cap = capacity_estimate(n, in.W, in.H);
+    compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+    char* geom = geometryBuffer(geometry_user, L.geom_bytes);
+    char* img = imageBuffer(image_user, L.image_bytes);
+    if (!geom || !img) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
+    if (((uintptr_t)geom & 127) || ((uintptr_t)img & 127))
+        return fail(GUAVA_ERR_ALLOC, "allocator must return 128-byte aligned memory");
+
+    GeomPtrs g;
+    g.rec = (SplatRec*)(geom + L.splat_rec);
+    g.depths = (float*)(geom + L.depths);
+    g.rects = (ushort4*)(geom + L.rects);
+    g.tiles_touched = (uint32_t*)(geom + L.tiles_touched);
+    ImagePtrs im;
+    im.final_T = (float*)(img + L.final_T);
+    im.n_contrib = (uint32_t*)(img + L.n_contrib);
+    im.ranges = (uint2*)(img + L.ranges);
+    im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
+    im.num_rendered = (uint32_t*)(img + L.num_rendered);
+
+    const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
+    volatile uint32_t* hslot = g_slots.host + slot;
+    *hslot = 0xFFFFFFFFu;
+
+    const int total_tiles = in.V * in.tiles;
+    StageTimer timer(stream);
+    timer.begin(0);
+    GUAVA_CUDA(cudaMemsetAsync(im.tile_cursor, 0, (size_t)total_tiles * 4, stream));
+    launch_preprocess_forward(in, g, im, radii, stream);
+    timer.end();
+    GUAVA_STAGE("preprocess", debug);
+    timer.begin(1);
+    launch_tile_scan(total_tiles, im, g_slots.dev + slot, exact ? (size_t)-1 : cap, stream);
+    timer.end();
+    GUAVA_STAGE("tile_scan", debug);
+
+    auto wait_R = [&](uint32_t& R) -> int {
+        unsigned spins = 0;
+        while (*hslot == 0xFFFFFFFFu) {
+            if ((++spins & 0x3ff) == 0) {
+                cudaError_t q = cudaStreamQuery(stream);
+                if (q == cudaSuccess) {
+                    if (*hslot == 0xFFFFFFFFu) return fail(GUAVA_ERR_CUDA, "num_rendered was never written");
+                    break;
+                }
+                if (q != cudaErrorNotReady)
+                    return fail(GUAVA_ERR_CUDA, std::string("waiting for num_rendered: ") + cudaGetErrorString(q));
+            }
+        }
+        R = *hslot;
+        return GUAVA_OK;
+    };
+
+    uint32_t R = 0;
+    bool have_R = false;
+    if (exact) {
+        int rc = wait_R(R);
+        if (rc) return rc;
+        have_R = true;
+        cap = R;
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+    }
+    char* bin = binningBuffer(binning_user, L.binning_bytes ? L.binning_bytes : 256);
+    if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
+
+    for (int attempt = 0; attempt < 2; attempt++) {
+        BinningPtrs b;
+        b.point_list = (uint32_t*)(bin + L.point_list);
+        b.keys_unsorted = (uint64_t*)(bin + L.keys_unsorted);
+        b.keys_sorted = emit_keys ? (uint64_t*)(bin + L.keys_sorted) : nullptr;
+        b.capacity = cap;
+        timer.begin(2);
+        launch_scatter(in, g, im, b, radii, stream);
+        timer.end();
+        GUAVA_STAGE("scatter", debug);
+        timer.begin(3);
+        launch_tile_sort(in, im, b, nullptr, stream);
+        timer.end();
+        GUAVA_STAGE("tile_sort", debug);
+        timer.begin(4);
+        launch_render_forward(in, g, im, b, out_color, out_invdepth, stream);
+        timer.end();
+        GUAVA_STAGE("render_forward", debug);
+        if (async_fwd) { R = 0xFFFFFFFFu; break; }
+        if (!have_R) {
+            int rc = wait_R(R);
+            if (rc) return rc;
+            have_R = true;
+        }
+        if ((size_t)R <= cap) break;
+        // estimate too small: every kernel after the scan skipped itself
+        cap = (size_t)R;
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+        bin = binningBuffer(binning_user, L.binning_bytes);
+        if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
+        reset_cursor_kernel<<<(total_tiles + 255) / 256, 256, 0, stream>>>(total_tiles, im.ranges, im.tile_cursor,
+                                                                           im.num_rendered, (unsigned long long)cap);
+        count_launch();
+    }
+    if (!async_fwd) capacity_record(n, in.W, in.H, R);
+    if (num_rendered) *num_rendered = async_fwd ? -1 : (int)R;
+    return GUAVA_OK;
+}
+
+// ------------------------------------------------------------------ backward
+static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, char* img,
+                         const float* dL_dpix, const float* dL_invdepths,
+                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                         float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D,
+                         float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream)
+{
+    if ((size_t)in.V * in.P == 0) return GUAVA_OK;
+    if (!geom || !bin || !img || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+        !dL_dmean3D || !dL_dcov3D || !radii)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (in.cov3D_precomp == nullptr && (!dL_dscale || !dL_drot))
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (dL_invdepths != nullptr && dL_dinvdepth == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "dL_dinvdepth buffer missing");
+    in.gx = (in.W + TILE_X - 1) / TILE_X;
+    in.gy = (in.H + TILE_Y - 1) / TILE_Y;
+    in.tiles = in.gx * in.gy;
+    guava_layout L;
+    compute_layout(in.V, in.P, in.W, in.H, 0, false, &L);
+    GeomPtrs g;
+    g.rec = (SplatRec*)(geom + L.splat_rec);
+    g.depths = (float*)(geom + L.depths);
+    g.rects = (ushort4*)(geom + L.rects);
+    g.tiles_touched = (uint32_t*)(geom + L.tiles_touched);
+    ImagePtrs im;
+    im.final_T = (float*)(img + L.final_T);
+    im.n_contrib = (uint32_t*)(img + L.n_contrib);
+    im.ranges = (uint2*)(img + L.ranges);
+    im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
+    im.num_rendered = (uint32_t*)(img + L.num_rendered);
+    BinningPtrs b;
+    b.point_list = (uint32_t*)(bin + L.point_list);   // offset 0 for every capacity
+    b.keys_unsorted = nullptr;
+    b.keys_sorted = nullptr;
+    b.capacity = 0;
+
+    StageTimer timer(stream);
+    timer.begin(5);
+    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+                           dL_invdepths ? dL_dinvdepth : nullptr, stream);
+    timer.end();
+    GUAVA_STAGE("render_backward", debug);
+    timer.begin(6);
+    launch_preprocess_backward(in, g, radii, dL_dmean2D, dL_dconic, dL_invdepths ? dL_dinvdepth : nullptr,
+                               dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot, stream);
+    timer.end();
+    GUAVA_STAGE("preprocess_backward", debug);
+    return GUAVA_OK;
+}
+
+}  // namespace guava
+
+using namespace guava;
+
+extern "C" {
+
+int guava_rasterizer_forward(
+    guava_alloc_fn geometryBuffer, void* geometry_user, guava_alloc_fn binningBuffer, void* binning_user,
+    guava_alloc_fn imageBuffer, void* image_user, int P, int D, int M, const float* background, int width,
+    int height, const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* cam_pos, float tan_fovx, float tan_fovy,
+    int prefiltered, float* out_color, float* out_invdepth, int antialiasing, int* radii, int debug,
+    void* stream, int* num_rendered)
+{
+    (void)D; (void)M; (void)cam_pos;
+    if (shs != nullptr)
+        return fail(GUAVA_ERR_UNSUPPORTED, "spherical harmonics are not supported by the 32-channel rasterizer");
+    if (!geometryBuffer || !binningBuffer || !imageBuffer)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null allocator");
+    Inputs in{};
+    in.V = 1; in.P = P; in.W = width; in.H = height;
+    in.means3D = means3D; in.colors = colors_precomp; in.opacities = opacities;
+    in.scales = scales; in.rotations = rotations; in.cov3D_precomp = cov3D_precomp;
+    in.scale_modifier = scale_modifier;
+    in.viewmatrix = viewmatrix; in.projmatrix = projmatrix;
+    in.tan_fov_dev = nullptr; in.tan_fovx = tan_fovx; in.tan_fovy = tan_fovy;
+    in.background = background; in.antialiasing = antialiasing; in.prefiltered = prefiltered;
+    return forward_impl(geometryBuffer, geometry_user, binningBuffer, binning_user, imageBuffer, image_user, in,
+                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered);
+}
+
+int guava_rasterizer_backward(
+    int P, int D, int M, int R, const float* background, int width, int height, const float* means3D,
+    const float* shs, const float* colors_precomp, const float* opacities, const float* scales,
+    float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+    const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+    char* geom_buffer, char* binning_buffer, char* image_buffer, const float* dL_dpix,
+    const float* dL_invdepths, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+    float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+    int antialiasing, int debug, void* stream)
+{
+    (void)D; (void)M; (void)R; (void)campos; (void)dL_dsh;
+    if (shs != nullptr)
+        return fail(GUAVA_ERR_UNSUPPORTED, "spherical harmonics are not supported by the 32-channel rasterizer");
+    Inputs in{};
+    in.V = 1; in.P = P; in.W = width; in.H = height;
+    in.means3D = means3D; in.colors = colors_precomp; in.opacities = opacities;
+    in.scales = scales; in.rotations = rotations; in.cov3D_precomp = cov3D_precomp;
+    in.scale_modifier = scale_modifier;
+    in.viewmatrix = viewmatrix; in.projmatrix = projmatrix;
+    in.tan_fov_dev = nullptr; in.tan_fovx = tan_fovx; in.tan_fovy = tan_fovy;
+    in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
+    if (colors_precomp == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "For non-RGB, provide precomputed Gaussian colors!");
+    return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, dL_dmean2D,
+                         dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dscale,
+                         dL_drot, debug, (cudaStream_t)stream);
+}
+
+int guava_rasterizer_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                                  uint8_t* present, void* stream)
+{
+    (void)projmatrix;
+    if (P < 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if (P == 0) return GUAVA_OK;
+    if (!means3D || !viewmatrix || !present) return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
+    return GUAVA_OK;
+}
+
+int guava_rasterizer_forward_batch(
+    guava_alloc_fn geometryBuffer, void* geometry_user, guava_alloc_fn binningBuffer, void* binning_user,
+    guava_alloc_fn imageBuffer, void* image_user, int V, int P, const float* background, int width, int height,
+    const float* means3D, size_t means3D_view_stride, const float* colors_precomp, size_t colors_view_stride,
+    const float* opacities, size_t opacities_view_stride, const float* scales, size_t scales_view_stride,
+    float scale_modifier, const float* rotations, size_t rotations_view_stride, const float* viewmatrix,
+    const float* projmatrix, const float* tan_fov, float* out_color, float* out_invdepth, int antialiasing,
+    int* radii, int debug, void* stream, int* num_rendered)
+{
+    if (!geometryBuffer || !binningBuffer || !imageBuffer)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null allocator");
+    if (tan_fov == nullptr) return fail(GUAVA_ERR_INVALID_ARGUMENT, "tan_fov must be a device array [V,2]");
+    Inputs in{};
+    in.V = V; in.P = P; in.W = width; in.H = height;
+    in.means3D = means3D; in.means3D_vs = means3D_view_stride;
+    in.colors = colors_precomp; in.colors_vs = colors_view_stride;
+    in.opacities = opacities; in.opacities_vs = opacities_view_stride;
+    in.scales = scales; in.scales_vs = scales_view_stride;
+    in.rotations = rotations; in.rotations_vs = rotations_view_stride;
+    in.cov3D_precomp = nullptr;
+    in.scale_modifier = scale_modifier;
+    in.viewmatrix = viewmatrix; in.projmatrix = projmatrix;
+    in.tan_fov_dev = tan_fov; in.tan_fovx = 0.f; in.tan_fovy = 0.f;
+    in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
+    return forward_impl(geometryBuffer, geometry_user, binningBuffer, binning_user, imageBuffer, image_user, in,
+                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered);
+}
+
+int guava_rasterizer_backward_batch(
+    int V, int P, int R, const float* background, int width, int height, const float* means3D,
+    size_t means3D_view_stride, const float* colors_precomp, size_t colors_view_stride, const float* opacities,
+    size_t opacities_view_stride, const float* scales, size_t scales_view_stride, float scale_modifier,
+    const float* rotations, size_t rotations_view_stride, const float* viewmatrix, const float* projmatrix,
+    const float* tan_fov, const int* radii, char* geom_buffer, char* binning_buffer, char* image_buffer,
+    const float* dL_dpix, const float* dL_invdepths, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+    float* dL_dcolor, float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot,
+    int antialiasing, int debug, void* stream)
+{
+    (void)R;
+    if (tan_fov == nullptr) return fail(GUAVA_ERR_INVALID_ARGUMENT, "tan_fov must be a device array [V,2]");
+    if (colors_precomp == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "For non-RGB, provide precomputed Gaussian colors!");
+    Inputs in{};
+    in.V = V; in.P = P; in.W = width; in.H = height;
+    in.means3D = means3D; in.means3D_vs = means3D_view_stride;
+    in.colors = colors_precomp; in.colors_vs = colors_view_stride;
+    in.opacities = opacities; in.opacities_vs = opacities_view_stride;
+    in.scales = scales; in.scales_vs = scales_view_stride;
+    in.rotations = rotations; in.rotations_vs = rotations_view_stride;
+    in.cov3D_precomp = nullptr;
+    in.scale_modifier = scale_modifier;
+    in.viewmatrix = viewmatrix; in.projmatrix = projmatrix;
+    in.tan_fov_dev = tan_fov;
+    in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
+    return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, dL_dmean2D,
+                         dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dscale,
+                         dL_drot, debug, (cudaStream_t)stream);
+}
+
+int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout* out)
+{
+    if (!out || V < 0 || P < 0 || width <= 0 || height <= 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "bad layout query");
+    compute_layout(V, P, width, height, capacity, g_opt_emit_sorted_keys.load() != 0, out);
+    return GUAVA_OK;
+}
+
+static std::atomic<long long>* find_option(const char* name)
+{
+    if (!name) return nullptr;
+    if (!strcmp(name, "emit_sorted_keys")) return &g_opt_emit_sorted_keys;
+    if (!strcmp(name, "exact_binning")) return &g_opt_exact_binning;
+    if (!strcmp(name, "capacity_hint")) return &g_opt_capacity_hint;
+    if (!strcmp(name, "async_forward")) return &g_opt_async_forward;
+    if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
+    return nullptr;
+}
+
+int guava_set_option(const char* name, long long value)
+{
+    auto* o = find_option(name);
+    if (!o) return fail(GUAVA_ERR_INVALID_ARGUMENT, "unknown option");
+    o->store(value);
+    return GUAVA_OK;
+}
+
+long long guava_get_option(const char* name)
+{
+    auto* o = find_option(name);
+    return o ? o->load() : -1;
+}
+
+unsigned long long guava_launch_count(void) { return g_launches.load(); }
+
+int guava_stage_time(const char* stage, double* total_ms, unsigned long long* calls)
+{
+    if (!stage) return fail(GUAVA_ERR_INVALID_ARGUMENT, "null stage name");
+    for (int i = 0; i < kNumStages; i++)
+        if (!strcmp(stage, kStageNames[i])) {
+            std::lock_guard<std::mutex> lk(g_stage_mu);
+            if (total_ms) *total_ms = g_stage_ms[i];
+            if (calls) *calls = g_stage_calls[i];
+            return GUAVA_OK;
+        }
+    return fail(GUAVA_ERR_INVALID_ARGUMENT, "unknown stage");
+}
+
+void guava_stage_time_reset(void)
+{
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    for (int i = 0; i < kNumStages; i++) { g_stage_ms[i] = 0.0; g_stage_calls[i] = 0; }
+}
+
+const char* guava_last_error(void) { return t_last_error.c_str(); }
+
+const char* guava_version(void) { return "guava_rasterizer_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,219 @@
+// Instance binning: tile scan -> bucket scatter -> per-tile depth sort.
+//
+// Replaces, with identical results, the reference chain
+//   cub::DeviceScan::InclusiveSum            rasterizer_impl.cu:280
+//   cudaMemcpy(num_rendered) (host sync)     rasterizer_impl.cu:284
+//   duplicateWithKeys                        rasterizer_impl.cu:70-111,292
+//   cub::DeviceRadixSort::SortPairs          rasterizer_impl.cu:303-311
+//   cudaMemset(ranges) + identifyTileRanges  rasterizer_impl.cu:313-320,116-138
+//
+// Why the results are identical although the algorithm is not an LSD sort of
+// 64-bit keys: the reference key is (tile << 32 | depth_bits) and its sort is
+// stable over an emission order that is ascending in Gaussian index; a Gaussian
+// touches a tile at most once, so the reference's final order is exactly the
+// strict total order (tile, depth_bits, gaussian_index).  Any algorithm that
+// sorts by that triple produces the same point_list, the same keys and the same
+// ranges.  Here the most significant digit (the tile id) is resolved by a
+// counting pass whose histogram was accumulated by the preprocess kernel and
+// whose scan *is* identifyTileRanges; the remaining (depth_bits, index) order is
+// established per tile inside shared memory.  HBM traffic per instance drops
+// from 152 B (1 histogram + 6 onesweep passes over 12-byte pairs) to 8 B
+// written by the scatter + 8 B read and 4 B written by the tile sort.
+#include "internal.cuh"
+
+namespace guava {
+
+// ------------------------------------------------------------ scan over tiles
+__global__ void __launch_bounds__(1024)
+tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges,
+                 uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
+{
+    __shared__ uint32_t warp_sums[32];
+    const int tid = threadIdx.x;
+    const int ipt = (n + 1023) / 1024;
+    const int begin = min(n, tid * ipt), end = min(n, begin + ipt);
+    uint32_t local = 0;
+    for (int k = begin; k < end; k++) local += cursor[k];
+    // block-wide exclusive scan of `local`
+    uint32_t incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += t;
+    }
+    if ((tid & 31) == 31) warp_sums[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        uint32_t w = warp_sums[tid];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (tid >= o) w += t;
+        }
+        warp_sums[tid] = w;
+    }
+    __syncthreads();
+    uint32_t run = incl - local + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
+    for (int k = begin; k < end; k++) {
+        const uint32_t c = cursor[k];
+        // untouched tiles keep (0,0), as the reference's memset leaves them
+        ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+        cursor[k] = run;
+        run += c;
+    }
+    if (tid == 1023) {
+        const uint32_t total = warp_sums[31];
+        num_rendered[0] = total;
+        num_rendered[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
+        if (host_R != nullptr) { *host_R = total; __threadfence_system(); }
+    }
+}
+
+void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity, cudaStream_t s)
+{
+    tile_scan_kernel<<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.num_rendered,
+                                        host_mapped_R, (unsigned long long)capacity);
+    count_launch();
+}
+
+// -------------------------------------------------------------------- scatter
+// One thread per (view, Gaussian): claim a slot in every touched tile's bucket.
+// Slot order inside a bucket is arbitrary (atomics); the tile sort fixes it.
+__global__ void __launch_bounds__(256)
+scatter_kernel(const Inputs in, const GeomPtrs g, const uint32_t* __restrict__ num_rendered,
+               uint32_t* __restrict__ cursor, uint64_t* __restrict__ keys, unsigned long long capacity)
+{
+    if (num_rendered[1]) return;   // capacity overflow: the host re-runs with a larger buffer
+    const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (gid >= (size_t)in.V * in.P) return;
+    const ushort4 rc = g.rects[gid];
+    if (rc.z <= rc.x || rc.w <= rc.y) return;
+    const int v = (int)(gid / in.P);
+    const uint32_t i = (uint32_t)(gid - (size_t)v * in.P);
+    const uint64_t key = ((uint64_t)__float_as_uint(g.depths[gid]) << 32) | i;
+    uint32_t* cur = cursor + (size_t)v * in.tiles;
+    for (uint32_t y = rc.y; y < rc.w; y++)
+        for (uint32_t x = rc.x; x < rc.z; x++) {
+            const uint32_t pos = atomicAdd(cur + y * in.gx + x, 1u);
+            if (pos < capacity) keys[pos] = key;
+        }
+}
+
+void launch_scatter(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
+                    const int* radii, cudaStream_t s)
+{
+    (void)radii;
+    const size_t n = (size_t)in.V * in.P;
+    if (n == 0) return;
+    scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, g, img.num_rendered, img.tile_cursor,
+                                                                b.keys_unsorted, (unsigned long long)b.capacity);
+    count_launch();
+}
+
+// ------------------------------------------------------------------ tile sort
+// In-place bitonic network in its "all comparators ascending" form (flip +
+// disperse steps).  Because every comparator moves the minimum to the lower
+// index, elements beyond n behave as +inf without being stored, so any n is
+// sorted in place without padding.
+template <typename Ptr>
+__device__ __forceinline__ void bitonic_sort_ascending(Ptr s, uint32_t n, uint32_t npow2, int tid, int nthreads)
+{
+    for (uint32_t k = 2; k <= npow2; k <<= 1) {
+        // flip: i ^ (k-1)
+        __syncthreads();
+        const uint32_t half = k >> 1;
+        for (uint32_t p = tid; p < (npow2 >> 1); p += nthreads) {
+            const uint32_t blk = p / half, t = p - blk * half;
+            const uint32_t i = blk * k + t, j = blk * k + (k - 1 - t);
+            if (j < n) {
+                const uint64_t a = s[i], b = s[j];
+                if (a > b) { s[i] = b; s[j] = a; }
+            }
+        }
+        for (uint32_t d = k >> 2; d > 0; d >>= 1) {
+            __syncthreads();
+            for (uint32_t p = tid; p < (npow2 >> 1); p += nthreads) {
+                const uint32_t i = 2 * p - (p & (d - 1)), j = i + d;
+                if (j < n) {
+                    const uint64_t a = s[i], b = s[j];
+                    if (a > b) { s[i] = b; s[j] = a; }
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t next_pow2(uint32_t n)
+{
+    return n <= 1 ? 1u : 1u << (32 - __clz(n - 1));
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_smem_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
+                      const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                      uint64_t* __restrict__ keys_sorted, int tiles_per_view, uint32_t lo, uint32_t hi)
+{
+    extern __shared__ uint64_t skeys[];
+    if (num_rendered[1]) return;
+    const uint2 r = ranges[blockIdx.x];
+    const uint32_t n = r.y - r.x;
+    if (n <= lo || n > hi) return;
+    const int tid = threadIdx.x;
+    for (uint32_t k = tid; k < n; k += THREADS) skeys[k] = keys[r.x + k];
+    bitonic_sort_ascending(skeys, n, next_pow2(n), tid, THREADS);
+    const uint64_t tile_hi = (uint64_t)(blockIdx.x % tiles_per_view) << 32;
+    for (uint32_t k = tid; k < n; k += THREADS) {
+        const uint64_t key = skeys[k];
+        point_list[r.x + k] = (uint32_t)key;
+        if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
+    }
+}
+
+// Buckets too long for shared memory: same network, in place in global memory
+// (L2-resident), one block per tile.
+__global__ void __launch_bounds__(1024)
+tile_sort_global_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
+                        uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                        uint64_t* __restrict__ keys_sorted, int tiles_per_view, uint32_t lo)
+{
+    if (num_rendered[1]) return;
+    const uint2 r = ranges[blockIdx.x];
+    const uint32_t n = r.y - r.x;
+    if (n <= lo) return;
+    const int tid = threadIdx.x;
+    volatile uint64_t* seg = keys + r.x;
+    bitonic_sort_ascending(seg, n, next_pow2(n), tid, 1024);
+    const uint64_t tile_hi = (uint64_t)(blockIdx.x % tiles_per_view) << 32;
+    for (uint32_t k = tid; k < n; k += 1024) {
+        const uint64_t key = seg[k];
+        point_list[r.x + k] = (uint32_t)key;
+        if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
+    }
+}
+
+static constexpr uint32_t SORT_SMALL = 2048;    // 16 KB of keys, 256 threads
+static constexpr uint32_t SORT_LARGE = 16384;   // 128 KB of keys, 1024 threads
+
+void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs& b, uint64_t* global_scratch, cudaStream_t s)
+{
+    (void)global_scratch;
+    const int total_tiles = in.V * in.tiles;
+    if (total_tiles == 0) return;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(tile_sort_smem_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(SORT_LARGE * sizeof(uint64_t)));
+        attr_set = true;
+    }
+    tile_sort_smem_kernel<256><<<total_tiles, 256, SORT_SMALL * sizeof(uint64_t), s>>>(
+        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, 0u, SORT_SMALL);
+    tile_sort_smem_kernel<1024><<<total_tiles, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
+        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, SORT_SMALL, SORT_LARGE);
+    tile_sort_global_kernel<<<total_tiles, 1024, 0, s>>>(
+        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, SORT_LARGE);
+    count_launch(3);
+}
+
+}  // namespace guava

@@ -1,0 +1,52 @@
+"""Multi-GPU plumbing: one process per GPU, views / frames sharded across ranks.
+
+The path shards by view: every view is a complete rasterizer
+call, so the forward pass has no cross-GPU traffic.  In training each rank sums
+the per-Gaussian parameter gradients of its local views and ONE fp32
+all-reduce(sum) over the concatenated [P, 3+3+4+1+32 = 43] buffer follows,
+mirroring the DDP all-reduce of the reference trainer (main/trainer.py:40-43,95).
+`torch.distributed` is plumbing: NCCL on the GPU box, gloo in the CPU tests.
+"""
+from __future__ import annotations
+
+from typing import List, Sequence
+
+import torch
+import torch.distributed as dist
+
+GRAD_WIDTHS = (3, 3, 4, 1, 32)   # means3D, scales, rotations, opacity, features
+
+
+def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
+    """Contiguous blocks (frame order is preserved per rank, as for C4's 240 frames)."""
+    if world_size <= 0 or not (0 <= rank < world_size):
+        raise ValueError("bad rank / world_size")
+    base, rem = divmod(num_views, world_size)
+    start = rank * base + min(rank, rem)
+    return list(range(start, start + base + (1 if rank < rem else 0)))
+
+
+def pack_gradients(grads: Sequence[torch.Tensor], out: torch.Tensor = None) -> torch.Tensor:
+    """Sum each [V,P,w] (or [P,w]) gradient over its local views and concatenate into [P,43]."""
+    cols = []
+    for g, w in zip(grads, GRAD_WIDTHS):
+        if g.dim() == 3:
+            g = g.sum(0)
+        if g.shape[-1] != w:
+            raise ValueError(f"expected width {w}, got {tuple(g.shape)}")
+        cols.append(g)
+    if out is None:
+        return torch.cat(cols, dim=1)
+    torch.cat(cols, dim=1, out=out)
+    return out
+
+
+def allreduce_gradients(buf: torch.Tensor, group=None, async_op: bool = False):
+    """In-place sum over ranks of the packed [P,43] buffer."""
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return None
+    return dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+
+def unpack_gradients(buf: torch.Tensor):
+    return torch.split(buf, list(GRAD_WIDTHS), dim=1)

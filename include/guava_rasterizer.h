@@ -1,0 +1,262 @@
+/*
+ * guava_rasterizer.h -- C ABI of the B200-native 32-channel Gaussian-splatting
+ * rasterizer (libguava_rasterizer_b200.so).
+ *
+ * Drop-in boundary.  Every entry point replaces one member of the reference's
+ * C++ library interface `CudaRasterizer::Rasterizer`
+ *   (/root/reference/submodules/diff-gaussian-rasterization-32/
+ *    cuda_rasterizer/rasterizer.h:24-90)
+ * which the reference's torch binding (rasterize_points.cu:35-244) calls.  The
+ * argument order and meaning follow that interface; the differences are the
+ * ones a C ABI forces:
+ *   - `std::function<char*(size_t)>` allocators become a function pointer plus
+ *     an opaque user pointer (same contract: "resize to N bytes, return the
+ *     device pointer"; may be called more than once per buffer);
+ *   - the return value is a status code (0 = ok); `num_rendered` is an out
+ *     parameter; C++ exceptions become codes + guava_last_error();
+ *   - a `stream` argument (cudaStream_t as void*).  The reference launches on
+ *     the legacy default stream; pass NULL for that behaviour;
+ *   - the three opaque buffers (geometry / binning / image) keep their role
+ *     (state handed from forward to backward) but have this library's own
+ *     layout, described by guava_buffer_layout().
+ * No torch types appear here: plain pointers and sizes only.  All pointers are
+ * device pointers unless stated otherwise; all tensors are fp32, contiguous,
+ * in the reference's layouts (means3D [P,3], colors_precomp [P,32], opacities
+ * [P], scales [P,3], rotations [P,4] wxyz *not normalised by the kernel*,
+ * cov3D_precomp [P,6], viewmatrix / projmatrix [16] transposed as in
+ * auxiliary.h:70-89, background [32], out_color [32,H,W], out_invdepth
+ * [1,H,W], radii [P] int32).  `colors_precomp` must be 16-byte aligned (rows
+ * are fetched with 128-byte TMA bulk copies).
+ */
+#ifndef GUAVA_RASTERIZER_H_INCLUDED
+#define GUAVA_RASTERIZER_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GUAVA_NUM_CHANNELS 32 /* cuda_rasterizer/config.h:15 */
+#define GUAVA_BLOCK_X 16      /* config.h:16 */
+#define GUAVA_BLOCK_Y 16      /* config.h:17 */
+
+/* status codes */
+#define GUAVA_OK 0
+#define GUAVA_ERR_INVALID_ARGUMENT 1 /* e.g. colors_precomp == NULL: the reference throws
+                                        "For non-RGB, provide precomputed Gaussian colors!"
+                                        (rasterizer_impl.cu:244-247) */
+#define GUAVA_ERR_CUDA 2             /* a CUDA call / kernel failed; text in guava_last_error() */
+#define GUAVA_ERR_ALLOC 3            /* an allocator callback returned NULL */
+#define GUAVA_ERR_UNSUPPORTED 4      /* spherical harmonics path (unreachable for 32 channels) */
+
+/* Allocator callback: make the buffer `bytes` long and return its device
+ * address (reference: resizeFunctional, rasterize_points.cu:27-33). */
+typedef char *(*guava_alloc_fn)(void *user, size_t bytes);
+
+/* Replaces CudaRasterizer::Rasterizer::forward (rasterizer.h:33-59,
+ * rasterizer_impl.cu:198-340).  D, M, shs, cam_pos and prefiltered are accepted
+ * for signature parity; shs must be NULL (32-channel build). */
+int guava_rasterizer_forward(
+    guava_alloc_fn geometryBuffer, void *geometry_user,
+    guava_alloc_fn binningBuffer, void *binning_user,
+    guava_alloc_fn imageBuffer, void *image_user,
+    int P, int D, int M,
+    const float *background,
+    int width, int height,
+    const float *means3D,
+    const float *shs,
+    const float *colors_precomp,
+    const float *opacities,
+    const float *scales,
+    float scale_modifier,
+    const float *rotations,
+    const float *cov3D_precomp,
+    const float *viewmatrix,
+    const float *projmatrix,
+    const float *cam_pos,
+    float tan_fovx, float tan_fovy,
+    int prefiltered,
+    float *out_color,
+    float *out_invdepth,
+    int antialiasing,
+    int *radii,
+    int debug,
+    void *stream,
+    int *num_rendered);
+
+/* Replaces CudaRasterizer::Rasterizer::backward (rasterizer.h:61-89,
+ * rasterizer_impl.cu:345-450).  R is the num_rendered returned by forward.
+ * dL_dmean2D [P,3], dL_dconic [P,4], dL_dopacity [P], dL_dcolor [P,32],
+ * dL_dinvdepth [P] or NULL must be zero-filled by the caller (as
+ * rasterize_points.cu:163-182 does); dL_dmean3D [P,3], dL_dcov3D [P,6],
+ * dL_dscale [P,3], dL_drot [P,4] are fully written for visible Gaussians and
+ * must be zero-filled for the rest. */
+int guava_rasterizer_backward(
+    int P, int D, int M, int R,
+    const float *background,
+    int width, int height,
+    const float *means3D,
+    const float *shs,
+    const float *colors_precomp,
+    const float *opacities,
+    const float *scales,
+    float scale_modifier,
+    const float *rotations,
+    const float *cov3D_precomp,
+    const float *viewmatrix,
+    const float *projmatrix,
+    const float *campos,
+    float tan_fovx, float tan_fovy,
+    const int *radii,
+    char *geom_buffer,
+    char *binning_buffer,
+    char *image_buffer,
+    const float *dL_dpix,
+    const float *dL_invdepths,
+    float *dL_dmean2D,
+    float *dL_dconic,
+    float *dL_dopacity,
+    float *dL_dcolor,
+    float *dL_dinvdepth,
+    float *dL_dmean3D,
+    float *dL_dcov3D,
+    float *dL_dsh,
+    float *dL_dscale,
+    float *dL_drot,
+    int antialiasing,
+    int debug,
+    void *stream);
+
+/* Replaces CudaRasterizer::Rasterizer::markVisible (rasterizer.h:27-31,
+ * rasterizer_impl.cu:141-153): present[i] = (view-space z > 0.2). */
+int guava_rasterizer_mark_visible(
+    int P,
+    const float *means3D,
+    const float *viewmatrix,
+    const float *projmatrix,
+    uint8_t *present,
+    void *stream);
+
+/* Batched multi-view entry (replaces the per-view Python
+ * loop of models/UbodyAvatar/gaussian_render.py:37-67).  V views of equal
+ * H x W are rasterized by ONE launch chain: tile ids and keys carry the view
+ * index, so per-view slices of every intermediate are identical to V
+ * single-view calls.  Per-view tensors are [V, ...] contiguous; a
+ * `*_view_stride` of 0 (in floats) shares one Gaussian tensor across all views.
+ * tan_fov is a device array [V][2] = (tan_fovx, tan_fovy). */
+int guava_rasterizer_forward_batch(
+    guava_alloc_fn geometryBuffer, void *geometry_user,
+    guava_alloc_fn binningBuffer, void *binning_user,
+    guava_alloc_fn imageBuffer, void *image_user,
+    int V, int P,
+    const float *background,            /* [V,32] */
+    int width, int height,
+    const float *means3D, size_t means3D_view_stride,
+    const float *colors_precomp, size_t colors_view_stride,
+    const float *opacities, size_t opacities_view_stride,
+    const float *scales, size_t scales_view_stride,
+    float scale_modifier,
+    const float *rotations, size_t rotations_view_stride,
+    const float *viewmatrix,            /* [V,16] */
+    const float *projmatrix,            /* [V,16] */
+    const float *tan_fov,               /* [V,2] device */
+    float *out_color,                   /* [V,32,H,W] */
+    float *out_invdepth,                /* [V,1,H,W] */
+    int antialiasing,
+    int *radii,                         /* [V,P] */
+    int debug,
+    void *stream,
+    int *num_rendered);                 /* total over views */
+
+/* Backward of the batched entry.  Gradient tensors are [V,P,...] (one slice
+ * per view; the caller sums over views when the Gaussians were shared). */
+int guava_rasterizer_backward_batch(
+    int V, int P, int R,
+    const float *background,
+    int width, int height,
+    const float *means3D, size_t means3D_view_stride,
+    const float *colors_precomp, size_t colors_view_stride,
+    const float *opacities, size_t opacities_view_stride,
+    const float *scales, size_t scales_view_stride,
+    float scale_modifier,
+    const float *rotations, size_t rotations_view_stride,
+    const float *viewmatrix,
+    const float *projmatrix,
+    const float *tan_fov,
+    const int *radii,
+    char *geom_buffer,
+    char *binning_buffer,
+    char *image_buffer,
+    const float *dL_dpix,               /* [V,32,H,W] */
+    const float *dL_invdepths,          /* [V,1,H,W] or NULL */
+    float *dL_dmean2D,                  /* [V,P,3] zero-filled */
+    float *dL_dconic,                   /* [V,P,4] zero-filled */
+    float *dL_dopacity,                 /* [V,P]   zero-filled */
+    float *dL_dcolor,                   /* [V,P,32] zero-filled */
+    float *dL_dinvdepth,                /* [V,P] zero-filled or NULL */
+    float *dL_dmean3D,                  /* [V,P,3] zero-filled */
+    float *dL_dcov3D,                   /* [V,P,6] zero-filled */
+    float *dL_dscale,                   /* [V,P,3] zero-filled */
+    float *dL_drot,                     /* [V,P,4] zero-filled */
+    int antialiasing,
+    int debug,
+    void *stream);
+
+/* Byte offsets of the arrays inside the three opaque buffers, so that tests
+ * and tools can inspect the intermediates the reference keeps in
+ * GeometryState / BinningState / ImageState (rasterizer_impl.h:33-66). */
+typedef struct guava_layout {
+    /* geometry buffer (per Gaussian instance g = view*P + i) */
+    size_t geom_bytes;
+    size_t splat_rec;      /* float[8] per g: mean2D.x, mean2D.y, conic.x, conic.y, conic.z,
+                              opacity*h_scale, 1/depth (rcp.rn), reserved */
+    size_t depths;         /* float per g (view-space z) */
+    size_t rects;          /* uint16[4] per g: tile rect min.x, min.y, max.x, max.y */
+    size_t tiles_touched;  /* uint32 per g */
+    /* image buffer */
+    size_t image_bytes;
+    size_t final_T;        /* float per pixel  [V*H*W] */
+    size_t n_contrib;      /* uint32 per pixel [V*H*W] */
+    size_t ranges;         /* uint2 per tile   [V*tiles]; values are offsets into point_list */
+    size_t tile_cursor;    /* uint32 per tile (scratch) */
+    size_t num_rendered;   /* uint32[4]: R, capacity-overflow flag, 0, 0 */
+    /* binning buffer for a capacity of `capacity` instances */
+    size_t binning_bytes;
+    size_t point_list;     /* uint32 per instance: Gaussian index within its view, sorted */
+    size_t keys_unsorted;  /* uint64 per instance: depth_bits<<32 | index (tile-bucketed) */
+    size_t keys_sorted;    /* uint64 per instance: tile<<32 | depth_bits; only written when
+                              guava_set_option("emit_sorted_keys", 1) */
+} guava_layout;
+
+int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout *out);
+
+/* Process-wide options (ints): "emit_sorted_keys" (0/1, default 0),
+ * "exact_binning" (0/1, default 0: 1 = wait for num_rendered before sizing the
+ * binning buffer, exactly as rasterizer_impl.cu:283-288 does),
+ * "capacity_hint" (instances; 0 = automatic),
+ * "async_forward" (0/1, default 0: 1 = never wait on the host; *num_rendered is
+ * set to -1 and a capacity overflow is only visible in the image buffer's
+ * num_rendered[1] flag -- for CUDA-graph capture),
+ * "profile_stages" (0/1, default 0: time every kernel with CUDA events, see
+ * guava_stage_time). Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
+int guava_set_option(const char *name, long long value);
+long long guava_get_option(const char *name);
+
+/* Number of kernels this library has launched since load (all threads). */
+unsigned long long guava_launch_count(void);
+
+/* Accumulated device time of one stage while "profile_stages" is on.  Stages:
+ * preprocess, tile_scan, scatter, tile_sort, render_forward, render_backward,
+ * preprocess_backward. */
+int guava_stage_time(const char *stage, double *total_ms, unsigned long long *calls);
+void guava_stage_time_reset(void);
+
+const char *guava_last_error(void);
+const char *guava_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GUAVA_RASTERIZER_H_INCLUDED */

@@ -1,0 +1,300 @@
+"""GPU parity tests (run on the B200 box: `pytest -m gpu`).
+
+Every test drives the CUDA path through the reference-shaped interface
+(`_C.rasterize_gaussians`, `GaussianRasterizer_32`, the batched entry), i.e.
+through the C ABI of libguava_rasterizer_b200.so, and checks it against
+
+  (A) the unmodified reference CUDA build (oracle/_ref, built from
+      /root/reference by oracle/build_ref.py) on identical inputs -- the gate named by
+      BASELINE.json: sorted keys+values, tile ranges, radii, n_contrib bit-exact;
+      features / inverse depth <= 1e-5 absolute; gradients <= 1e-4 relative;
+  (B) the CPU oracle (oracle/splat_oracle.c): bit-exact for everything that does not pass
+      through the hardware exp2 (radii, means2D, depths, conics, keys, lists, ranges),
+      tolerance-based for the compositing outputs;
+  (C) size-independent properties at the full benchmark sizes.
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+import guava_renderer_b200 as grb  # noqa: E402
+import diff_gaussian_rasterization_32 as ours  # noqa: E402
+
+DEV = "cuda:0"
+CAP = 1 << 22
+
+
+@pytest.fixture(autouse=True)
+def _options():
+    grb.set_option("emit_sorted_keys", 1)
+    grb.set_option("capacity_hint", CAP)
+    grb.set_option("exact_binning", 0)
+    yield
+    grb.set_option("emit_sorted_keys", 0)
+    grb.set_option("capacity_hint", 0)
+
+
+@pytest.fixture(scope="module")
+def ref():
+    m = util.import_reference()
+    if m is None:
+        pytest.skip("oracle/_ref (reference CUDA build) not present")
+    return m
+
+
+def _ours_forward(inp, antialiasing=False, scale_modifier=1.0):
+    R, color, radii, geom, binning, img, invd = util.c_forward(ours, inp, DEV, antialiasing, scale_modifier)
+    torch.cuda.synchronize()
+    dec = util.decode_ours(geom, binning, img, 1, inp["xyz"].shape[0], inp["W"], inp["H"], CAP)
+    dec.update(R=R, color=color.cpu().numpy(), radii=radii.cpu().numpy(), invdepth=invd.cpu().numpy())
+    return dec
+
+
+CASES = [
+    dict(P=10_000, H=512, W=512, seed=1000, scale_mult=1.0),            # BASELINE config 1
+    dict(P=3_000, H=200, W=152, seed=21, scale_mult=1.5),               # ragged image, partial tiles
+    dict(P=20_000, H=128, W=256, seed=33, scale_mult=3.0),              # long per-tile lists (> 2048)
+    dict(P=1, H=64, W=64, seed=4, scale_mult=0.02),                     # single Gaussian
+    dict(P=257, H=17, W=33, seed=5, scale_mult=0.2),                    # tiny odd image
+]
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
+@pytest.mark.parametrize("antialiasing", [False, True])
+def test_forward_vs_cpu_oracle(case, antialiasing):
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    f = util.oracle_forward(inp, antialiasing=antialiasing)
+    o = _ours_forward(inp, antialiasing)
+    vis = f["radii"] > 0
+    assert o["R"] == f["num_rendered"] == o["num_rendered"]
+    assert np.array_equal(o["radii"], f["radii"])
+    assert np.array_equal(o["tiles_touched"], f["tiles_touched"])
+    assert np.array_equal(_bits(o["depths"][vis]), _bits(f["depths"][vis]))
+    assert np.array_equal(_bits(o["means2D"][vis]), _bits(f["means2D"][vis]))
+    assert np.array_equal(_bits(o["conic_opacity"][vis]), _bits(f["conic_opacity"][vis]))
+    assert np.array_equal(o["ranges"], f["ranges"])
+    assert np.array_equal(o["point_list"], f["point_list"])
+    assert np.array_equal(o["keys"], f["keys"])
+    # compositing goes through MUFU.EX2 on the GPU and exp2() on the CPU
+    assert np.mean(o["n_contrib"] != f["n_contrib"]) < 2e-3
+    d = np.abs(o["color"] - f["color"])
+    assert np.mean(d > 1e-5) < 2e-3 and np.median(d) < 1e-6, d.max()
+    assert np.mean(np.abs(o["invdepth"] - f["invdepth"]) > 1e-5) < 2e-3
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
+@pytest.mark.parametrize("antialiasing", [False, True])
+def test_forward_vs_reference_build(ref, case, antialiasing):
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    o = _ours_forward(inp, antialiasing)
+    R, color, radii, geom, binning, img, invd = util.c_forward(ref, inp, DEV, antialiasing)
+    torch.cuda.synchronize()
+    r = util.decode_reference(geom, binning, img, inp["xyz"].shape[0], inp["H"], inp["W"], R)
+    radii = radii.cpu().numpy()
+    vis = radii > 0
+    assert o["R"] == R
+    assert np.array_equal(o["radii"], radii)                                   # bit-exact gates
+    assert np.array_equal(o["keys"], r["keys"])
+    assert np.array_equal(o["point_list"], r["point_list"])
+    assert np.array_equal(o["ranges"], r["ranges"])
+    assert np.array_equal(o["n_contrib"], r["n_contrib"])
+    assert np.array_equal(o["tiles_touched"], r["tiles_touched"])              # extra diagnostics
+    assert np.array_equal(_bits(o["depths"][vis]), _bits(r["depths"][vis]))
+    assert np.array_equal(_bits(o["means2D"][vis]), _bits(r["means2D"][vis]))
+    assert np.array_equal(_bits(o["conic_opacity"][vis]), _bits(r["conic_opacity"][vis]))
+    assert np.array_equal(_bits(o["final_T"]), _bits(r["final_T"]))
+    assert np.abs(o["color"] - color.cpu().numpy()).max() <= 1e-5              # tolerance gates
+    assert np.abs(o["invdepth"] - invd.cpu().numpy()).max() <= 1e-5
+
+
+def _run_autograd(mod, inp, dL_dcolor, dL_dinv, antialiasing=False):
+    """The call pattern of models/UbodyAvatar/gaussian_render.py:30-63 for one view."""
+    leaf = {k: inp[k].to(DEV).clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+    mean_2d = torch.zeros_like(leaf["xyz"], requires_grad=True)
+    rast = mod.GaussianRasterizer_32(raster_settings=util.settings_for(mod, inp, DEV, antialiasing))
+    color, radii, invd = rast(means3D=leaf["xyz"], means2D=mean_2d, shs=None, colors_precomp=leaf["features"],
+                              opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"],
+                              cov3D_precomp=None)
+    loss = (color * dL_dcolor.to(DEV)).sum()
+    if dL_dinv is not None:
+        loss = loss + (invd * dL_dinv.to(DEV)).sum()
+    loss.backward()
+    torch.cuda.synchronize()
+    g = {k: v.grad.cpu().numpy() for k, v in leaf.items()}
+    g["means2D"] = mean_2d.grad.cpu().numpy()
+    return color.detach().cpu().numpy(), g
+
+
+GRAD_CASES = [CASES[0], CASES[1], CASES[2]]
+
+
+@pytest.mark.parametrize("case", GRAD_CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
+@pytest.mark.parametrize("with_invdepth", [False, True])
+def test_backward_vs_reference_build(ref, case, with_invdepth):
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(9)
+    dL_dcolor = torch.randn(32, case["H"], case["W"], generator=g)
+    dL_dinv = torch.randn(1, case["H"], case["W"], generator=g) if with_invdepth else None
+    _, go = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
+    _, gr = _run_autograd(ref, inp, dL_dcolor, dL_dinv)
+    for k in gr:
+        assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+
+
+@pytest.mark.parametrize("antialiasing", [False, True])
+def test_backward_vs_cpu_oracle(antialiasing):
+    import oracle
+    case = CASES[1]
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(9)
+    dL_dcolor = torch.randn(32, case["H"], case["W"], generator=g)
+    dL_dinv = torch.randn(1, case["H"], case["W"], generator=g)
+    _, go = _run_autograd(ours, inp, dL_dcolor, dL_dinv, antialiasing)
+    f = util.oracle_forward(inp, antialiasing=antialiasing)
+    gc = oracle.backward(f, dL_dcolor.numpy(), dL_dinv.numpy())
+    names = dict(xyz="dL_dmeans3D", features="dL_dcolors", opacity="dL_dopacity", scaling="dL_dscales",
+                 rotation="dL_drotations", means2D="dL_dmeans2D")
+    for k, n in names.items():
+        e = util.rel_err(go[k], gc[n].reshape(go[k].shape))
+        assert e <= 1e-3, (k, e)
+
+
+def test_batched_entry_equals_per_view_loop():
+    """One launch chain over V views == V single-view calls (bitwise forward, tolerance backward)."""
+    V, P, H, W = 3, 5000, 160, 176
+    views = [util.inputs_for(P, H, W, seed=700 + v, view=v, num_views=V, scale_mult=1.3) for v in range(V)]
+    g = torch.Generator().manual_seed(1)
+    dL = torch.randn(V, 32, H, W, generator=g).to(DEV)
+
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    leaf = {k: stack(k).requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+    cam = {
+        "world_view_transform": stack("viewmatrix"), "full_proj_transform": stack("projmatrix"),
+        "tanfovx": torch.tensor([x["tanfovx"] for x in views]), "tanfovy": torch.tensor([x["tanfovy"] for x in views]),
+        "image_height": torch.tensor([H] * V), "image_width": torch.tensor([W] * V),
+        "camera_center": stack("campos"),
+    }
+    out = grb.render_views(dict(xyz=leaf["xyz"], opacity=leaf["opacity"], scaling=leaf["scaling"],
+                                rotation=leaf["rotation"], features_color=leaf["features"]), cam, bg=0.25)
+    (out["rendered_images"] * dL).sum().backward()
+    torch.cuda.synchronize()
+
+    for v in range(V):
+        inp = dict(views[v]); inp["bg"] = torch.full((32,), 0.25)
+        color, gv = _run_autograd(ours, inp, dL[v].cpu(), None)
+        assert np.array_equal(out["rendered_images"][v].detach().cpu().numpy(), color)
+        o = _ours_forward(inp)
+        assert np.array_equal(out["radiis"][v].cpu().numpy(), o["radii"])
+        for k in ("xyz", "features", "opacity", "scaling", "rotation"):
+            assert util.rel_err(leaf[k].grad[v].cpu().numpy(), gv[k]) <= 1e-4, k
+        assert util.rel_err(out["viewspace_points"].grad[v].cpu().numpy(), gv["means2D"]) <= 1e-4
+
+
+def test_capacity_overflow_is_recovered():
+    inp = util.inputs_for(**CASES[1])
+    a = _ours_forward(inp)
+    grb.set_option("capacity_hint", 512)          # far below num_rendered: forces the re-run path
+    R, color, radii, geom, binning, img, invd = util.c_forward(ours, inp, DEV)
+    torch.cuda.synchronize()
+    assert R == a["R"] > 512
+    assert np.array_equal(color.cpu().numpy(), a["color"])
+    grb.set_option("capacity_hint", 0)
+    grb.set_option("exact_binning", 1)            # the reference's wait-then-allocate order
+    R2, color2, *_ = util.c_forward(ours, inp, DEV)
+    assert R2 == R and np.array_equal(color2.cpu().numpy(), a["color"])
+    grb.set_option("exact_binning", 0)
+
+
+def test_mark_visible_and_empty_inputs():
+    import oracle
+    inp = util.inputs_for(4096, 64, 64, seed=8)
+    inp["xyz"][::3, 2] -= 40.0                     # a third of the points behind the near plane
+    rast = ours.GaussianRasterizer_32(util.settings_for(ours, inp, DEV))
+    vis = rast.markVisible(inp["xyz"].to(DEV)).cpu().numpy()
+    assert np.array_equal(vis, oracle.mark_visible(inp["xyz"].numpy(), inp["viewmatrix"].numpy(), inp["projmatrix"].numpy()))
+    o = _ours_forward(inp)
+    f = util.oracle_forward(inp)
+    assert np.array_equal(o["radii"], f["radii"]) and (o["radii"][::3] == 0).all()
+    # P == 0 (rasterize_points.cu:88): zeros, rendered = 0
+    e = torch.Tensor([])
+    z = torch.zeros(0, 3, device=DEV)
+    R, color, radii, *_ = ours._C.rasterize_gaussians(
+        inp["bg"].to(DEV), z, torch.zeros(0, 32, device=DEV), torch.zeros(0, 1, device=DEV), z, torch.zeros(0, 4, device=DEV),
+        1.0, e, inp["viewmatrix"].to(DEV), inp["projmatrix"].to(DEV), inp["tanfovx"], inp["tanfovy"], 64, 64, e, 0,
+        inp["campos"].to(DEV), False, False, False)
+    assert R == 0 and color.shape == (32, 64, 64) and not color.any() and radii.numel() == 0
+
+
+def test_error_behaviour_matches_reference():
+    inp = util.inputs_for(16, 32, 32, seed=1)
+    rast = ours.GaussianRasterizer_32(util.settings_for(ours, inp, DEV))
+    d = lambda k: inp[k].to(DEV)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        rast(means3D=d("xyz"), means2D=d("xyz"), opacities=d("opacity"), scales=d("scaling"), rotations=d("rotation"))
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        rast(means3D=d("xyz"), means2D=d("xyz"), opacities=d("opacity"), colors_precomp=d("features"))
+    with pytest.raises(RuntimeError, match="means3D must have dimensions"):
+        rast(means3D=d("xyz").reshape(-1), means2D=d("xyz"), opacities=d("opacity"), colors_precomp=d("features"),
+             scales=d("scaling"), rotations=d("rotation"))
+    with pytest.raises(RuntimeError, match="For non-RGB, provide precomputed Gaussian colors"):
+        rast(means3D=d("xyz"), means2D=d("xyz"), opacities=d("opacity"), shs=torch.zeros(16, 1, 3, device=DEV),
+             scales=d("scaling"), rotations=d("rotation"))
+
+
+def test_cov3d_precomp_path():
+    inp = util.inputs_for(2000, 96, 96, seed=12, scale_mult=0.6)
+    f = util.oracle_forward(inp)
+    e = torch.Tensor([])
+    d = lambda k: inp[k].to(DEV)
+    R, color, radii, *_ = ours._C.rasterize_gaussians(
+        d("bg"), d("xyz"), d("features"), d("opacity"), e, e, 1.0, torch.from_numpy(f["cov3D"]).to(DEV),
+        d("viewmatrix"), d("projmatrix"), inp["tanfovx"], inp["tanfovy"], 96, 96, e, 0, d("campos"), False, False, False)
+    assert R == f["num_rendered"] and np.array_equal(radii.cpu().numpy(), f["radii"])
+
+
+def test_full_size_properties():
+    """BASELINE config 2 shape (100k Gaussians, 512x512, 8 views, one launch chain): properties that
+    do not need an oracle run at this size."""
+    V, P, H, W = 8, 100_000, 512, 512
+    from guava_renderer_b200 import synthetic
+    data = synthetic.make_views(2, P, H, W, list(range(V)), V)
+    tanfov = torch.tensor([[data["tanfovx"], data["tanfovy"]]] * V, device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=DEV), 1.0,
+                                        data["viewmatrix"].to(DEV), data["projmatrix"].to(DEV))
+    grb.set_option("capacity_hint", 0)
+    m2 = torch.zeros(V, P, 3, device=DEV)
+    color, radii, invd = grb.rasterize_gaussians_batch(
+        data["xyz"].to(DEV), m2, data["features_color"].to(DEV), data["opacity"].to(DEV),
+        data["scaling"].to(DEV), data["rotation"].to(DEV), st)
+    torch.cuda.synchronize()
+    assert torch.isfinite(color).all() and torch.isfinite(invd).all()
+    assert (radii >= 0).all() and (radii > 0).float().mean() > 0.9
+    # coverage of the synthetic avatar (~39-45 % of the frame)
+    cov = (color.abs().sum(1) > 0).float().mean().item()
+    assert 0.25 < cov < 0.7, cov
+    # view 0 of the batch equals a single-view call on the same inputs
+    inp = dict(xyz=data["xyz"][0], features=data["features_color"][0], opacity=data["opacity"][0],
+               scaling=data["scaling"][0], rotation=data["rotation"][0], viewmatrix=data["viewmatrix"][0],
+               projmatrix=data["projmatrix"][0], campos=data["campos"][0], tanfovx=data["tanfovx"],
+               tanfovy=data["tanfovy"], H=H, W=W, bg=torch.zeros(32))
+    grb.set_option("capacity_hint", CAP)
+    o = _ours_forward(inp)
+    assert np.array_equal(o["color"], color[0].cpu().numpy())
+    keys = o["keys"]
+    assert np.all(keys[1:] >= keys[:-1])                                  # sortedness
+    lens = o["ranges"][:, 1].astype(np.int64) - o["ranges"][:, 0]
+    assert lens.sum() == o["R"] == int(o["tiles_touched"].sum())         # a checksum of checksums
+    same = keys[1:] == keys[:-1]
+    assert np.all(o["point_list"][1:][same] > o["point_list"][:-1][same])  # ties keep index order
