@@ -40,7 +40,7 @@ GUAVA_ERR_UNSUPPORTED = 4
 
 class Layout(Structure):
     _fields_ = [(n, c_size_t) for n in (
-        "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched",
+        "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched", "grad_geo",
         "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "num_rendered",
         "binning_bytes", "point_list", "keys_unsorted", "keys_sorted")]
 
@@ -106,6 +106,10 @@ def load() -> ctypes.CDLL:
     lib.guava_last_error.restype = c_char_p
     lib.guava_version.restype = c_char_p
     _lib = lib
+    # development switches: GUAVA_OPT_<name>=<int> presets an option at load time
+    for k, v in os.environ.items():
+        if k.startswith("GUAVA_OPT_"):
+            lib.guava_set_option(k[len("GUAVA_OPT_"):].lower().encode(), int(v))
     return lib
 
 

@@ -32,6 +32,7 @@ static std::atomic<long long> g_opt_emit_sorted_keys{0};
 static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_async_forward{0};
+static std::atomic<long long> g_opt_scalar_red{0};
 
 static int fail(int code, const std::string& msg)
 {
@@ -120,6 +121,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->depths = o;        o = align_up(o + n * 4);
     L->rects = o;         o = align_up(o + n * 8);
     L->tiles_touched = o; o = align_up(o + n * 4);
+    L->grad_geo = o;      o = align_up(o + n * 32);
     L->geom_bytes = o;
     o = 0;
     L->final_T = o;      o = align_up(o + npix * 4);
@@ -243,6 +245,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     g.depths = (float*)(geom + L.depths);
     g.rects = (ushort4*)(geom + L.rects);
     g.tiles_touched = (uint32_t*)(geom + L.tiles_touched);
+    g.grad_geo = (float*)(geom + L.grad_geo);
     ImagePtrs im;
     im.final_T = (float*)(img + L.final_T);
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
@@ -359,6 +362,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     g.depths = (float*)(geom + L.depths);
     g.rects = (ushort4*)(geom + L.rects);
     g.tiles_touched = (uint32_t*)(geom + L.tiles_touched);
+    g.grad_geo = (float*)(geom + L.grad_geo);
     ImagePtrs im;
     im.final_T = (float*)(img + L.final_T);
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
@@ -371,14 +375,16 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     b.keys_sorted = nullptr;
     b.capacity = 0;
 
+    // 16-byte vector reductions need 16-byte aligned rows (dL_dcolor rows are 128 bytes)
+    const int vec_red = (((uintptr_t)dL_dcolor & 15) == 0) && g_opt_scalar_red.load() == 0;
     StageTimer timer(stream);
     timer.begin(5);
-    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor,
-                           dL_invdepths ? dL_dinvdepth : nullptr, stream);
+    GUAVA_CUDA(cudaMemsetAsync(g.grad_geo, 0, (size_t)in.V * in.P * 32, stream));
+    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, vec_red, stream);
     timer.end();
     GUAVA_STAGE("render_backward", debug);
     timer.begin(6);
-    launch_preprocess_backward(in, g, radii, dL_dmean2D, dL_dconic, dL_invdepths ? dL_dinvdepth : nullptr,
+    launch_preprocess_backward(in, g, radii, dL_invdepths != nullptr, dL_dmean2D, dL_dconic, dL_dinvdepth,
                                dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot, stream);
     timer.end();
     GUAVA_STAGE("preprocess_backward", debug);
@@ -532,6 +538,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "capacity_hint")) return &g_opt_capacity_hint;
     if (!strcmp(name, "async_forward")) return &g_opt_async_forward;
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
+    if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
     return nullptr;
 }
 

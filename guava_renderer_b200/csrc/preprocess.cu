@@ -232,15 +232,27 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 // recomputed from scale/rotation (12 FFMA-chains) instead of being stored by
 // the forward pass and re-read here (24 B/Gaussian each way).
 __global__ void __launch_bounds__(256)
-preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
-                           const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
-                           const float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
+preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const float* __restrict__ grad_geo,
+                           int has_invdepth, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
+                           float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
                            float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
 {
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (gid >= (size_t)in.V * in.P) return;
     if (!(radii[gid] > 0)) return;
+    // packed screen-space gradients accumulated by the backward compositing kernel
+    const float4 gg0 = reinterpret_cast<const float4*>(grad_geo)[2 * gid];       // mean2D.x, .y, conic.x, .y
+    const float4 gg1 = reinterpret_cast<const float4*>(grad_geo)[2 * gid + 1];   // conic.w, opacity, invdepth, -
+    // outputs the reference's binding returns / keeps (rasterize_points.cu:163-172)
+    dL_dmean2D[3 * gid] = gg0.x;
+    dL_dmean2D[3 * gid + 1] = gg0.y;
+    if (dL_dconic != nullptr) {
+        dL_dconic[4 * gid] = gg0.z;
+        dL_dconic[4 * gid + 1] = gg0.w;
+        dL_dconic[4 * gid + 3] = gg1.x;
+    }
+    if (has_invdepth && dL_dinvdepth != nullptr) dL_dinvdepth[gid] = gg1.z;
     const int v = (int)(gid / in.P);
     const int i = (int)(gid - (size_t)v * in.P);
     const float* __restrict__ V = in.viewmatrix + 16 * v;
@@ -264,7 +276,7 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
         cov3d_from_scale_rot(sc, in.scale_modifier, q, c3);
     }
 
-    const float dLc_x = dL_dconic[4 * gid], dLc_y = dL_dconic[4 * gid + 1], dLc_z = dL_dconic[4 * gid + 3];
+    const float dLc_x = gg0.z, dLc_y = gg0.w, dLc_z = gg1.x;
     float tx = xform_row(V, 0, mx, my, mz);
     float ty = xform_row(V, 1, mx, my, mz);
     const float tz = xform_row(V, 2, mx, my, mz);
@@ -301,12 +313,13 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
         c_xx += h_var; c_yy += h_var;
         const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
         const float h_scale = sqrtf(fmaxf(0.000025f, det_cov / det_cov_plus_h_cov));
-        const float dL_dop_v = dL_dopacity[gid];
+        const float dL_dop_v = gg1.y;
         const float d_h_scale = dL_dop_v * in.opacities[(size_t)v * in.opacities_vs + i];
         dL_dopacity[gid] = dL_dop_v * h_scale;
         d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f ? 0.0f : d_h_scale / (2 * h_scale);
     } else {
         c_xx += h_var; c_yy += h_var;
+        dL_dopacity[gid] = gg1.y;
     }
     float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
     if (in.antialiasing) {
@@ -352,7 +365,7 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
     const float dL_dty = y_grad_mul * -h_y * itz2 * dL_dJ12;
     float dL_dtz = -h_x * itz2 * dL_dJ00 - h_y * itz2 * dL_dJ11
                  + (2 * h_x * tx) * itz3 * dL_dJ02 + (2 * h_y * ty) * itz3 * dL_dJ12;
-    if (dL_dinvdepth != nullptr) dL_dtz -= dL_dinvdepth[gid] / (tz * tz);
+    if (has_invdepth) dL_dtz -= gg1.z / (tz * tz);
 
     float gmx = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
     float gmy = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
@@ -362,7 +375,7 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
     const float m_w = 1.0f / (xform_row(proj, 3, mx, my, mz) + 0.0000001f);
     const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
     const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
-    const float g2x = dL_dmean2D[3 * gid], g2y = dL_dmean2D[3 * gid + 1];
+    const float g2x = gg0.x, g2y = gg0.y;
     gmx += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
     gmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
     gmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
@@ -405,16 +418,16 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii,
     }
 }
 
-void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const int* radii,
-                                const float* dL_dmean2D, const float* dL_dconic, const float* dL_dinvdepth,
+void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const int* radii, int has_invdepth,
+                                float* dL_dmean2D, float* dL_dconic, float* dL_dinvdepth,
                                 float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D,
                                 float* dL_dscale, float* dL_drot, cudaStream_t s)
 {
-    (void)g;
     const size_t n = (size_t)in.V * in.P;
     if (n == 0) return;
     preprocess_backward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
-        in, radii, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot);
+        in, radii, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
+        dL_dscale, dL_drot);
     count_launch();
 }
 

@@ -9,16 +9,27 @@
 // B200 design:
 //  * same TMA-staged, double-buffered instance batches as the forward kernel
 //    (SplatRec + 128-byte feature row per instance), walked in reverse;
+//  * warp-footprint culling (splat_may_touch, internal.cuh): each warp owns an
+//    8x4 pixel block and walks only the staged splats that can reach
+//    alpha >= 1/255 somewhere in that block;
 //  * the reference's per-channel recurrence
 //        accum_rec[ch] = last_alpha*last_color[ch] + (1-last_alpha)*accum_rec[ch]
 //        dL_dalpha += (c[ch] - accum_rec[ch]) * dL_dpixel[ch]
 //    is linear in the channel index, so only its contraction with dL_dpixel is
 //    carried:  A = last_alpha*last_d + (1-last_alpha)*A,  d = <c, dL_dpixel>.
 //    That removes 64 live registers per thread;
-//  * per-Gaussian gradients are reduced across the 32 pixels of a warp with a
-//    transposing butterfly (31 shuffles put channel `lane` of the warp total in
-//    lane `lane`) and leave the SM as ONE coalesced 128-byte red.global per
-//    (warp, Gaussian) plus 7 scalar reds, instead of 39 per pixel.
+//  * dL_dcolor[g][ch] = sum over pixels of w(pixel,g) * dL_dpixel[pixel][ch] is
+//    a (32 pixels) x (32 channels) matrix-vector product per (warp, Gaussian)
+//    whose matrix -- the warp's upstream gradients -- never changes.  Each lane
+//    keeps column `lane` of that matrix in registers (transposed once per tile
+//    through shared memory); the 32 blending weights of the warp are exchanged
+//    through 128 bytes of shared memory and every lane does 32 FFMAs.  The
+//    reference's 32 atomics per PIXEL become one 128-byte reduction per WARP,
+//    without the shuffle tree a per-pixel formulation needs;
+//  * the seven geometric partials (mean2D.xy, conic.xyw, opacity, invdepth) are
+//    reduced with a transposing butterfly and leave the SM as one 32-byte
+//    reduction into a packed per-Gaussian record (GeomPtrs::grad_geo) that the
+//    backward preprocess kernel consumes.
 #include "internal.cuh"
 #include "tma.cuh"
 
@@ -32,15 +43,14 @@ struct __align__(128) BwdStage {
     SplatRec rec[BWD_NB];
     uint32_t id[BWD_NB];
 };
+static_assert(2 * sizeof(BwdStage) >= 8 * 32 * 32 * sizeof(float), "stages double as the transpose scratch");
 
-// After the call lane l holds in v[0] the warp-wide sum of element l (N == 32),
-// or of element (l >> (5 - log2 N)) for smaller N once `finish` has run.
-template <int N>
-__device__ __forceinline__ void warp_transpose_reduce(float (&v)[N], int lane)
+// After the call lane 4*k holds in v[0] the warp-wide sum of element k.
+__device__ __forceinline__ void warp_transpose_reduce8(float (&v)[8], int lane)
 {
     int mask = 16;
 #pragma unroll
-    for (int half = N / 2; half >= 1; half >>= 1, mask >>= 1) {
+    for (int half = 4; half >= 1; half >>= 1, mask >>= 1) {
         const bool upper = (lane & mask) != 0;
 #pragma unroll
         for (int i = 0; i < half; i++) {
@@ -49,20 +59,31 @@ __device__ __forceinline__ void warp_transpose_reduce(float (&v)[N], int lane)
             v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
         }
     }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-__global__ void __launch_bounds__(TILE_PIXELS)
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
+{
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+// VEC_RED: 1 = 16-byte vector reductions (red.global.add.v4.f32, 8 + 2 lanes per
+// (warp, Gaussian)); 0 = 4-byte reductions (32 + 8 lanes), for unaligned outputs.
+template <int VEC_RED>
+__global__ void __launch_bounds__(TILE_PIXELS, 2)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                        const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
-                       float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
-                       float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor,
-                       float* __restrict__ dL_dinvdepth)
+                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo)
 {
-    __shared__ BwdStage stage[2];
+    __shared__ __align__(128) unsigned char stage_raw[2 * sizeof(BwdStage)];
     __shared__ __align__(8) uint64_t full_bar[2];
     __shared__ uint32_t warp_max_s[8];
+    __shared__ __align__(16) float wbuf[8][2][32];
+    BwdStage* stage = reinterpret_cast<BwdStage*>(stage_raw);
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -73,6 +94,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const uint32_t py = tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
     const float pxf = (float)px, pyf = (float)py;
+    const float wx0 = (float)(tile_x * TILE_X + (warp & 1) * 8), wy0 = (float)(tile_y * TILE_Y + (warp >> 1) * 4);
     const size_t HW = (size_t)in.H * in.W;
     const size_t pix = (size_t)py * in.W + px;
 
@@ -93,6 +115,35 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const int nbatches = (int)((total + BWD_NB - 1) / BWD_NB);
     if (nbatches == 0) return;
 
+    // upstream gradients of this pixel, all channels (row of the warp's 32x32 matrix) ...
+    float g[NUM_CHANNELS];
+    float g_inv = 0.0f, bgdot = 0.0f;
+    const float T_final = inside ? final_Ts[(size_t)v * HW + pix] : 0.0f;
+    {
+        const float* __restrict__ bg = in.background + (size_t)v * NUM_CHANNELS;
+        const float* __restrict__ gp = dL_dpix + (size_t)v * NUM_CHANNELS * HW + pix;
+#pragma unroll
+        for (int ch = 0; ch < NUM_CHANNELS; ch++) {
+            g[ch] = inside ? gp[(size_t)ch * HW] : 0.0f;
+            bgdot = fmaf(bg[ch], g[ch], bgdot);
+        }
+        if (dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
+    }
+    // ... and channel `lane` of all 32 pixels of the warp (column), through an XOR-swizzled
+    // 32x32 tile per warp in the not-yet-used staging memory (conflict-free both ways).
+    float gT[32];
+    {
+        float* scratch = reinterpret_cast<float*>(stage_raw) + warp * 1024;
+#pragma unroll
+        for (int c = 0; c < NUM_CHANNELS; c++) scratch[lane * 32 + (c ^ lane)] = g[c];
+        __syncwarp();
+#pragma unroll
+        for (int p = 0; p < 32; p++) gT[p] = scratch[p * 32 + (lane ^ p)];
+    }
+    // generic-proxy accesses to the scratch must be ordered before the async-proxy (TMA) writes
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
 
@@ -111,24 +162,11 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     };
     issue(0);
 
-    float g[NUM_CHANNELS];
-    float g_inv = 0.0f, bgdot = 0.0f;
-    const float T_final = inside ? final_Ts[(size_t)v * HW + pix] : 0.0f;
-    {
-        const float* __restrict__ bg = in.background + (size_t)v * NUM_CHANNELS;
-        const float* __restrict__ gp = dL_dpix + (size_t)v * NUM_CHANNELS * HW + pix;
-#pragma unroll
-        for (int ch = 0; ch < NUM_CHANNELS; ch++) {
-            g[ch] = inside ? gp[(size_t)ch * HW] : 0.0f;
-            bgdot = fmaf(bg[ch], g[ch], bgdot);
-        }
-        if (dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
-    }
     const float ddelx_dx = 0.5f * in.W, ddely_dy = 0.5f * in.H;
-
     float T = T_final;
     float A = 0.0f, last_alpha = 0.0f, last_d = 0.0f;
     const size_t gbase = (size_t)v * in.P;
+    uint32_t parity = 0;   // which half of wbuf the next exchange uses
 
     for (int b = 0; b < nbatches; b++) {
         if (b + 1 < nbatches) issue(b + 1);
@@ -136,81 +174,106 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         tma::mbar_wait(&full_bar[s], (uint32_t)((b >> 1) & 1));
         const int nb = min(BWD_NB, (int)total - b * BWD_NB);
         const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
-        for (int j = 0; j < nb; j++) {
-            const uint32_t pos = total - 1 - (uint32_t)(b * BWD_NB + j);
-            if (pos >= warp_max) continue;                      // warp-uniform
-            const float4 r0 = rec4[2 * j];      // x, y, cx, cy
-            const float4 r1 = rec4[2 * j + 1];  // cz, op, rdepth, aux
-            const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
-            const float t1 = fmul(dy, fmul(dy, r1.x));
-            const float sq = ffma(dx, fmul(dx, r0.z), t1);
-            const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
-            const float G = expf(power);
-            const float alpha = fminf(0.99f, fmul(r1.y, G));
-            const bool take = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            if (!__any_sync(0xffffffffu, take)) continue;
+        const uint32_t pos0 = total - 1 - (uint32_t)(b * BWD_NB);   // list position of slot 0
 
-            float vals[NUM_CHANNELS];
-            float geo[8];
-            if (take) {
-                const float om = 1.0f - alpha;
-                T = T / om;
-                const float w = alpha * T;
-                const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[j][0]);
-                float d = 0.0f;
+        uint32_t live[BWD_NB / 32];
 #pragma unroll
-                for (int q = 0; q < NUM_CHANNELS / 4; q++) {
-                    const float4 f = f4[q];
-                    d = fmaf(f.x, g[4 * q + 0], d);
-                    d = fmaf(f.y, g[4 * q + 1], d);
-                    d = fmaf(f.z, g[4 * q + 2], d);
-                    d = fmaf(f.w, g[4 * q + 3], d);
-                    vals[4 * q + 0] = w * g[4 * q + 0];
-                    vals[4 * q + 1] = w * g[4 * q + 1];
-                    vals[4 * q + 2] = w * g[4 * q + 2];
-                    vals[4 * q + 3] = w * g[4 * q + 3];
-                }
-                d = fmaf(r1.z, g_inv, d);
-                A = last_alpha * last_d + (1.0f - last_alpha) * A;
-                last_d = d;
-                float dL_dalpha = (d - A) * T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final / om) * bgdot;
-                const float dL_dG = r1.y * dL_dalpha;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
-                const float dG_ddely = -gdy * r1.x - gdx * r0.w;
-                geo[0] = dL_dG * dG_ddelx * ddelx_dx;
-                geo[1] = dL_dG * dG_ddely * ddely_dy;
-                geo[2] = -0.5f * gdx * dx * dL_dG;
-                geo[3] = -0.5f * gdx * dy * dL_dG;
-                geo[4] = -0.5f * gdy * dy * dL_dG;
-                geo[5] = G * dL_dalpha;
-                geo[6] = w * g_inv;
-                geo[7] = 0.0f;
-            } else {
+        for (int r = 0; r < BWD_NB / 32; r++) {
+            const int j = 32 * r + lane;
+            bool keep = false;
+            if (j < nb && (pos0 - (uint32_t)j) < warp_max) {
+                const float4 c0 = rec4[2 * j], c1 = rec4[2 * j + 1];
+                keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
+            }
+            live[r] = __ballot_sync(0xffffffffu, keep);
+        }
+
 #pragma unroll
-                for (int ch = 0; ch < NUM_CHANNELS; ch++) vals[ch] = 0.0f;
+        for (int r = 0; r < BWD_NB / 32; r++) {
+            uint32_t m = live[r];
+            while (m != 0u) {
+                const int j = 32 * r + __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t pos = pos0 - (uint32_t)j;
+                const float4 r0 = rec4[2 * j];      // x, y, cx, cy
+                const float4 r1 = rec4[2 * j + 1];  // cz, op, rdepth, aux
+                const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
+                const float t1 = fmul(dy, fmul(dy, r1.x));
+                const float sq = ffma(dx, fmul(dx, r0.z), t1);
+                const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, fmul(r1.y, G));
+                const bool take = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (!__any_sync(0xffffffffu, take)) continue;
+
+                float w = 0.0f;
+                float geo[8];
 #pragma unroll
                 for (int k = 0; k < 8; k++) geo[k] = 0.0f;
-            }
-            warp_transpose_reduce<NUM_CHANNELS>(vals, lane);
-            warp_transpose_reduce<8>(geo, lane);
-            geo[0] += __shfl_xor_sync(0xffffffffu, geo[0], 2);
-            geo[0] += __shfl_xor_sync(0xffffffffu, geo[0], 1);
+                if (take) {
+                    const float om = 1.0f - alpha;
+                    T = __fdividef(T, om);
+                    w = alpha * T;
+                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[j][0]);
+                    float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f, d3 = 0.0f;
+#pragma unroll
+                    for (int q = 0; q < NUM_CHANNELS / 4; q++) {
+                        const float4 f = f4[q];
+                        d0 = fmaf(f.x, g[4 * q + 0], d0);
+                        d1 = fmaf(f.y, g[4 * q + 1], d1);
+                        d2 = fmaf(f.z, g[4 * q + 2], d2);
+                        d3 = fmaf(f.w, g[4 * q + 3], d3);
+                    }
+                    const float d = fmaf(r1.z, g_inv, (d0 + d1) + (d2 + d3));
+                    A = last_alpha * last_d + (1.0f - last_alpha) * A;
+                    last_d = d;
+                    float dL_dalpha = (d - A) * T;
+                    last_alpha = alpha;
+                    dL_dalpha += __fdividef(-T_final, om) * bgdot;
+                    const float dL_dG = r1.y * dL_dalpha;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
+                    const float dG_ddely = -gdy * r1.x - gdx * r0.w;
+                    geo[0] = dL_dG * dG_ddelx * ddelx_dx;
+                    geo[1] = dL_dG * dG_ddely * ddely_dy;
+                    geo[2] = -0.5f * gdx * dx * dL_dG;
+                    geo[3] = -0.5f * gdx * dy * dL_dG;
+                    geo[4] = -0.5f * gdy * dy * dL_dG;
+                    geo[5] = G * dL_dalpha;
+                    geo[6] = w * g_inv;
+                }
+                // exchange the warp's 32 weights, then lane c accumulates column c
+                float* wb = &wbuf[warp][parity][0];
+                parity ^= 1u;
+                wb[lane] = w;
+                __syncwarp();
+                const float4* __restrict__ w4 = reinterpret_cast<const float4*>(wb);
+                float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, c3 = 0.0f;
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const float4 ww = w4[q];
+                    c0 = fmaf(ww.x, gT[4 * q + 0], c0);
+                    c1 = fmaf(ww.y, gT[4 * q + 1], c1);
+                    c2 = fmaf(ww.z, gT[4 * q + 2], c2);
+                    c3 = fmaf(ww.w, gT[4 * q + 3], c3);
+                }
+                const float col = (c0 + c1) + (c2 + c3);
+                warp_transpose_reduce8(geo, lane);
 
-            const size_t gi = gbase + stage[s].id[j];
-            atomicAdd(dL_dcolor + gi * NUM_CHANNELS + lane, vals[0]);
-            if ((lane & 3) == 0) {
-                const int k = lane >> 2;
-                float* dst = nullptr;
-                if (k < 2) dst = dL_dmean2D + gi * 3 + k;
-                else if (k == 2) dst = dL_dconic + gi * 4 + 0;
-                else if (k == 3) dst = dL_dconic + gi * 4 + 1;
-                else if (k == 4) dst = dL_dconic + gi * 4 + 3;
-                else if (k == 5) dst = dL_dopacity + gi;
-                else if (k == 6 && dL_dinvdepth != nullptr) dst = dL_dinvdepth + gi;
-                if (dst != nullptr) atomicAdd(dst, geo[0]);
+                const size_t gi = gbase + stage[s].id[j];
+                if (VEC_RED) {
+                    const float a1 = __shfl_down_sync(0xffffffffu, col, 1);
+                    const float a2 = __shfl_down_sync(0xffffffffu, col, 2);
+                    const float a3 = __shfl_down_sync(0xffffffffu, col, 3);
+                    const float b1 = __shfl_down_sync(0xffffffffu, geo[0], 4);
+                    const float b2 = __shfl_down_sync(0xffffffffu, geo[0], 8);
+                    const float b3 = __shfl_down_sync(0xffffffffu, geo[0], 12);
+                    if ((lane & 3) == 0) red_add_v4(dL_dcolor + gi * NUM_CHANNELS + lane, col, a1, a2, a3);
+                    if ((lane & 15) == 0) red_add_v4(grad_geo + gi * 8 + (lane >> 2), geo[0], b1, b2, b3);
+                } else {
+                    atomicAdd(dL_dcolor + gi * NUM_CHANNELS + lane, col);
+                    if ((lane & 3) == 0) atomicAdd(grad_geo + gi * 8 + (lane >> 2), geo[0]);
+                }
             }
         }
         __syncthreads();   // all warps are done with stage s before it is refilled
@@ -218,15 +281,19 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 }
 
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
-                            const float* dL_dpix, const float* dL_dinvdepth_pix,
-                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
-                            float* dL_dcolor, float* dL_dinvdepth, cudaStream_t s)
+                            const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor, int vec_red,
+                            cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     dim3 grid(in.tiles, in.V);
-    render_backward_kernel<<<grid, TILE_PIXELS, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T,
-                                                        img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dmean2D,
-                                                        dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth);
+    if (vec_red)
+        render_backward_kernel<1><<<grid, TILE_PIXELS, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T,
+                                                               img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,
+                                                               g.grad_geo);
+    else
+        render_backward_kernel<0><<<grid, TILE_PIXELS, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T,
+                                                               img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,
+                                                               g.grad_geo);
     count_launch();
 }
 

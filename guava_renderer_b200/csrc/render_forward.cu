@@ -50,6 +50,8 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const uint32_t py = tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
     const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
     const float pxf = (float)px, pyf = (float)py;
+    // this warp's 8x4 pixel block (pixel centres wx0..wx0+7, wy0..wy0+3)
+    const float wx0 = (float)(tile_x * TILE_X + (warp & 1) * 8), wy0 = (float)(tile_y * TILE_Y + (warp >> 1) * 4);
 
     const uint2 range = ranges[(size_t)v * in.tiles + tile];
     const int len = (int)(range.y - range.x);
@@ -94,34 +96,53 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         const int nb = min(FWD_NB, len - b * FWD_NB);
         if (!warp_done) {
             const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
-            for (int j = 0; j < nb; j++) {
-                const float4 r0 = rec4[2 * j];      // x, y, cx, cy
-                const float4 r1 = rec4[2 * j + 1];  // cz, op, rdepth, aux
-                // SASS order of forward.cu:350-353
-                const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
-                const float t1 = fmul(dy, fmul(dy, r1.x));
-                const float sq = ffma(dx, fmul(dx, r0.z), t1);
-                const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
-                bool take = !done && !(power > 0.0f);
-                const float alpha = fminf(fmul(r1.y, expf(power)), 0.99f);
-                take = take && !(alpha < 1.0f / 255.0f);
-                const float test_T = fmul(T, fsub(1.0f, alpha));
-                if (take && test_T < 0.0001f) { done = true; take = false; }
-                if (__any_sync(0xffffffffu, take)) {
-                    const float w = take ? fmul(alpha, T) : 0.0f;
-                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[j][0]);
+            // Warp-footprint culling: lane L tests staged splat 32*r+L against this warp's
+            // 8x4 pixel block; only the survivors are walked (in list order) below.
+            uint32_t live[FWD_NB / 32];
 #pragma unroll
-                    for (int q = 0; q < NUM_CHANNELS / 4; q++) {
-                        const float4 f = f4[q];
-                        C[4 * q + 0] = fmaf(w, f.x, C[4 * q + 0]);
-                        C[4 * q + 1] = fmaf(w, f.y, C[4 * q + 1]);
-                        C[4 * q + 2] = fmaf(w, f.z, C[4 * q + 2]);
-                        C[4 * q + 3] = fmaf(w, f.w, C[4 * q + 3]);
-                    }
-                    D = fmaf(w, r1.z, D);
-                    if (take) { T = test_T; last_contributor = (uint32_t)(b * FWD_NB + j + 1); }
+            for (int r = 0; r < FWD_NB / 32; r++) {
+                const int j = 32 * r + lane;
+                bool keep = false;
+                if (j < nb) {
+                    const float4 c0 = rec4[2 * j], c1 = rec4[2 * j + 1];
+                    keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
                 }
-                if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+                live[r] = __ballot_sync(0xffffffffu, keep);
+            }
+#pragma unroll
+            for (int r = 0; r < FWD_NB / 32; r++) {
+                uint32_t m = live[r];
+                while (m != 0u && !warp_done) {
+                    const int j = 32 * r + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float4 r0 = rec4[2 * j];      // x, y, cx, cy
+                    const float4 r1 = rec4[2 * j + 1];  // cz, op, rdepth, aux
+                    // SASS order of forward.cu:350-353
+                    const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
+                    const float t1 = fmul(dy, fmul(dy, r1.x));
+                    const float sq = ffma(dx, fmul(dx, r0.z), t1);
+                    const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
+                    bool take = !done && !(power > 0.0f);
+                    const float alpha = fminf(fmul(r1.y, expf(power)), 0.99f);
+                    take = take && !(alpha < 1.0f / 255.0f);
+                    const float test_T = fmul(T, fsub(1.0f, alpha));
+                    if (take && test_T < 0.0001f) { done = true; take = false; }
+                    if (__any_sync(0xffffffffu, take)) {
+                        const float w = take ? fmul(alpha, T) : 0.0f;
+                        const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[j][0]);
+#pragma unroll
+                        for (int q = 0; q < NUM_CHANNELS / 4; q++) {
+                            const float4 f = f4[q];
+                            C[4 * q + 0] = fmaf(w, f.x, C[4 * q + 0]);
+                            C[4 * q + 1] = fmaf(w, f.y, C[4 * q + 1]);
+                            C[4 * q + 2] = fmaf(w, f.z, C[4 * q + 2]);
+                            C[4 * q + 3] = fmaf(w, f.w, C[4 * q + 3]);
+                        }
+                        D = fmaf(w, r1.z, D);
+                        if (take) { T = test_T; last_contributor = (uint32_t)(b * FWD_NB + j + 1); }
+                    }
+                    if (__all_sync(0xffffffffu, done)) warp_done = true;
+                }
             }
         }
         // also orders this batch's shared-memory reads before the refill of stage s

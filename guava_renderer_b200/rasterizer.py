@@ -178,13 +178,14 @@ def rasterize_gaussians_backward_C(background, means3D, radii, colors, opacities
     with _device_of(means3D):
         has_inv = dL_dout_invdepth is not None and dL_dout_invdepth.numel() != 0 and dL_dout_invdepth.size(0) != 0
         # one zero fill for all gradient tensors (the reference issues ten)
-        widths = [3, 32, 1, 3, 6, 3, 4, 4] + ([1] if has_inv else [])
+        # dL_dcolors first: its rows must stay 16-byte aligned for the vector reductions
+        widths = [32, 3, 1, 3, 6, 3, 4, 4] + ([1] if has_inv else [])
         flat = torch.zeros(P * sum(widths), dtype=torch.float32, device=dev)
         parts, o = [], 0
         for w in widths:
             parts.append(flat[o:o + P * w].view(P, w))
             o += P * w
-        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations, dL_dconic = parts[:8]
+        dL_dcolors, dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations, dL_dconic = parts[:8]
         dL_dinvdepths = parts[8] if has_inv else None
         dL_dsh = torch.zeros(P, M, 3, dtype=torch.float32, device=dev)
         if P != 0:
@@ -398,14 +399,14 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         dev = m.device
         with _device_of(m):
             has_inv = grad_invdepth is not None
-            widths = [3, 32, 1, 3, 6, 3, 4, 4] + ([1] if has_inv else [])
+            widths = [32, 3, 1, 3, 6, 3, 4, 4] + ([1] if has_inv else [])
             n = V * P
             flat = torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
             parts, off = [], 0
             for w in widths:
                 parts.append(flat[off:off + n * w].view(V, P, w))
                 off += n * w
-            g_mean2D, g_color, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot, g_conic = parts[:8]
+            g_color, g_mean2D, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot, g_conic = parts[:8]
             g_invd = parts[8] if has_inv else None
             if n:
                 gc = _f32c(grad_color)
