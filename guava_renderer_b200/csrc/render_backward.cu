@@ -35,15 +35,11 @@
 
 namespace guava {
 
-constexpr int BWD_NB = 128;
-constexpr uint32_t BWD_BYTES_PER_INST = sizeof(SplatRec) + NUM_CHANNELS * sizeof(float);
-
 struct __align__(128) BwdStage {
-    float feat[BWD_NB][NUM_CHANNELS];
-    SplatRec rec[BWD_NB];
-    uint32_t id[BWD_NB];
+    float feat[32][NUM_CHANNELS];   // 4 KB
+    SplatRec rec[32];               // 1 KB
 };
-static_assert(2 * sizeof(BwdStage) >= 8 * 32 * 32 * sizeof(float), "stages double as the transpose scratch");
+static_assert(sizeof(BwdStage) >= 32 * 32 * sizeof(float), "a stage doubles as the transpose scratch");
 
 // After the call lane 4*k holds in v[0] the warp-wide sum of element k.
 __device__ __forceinline__ void warp_transpose_reduce8(float (&v)[8], int lane)
@@ -69,53 +65,48 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                  : "memory");
 }
 
+// One warp (= one CTA) per 8x4 pixel block, as in the forward kernel: no block
+// barrier, private double-buffered stage of culled survivors.
 // VEC_RED: 1 = 16-byte vector reductions (red.global.add.v4.f32, 8 + 2 lanes per
 // (warp, Gaussian)); 0 = 4-byte reductions (32 + 8 lanes), for unaligned outputs.
 template <int VEC_RED>
-__global__ void __launch_bounds__(TILE_PIXELS, 2)
+__global__ void __launch_bounds__(32, 16)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                        const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo)
 {
-    __shared__ __align__(128) unsigned char stage_raw[2 * sizeof(BwdStage)];
+    __shared__ BwdStage stage[2];
     __shared__ __align__(8) uint64_t full_bar[2];
-    __shared__ uint32_t warp_max_s[8];
-    __shared__ __align__(16) float wbuf[8][2][32];
-    BwdStage* stage = reinterpret_cast<BwdStage*>(stage_raw);
+    __shared__ __align__(16) float wbuf[2][32];
 
-    const int tid = threadIdx.x;
-    const int warp = tid >> 5, lane = tid & 31;
+    const int lane = threadIdx.x;
     const int v = blockIdx.y;
-    const int tile = blockIdx.x;
+    const int tile = blockIdx.x >> 3, sub = blockIdx.x & 7;
     const int tile_x = tile % in.gx, tile_y = tile / in.gx;
-    const uint32_t px = tile_x * TILE_X + (warp & 1) * 8 + (lane & 7);
-    const uint32_t py = tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const uint32_t bx = tile_x * TILE_X + (sub & 1) * 8, by = tile_y * TILE_Y + (sub >> 1) * 4;
+    if (bx >= (uint32_t)in.W || by >= (uint32_t)in.H) return;
+    const uint32_t px = bx + (lane & 7), py = by + (lane >> 3);
     const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
     const float pxf = (float)px, pyf = (float)py;
-    const float wx0 = (float)(tile_x * TILE_X + (warp & 1) * 8), wy0 = (float)(tile_y * TILE_Y + (warp >> 1) * 4);
+    const float wx0 = (float)bx, wy0 = (float)by;
     const size_t HW = (size_t)in.H * in.W;
     const size_t pix = (size_t)py * in.W + px;
 
+    const uint32_t last_contributor = inside ? n_contrib[(size_t)v * HW + pix] : 0u;
+    const int total = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // list entries this block walks
+    if (total == 0) return;
+    const int nchunks = (total + 31) >> 5;
     const uint2 range = ranges[(size_t)v * in.tiles + tile];
 
-    const uint32_t last_contributor = inside ? n_contrib[(size_t)v * HW + pix] : 0u;
-    const uint32_t warp_max = __reduce_max_sync(0xffffffffu, last_contributor);
-    if (lane == 0) warp_max_s[warp] = warp_max;
-    if (tid == 0) {
+    if (lane == 0) {
         tma::mbar_init(&full_bar[0], 1);
         tma::mbar_init(&full_bar[1], 1);
         tma::fence_mbar_init();
     }
-    __syncthreads();
-    uint32_t total = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) total = max(total, warp_max_s[w]);
-    const int nbatches = (int)((total + BWD_NB - 1) / BWD_NB);
-    if (nbatches == 0) return;
 
-    // upstream gradients of this pixel, all channels (row of the warp's 32x32 matrix) ...
+    // upstream gradients of this pixel, all channels (row of the block's 32x32 matrix) ...
     float g[NUM_CHANNELS];
     float g_inv = 0.0f, bgdot = 0.0f;
     const float T_final = inside ? final_Ts[(size_t)v * HW + pix] : 0.0f;
@@ -129,74 +120,82 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         }
         if (dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
     }
-    // ... and channel `lane` of all 32 pixels of the warp (column), through an XOR-swizzled
-    // 32x32 tile per warp in the not-yet-used staging memory (conflict-free both ways).
+    // ... and channel `lane` of all 32 pixels (column), through an XOR-swizzled 32x32 tile
+    // in the not-yet-used staging memory (conflict-free both ways).
     float gT[32];
     {
-        float* scratch = reinterpret_cast<float*>(stage_raw) + warp * 1024;
+        float* scratch = &stage[0].feat[0][0];
 #pragma unroll
         for (int c = 0; c < NUM_CHANNELS; c++) scratch[lane * 32 + (c ^ lane)] = g[c];
         __syncwarp();
 #pragma unroll
         for (int p = 0; p < 32; p++) gT[p] = scratch[p * 32 + (lane ^ p)];
     }
-    // generic-proxy accesses to the scratch must be ordered before the async-proxy (TMA) writes
+    // generic-proxy accesses to the scratch are ordered before the async-proxy (TMA) writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncthreads();
+    __syncwarp();
 
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
+    const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // batch b, slot j  <->  list position  total-1-(b*NB+j)
-    auto issue = [&](int b) {
-        const int s = b & 1;
-        const int nb = min(BWD_NB, (int)total - b * BWD_NB);
-        if (tid == 0) tma::mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nb * BWD_BYTES_PER_INST);
-        if (tid < nb) {
-            const uint32_t id = point_list[range.x + (total - 1 - (uint32_t)(b * BWD_NB + tid))];
-            stage[s].id[tid] = id;
-            tma::bulk_g2s(&stage[s].rec[tid], vrecs + id, sizeof(SplatRec), &full_bar[s]);
-            tma::bulk_g2s(&stage[s].feat[tid][0], vfeat + (size_t)id * NUM_CHANNELS,
-                          NUM_CHANNELS * sizeof(float), &full_bar[s]);
+    // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front)
+    auto prefetch = [&](int c, uint32_t& id_out) -> uint32_t {
+        const int k = (c << 5) + lane;
+        bool keep = false;
+        uint32_t id = 0;
+        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
+        if (k < total) {
+            id = point_list[range.x + (uint32_t)(total - 1 - k)];
+            const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + id);
+            c0 = rp[0];
+            c1 = rp[1];
+            keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         }
+        id_out = id;
+        const uint32_t mask = __ballot_sync(0xffffffffu, keep);
+        if (mask != 0u) {
+            BwdStage& st = stage[c & 1];
+            uint64_t* bar = &full_bar[c & 1];
+            if (lane == 0) tma::mbar_arrive_expect_tx(bar, (uint32_t)__popc(mask) * (NUM_CHANNELS * 4u));
+            __syncwarp();
+            if (keep) {
+                const int slot = __popc(mask & lt_mask);
+                float4* dst = reinterpret_cast<float4*>(&st.rec[slot]);
+                dst[0] = c0;
+                dst[1] = c1;
+                tma::bulk_g2s(&st.feat[slot][0], vfeat + (size_t)id * NUM_CHANNELS, NUM_CHANNELS * sizeof(float), bar);
+            }
+        }
+        return mask;
     };
-    issue(0);
 
     const float ddelx_dx = 0.5f * in.W, ddely_dy = 0.5f * in.H;
     float T = T_final;
     float A = 0.0f, last_alpha = 0.0f, last_d = 0.0f;
     const size_t gbase = (size_t)v * in.P;
     uint32_t parity = 0;   // which half of wbuf the next exchange uses
+    uint32_t phase = 0;
 
-    for (int b = 0; b < nbatches; b++) {
-        if (b + 1 < nbatches) issue(b + 1);
-        const int s = b & 1;
-        tma::mbar_wait(&full_bar[s], (uint32_t)((b >> 1) & 1));
-        const int nb = min(BWD_NB, (int)total - b * BWD_NB);
-        const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
-        const uint32_t pos0 = total - 1 - (uint32_t)(b * BWD_NB);   // list position of slot 0
-
-        uint32_t live[BWD_NB / 32];
-#pragma unroll
-        for (int r = 0; r < BWD_NB / 32; r++) {
-            const int j = 32 * r + lane;
-            bool keep = false;
-            if (j < nb && (pos0 - (uint32_t)j) < warp_max) {
-                const float4 c0 = rec4[2 * j], c1 = rec4[2 * j + 1];
-                keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
-            }
-            live[r] = __ballot_sync(0xffffffffu, keep);
-        }
-
-#pragma unroll
-        for (int r = 0; r < BWD_NB / 32; r++) {
-            uint32_t m = live[r];
+    uint32_t id_cur = 0, id_next = 0;
+    uint32_t mask_cur = prefetch(0, id_cur);
+    for (int c = 0; c < nchunks; c++) {
+        const uint32_t mask_next = (c + 1 < nchunks) ? prefetch(c + 1, id_next) : 0u;
+        const int s = c & 1;
+        if (mask_cur != 0u) {
+            tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
+            phase ^= 1u << s;
+            __syncwarp();
+            const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            uint32_t m = mask_cur;
+            int slot = -1;
             while (m != 0u) {
-                const int j = 32 * r + __ffs(m) - 1;
+                const int jl = __ffs(m) - 1;
                 m &= m - 1;
-                const uint32_t pos = pos0 - (uint32_t)j;
-                const float4 r0 = rec4[2 * j];      // x, y, cx, cy
-                const float4 r1 = rec4[2 * j + 1];  // cz, op, rdepth, aux
+                slot++;
+                const uint32_t pos = (uint32_t)(total - 1 - ((c << 5) + jl));
+                const float4 r0 = rec4[2 * slot];      // x, y, cx, cy
+                const float4 r1 = rec4[2 * slot + 1];  // cz, op, rdepth, aux
                 const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
                 const float t1 = fmul(dy, fmul(dy, r1.x));
                 const float sq = ffma(dx, fmul(dx, r0.z), t1);
@@ -214,7 +213,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     const float om = 1.0f - alpha;
                     T = __fdividef(T, om);
                     w = alpha * T;
-                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[j][0]);
+                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[slot][0]);
                     float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f, d3 = 0.0f;
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
@@ -242,8 +241,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     geo[5] = G * dL_dalpha;
                     geo[6] = w * g_inv;
                 }
-                // exchange the warp's 32 weights, then lane c accumulates column c
-                float* wb = &wbuf[warp][parity][0];
+                // exchange the block's 32 weights, then lane c accumulates column c
+                float* wb = &wbuf[parity][0];
                 parity ^= 1u;
                 wb[lane] = w;
                 __syncwarp();
@@ -260,7 +259,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 const float col = (c0 + c1) + (c2 + c3);
                 warp_transpose_reduce8(geo, lane);
 
-                const size_t gi = gbase + stage[s].id[j];
+                const size_t gi = gbase + __shfl_sync(0xffffffffu, id_cur, jl);
                 if (VEC_RED) {
                     const float a1 = __shfl_down_sync(0xffffffffu, col, 1);
                     const float a2 = __shfl_down_sync(0xffffffffu, col, 2);
@@ -276,7 +275,9 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 }
             }
         }
-        __syncthreads();   // all warps are done with stage s before it is refilled
+        mask_cur = mask_next;
+        id_cur = id_next;
+        __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
     }
 }
 
@@ -285,15 +286,13 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
                             cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
-    dim3 grid(in.tiles, in.V);
+    dim3 grid(in.tiles * 8, in.V);
     if (vec_red)
-        render_backward_kernel<1><<<grid, TILE_PIXELS, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T,
-                                                               img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,
-                                                               g.grad_geo);
+        render_backward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T, img.n_contrib,
+                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo);
     else
-        render_backward_kernel<0><<<grid, TILE_PIXELS, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T,
-                                                               img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,
-                                                               g.grad_geo);
+        render_backward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T, img.n_contrib,
+                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo);
     count_launch();
 }
 
