@@ -107,29 +107,37 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     }
 
     // upstream gradients of this pixel, all channels (row of the block's 32x32 matrix) ...
-    float g[NUM_CHANNELS];
+    float2 g[NUM_CHANNELS / 2];   // channel pairs, for packed FFMA2 (sm_100 fma.rn.f32x2)
     float g_inv = 0.0f, bgdot = 0.0f;
     const float T_final = inside ? final_Ts[(size_t)v * HW + pix] : 0.0f;
     {
         const float* __restrict__ bg = in.background + (size_t)v * NUM_CHANNELS;
         const float* __restrict__ gp = dL_dpix + (size_t)v * NUM_CHANNELS * HW + pix;
 #pragma unroll
-        for (int ch = 0; ch < NUM_CHANNELS; ch++) {
-            g[ch] = inside ? gp[(size_t)ch * HW] : 0.0f;
-            bgdot = fmaf(bg[ch], g[ch], bgdot);
+        for (int ch = 0; ch < NUM_CHANNELS / 2; ch++) {
+            g[ch].x = inside ? gp[(size_t)(2 * ch) * HW] : 0.0f;
+            g[ch].y = inside ? gp[(size_t)(2 * ch + 1) * HW] : 0.0f;
+            bgdot = fmaf(bg[2 * ch], g[ch].x, bgdot);
+            bgdot = fmaf(bg[2 * ch + 1], g[ch].y, bgdot);
         }
         if (dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
     }
     // ... and channel `lane` of all 32 pixels (column), through an XOR-swizzled 32x32 tile
     // in the not-yet-used staging memory (conflict-free both ways).
-    float gT[32];
+    float2 gT[16];   // gT[k] = channel `lane` of pixels 2k, 2k+1
     {
         float* scratch = &stage[0].feat[0][0];
 #pragma unroll
-        for (int c = 0; c < NUM_CHANNELS; c++) scratch[lane * 32 + (c ^ lane)] = g[c];
+        for (int c = 0; c < NUM_CHANNELS / 2; c++) {
+            scratch[lane * 32 + ((2 * c) ^ lane)] = g[c].x;
+            scratch[lane * 32 + ((2 * c + 1) ^ lane)] = g[c].y;
+        }
         __syncwarp();
 #pragma unroll
-        for (int p = 0; p < 32; p++) gT[p] = scratch[p * 32 + (lane ^ p)];
+        for (int p = 0; p < 16; p++) {
+            gT[p].x = scratch[(2 * p) * 32 + (lane ^ (2 * p))];
+            gT[p].y = scratch[(2 * p + 1) * 32 + (lane ^ (2 * p + 1))];
+        }
     }
     // generic-proxy accesses to the scratch are ordered before the async-proxy (TMA) writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -139,20 +147,23 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
     const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front)
-    auto prefetch = [&](int c, uint32_t& id_out) -> uint32_t {
+    constexpr uint32_t NO_ID = 0xffffffffu;
+    // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front); same software
+    // pipeline as the forward kernel (ids two chunks ahead, SplatRecs one chunk ahead).
+    auto load_id = [&](int c) -> uint32_t {
         const int k = (c << 5) + lane;
-        bool keep = false;
-        uint32_t id = 0;
-        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
-        if (k < total) {
-            id = point_list[range.x + (uint32_t)(total - 1 - k)];
+        return k < total ? point_list[range.x + (uint32_t)(total - 1 - k)] : NO_ID;
+    };
+    auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
+        if (id != NO_ID) {
             const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + id);
             c0 = rp[0];
             c1 = rp[1];
-            keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         }
-        id_out = id;
+    };
+    auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
+        const bool keep = id != NO_ID &&
+                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             BwdStage& st = stage[c & 1];
@@ -177,10 +188,20 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     uint32_t parity = 0;   // which half of wbuf the next exchange uses
     uint32_t phase = 0;
 
-    uint32_t id_cur = 0, id_next = 0;
-    uint32_t mask_cur = prefetch(0, id_cur);
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    uint32_t id_cur = load_id(0);
+    uint32_t id_next = load_id(1);
+    load_rec(id_cur, a0, a1);
+    uint32_t mask_cur = stage_chunk(0, id_cur, a0, a1);
+    load_rec(id_next, a0, a1);
+    uint32_t id_nn = load_id(2);
     for (int c = 0; c < nchunks; c++) {
-        const uint32_t mask_next = (c + 1 < nchunks) ? prefetch(c + 1, id_next) : 0u;
+        // id_cur: ids of chunk c (for the gradient addresses); id_next / a0,a1: chunk c+1
+        const uint32_t mask_next = (c + 1 < nchunks) ? stage_chunk(c + 1, id_next, a0, a1) : 0u;
+        const uint32_t id_after = id_next;
+        id_next = id_nn;
+        load_rec(id_next, a0, a1);
+        id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
             tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
@@ -214,16 +235,14 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     T = __fdividef(T, om);
                     w = alpha * T;
                     const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[slot][0]);
-                    float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f, d3 = 0.0f;
+                    float2 d01 = make_float2(0.0f, 0.0f), d23 = d01;
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
                         const float4 f = f4[q];
-                        d0 = fmaf(f.x, g[4 * q + 0], d0);
-                        d1 = fmaf(f.y, g[4 * q + 1], d1);
-                        d2 = fmaf(f.z, g[4 * q + 2], d2);
-                        d3 = fmaf(f.w, g[4 * q + 3], d3);
+                        d01 = __ffma2_rn(make_float2(f.x, f.y), g[2 * q + 0], d01);
+                        d23 = __ffma2_rn(make_float2(f.z, f.w), g[2 * q + 1], d23);
                     }
-                    const float d = fmaf(r1.z, g_inv, (d0 + d1) + (d2 + d3));
+                    const float d = fmaf(r1.z, g_inv, (d01.x + d01.y) + (d23.x + d23.y));
                     A = last_alpha * last_d + (1.0f - last_alpha) * A;
                     last_d = d;
                     float dL_dalpha = (d - A) * T;
@@ -247,16 +266,14 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 wb[lane] = w;
                 __syncwarp();
                 const float4* __restrict__ w4 = reinterpret_cast<const float4*>(wb);
-                float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, c3 = 0.0f;
+                float2 c01 = make_float2(0.0f, 0.0f), c23 = c01;
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
                     const float4 ww = w4[q];
-                    c0 = fmaf(ww.x, gT[4 * q + 0], c0);
-                    c1 = fmaf(ww.y, gT[4 * q + 1], c1);
-                    c2 = fmaf(ww.z, gT[4 * q + 2], c2);
-                    c3 = fmaf(ww.w, gT[4 * q + 3], c3);
+                    c01 = __ffma2_rn(make_float2(ww.x, ww.y), gT[2 * q + 0], c01);
+                    c23 = __ffma2_rn(make_float2(ww.z, ww.w), gT[2 * q + 1], c23);
                 }
-                const float col = (c0 + c1) + (c2 + c3);
+                const float col = (c01.x + c01.y) + (c23.x + c23.y);
                 warp_transpose_reduce8(geo, lane);
 
                 const size_t gi = gbase + __shfl_sync(0xffffffffu, id_cur, jl);
@@ -276,7 +293,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             }
         }
         mask_cur = mask_next;
-        id_cur = id_next;
+        id_cur = id_after;
         __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
     }
 }

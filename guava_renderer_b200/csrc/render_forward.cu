@@ -35,7 +35,7 @@ struct __align__(128) FwdStage {
     SplatRec rec[32];               // 1 KB
 };
 
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32, 20)
 render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       const uint32_t* __restrict__ num_rendered,
@@ -72,20 +72,27 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
     const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // Test list entries [32c, 32c+32) and stage the survivors into stage[c & 1].
-    // Returns the survivor mask (bit = lane = list offset within the chunk).
-    auto prefetch = [&](int c) -> uint32_t {
+    constexpr uint32_t NO_ID = 0xffffffffu;
+    // Software pipeline over 32-entry chunks of the tile list.  While chunk c is blended,
+    // the SplatRecs of chunk c+1 (gathered through ids loaded one iteration earlier) and
+    // the ids of chunk c+2 are in flight; chunk c+1 is tested and its survivors' feature
+    // rows are requested at the top of the next iteration.
+    auto load_id = [&](int c) -> uint32_t {
         const int k = (c << 5) + lane;
-        bool keep = false;
-        uint32_t id = 0;
-        float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
-        if (k < len) {
-            id = point_list[range.x + k];
+        return k < len ? point_list[range.x + k] : NO_ID;
+    };
+    auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
+        if (id != NO_ID) {
             const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + id);
             c0 = rp[0];
             c1 = rp[1];
-            keep = splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         }
+    };
+    // Test chunk c (one list entry per lane) and stage the survivors into stage[c & 1].
+    // Returns the survivor mask (bit = lane = list offset within the chunk).
+    auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
+        const bool keep = id != NO_ID &&
+                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             FwdStage& st = stage[c & 1];
@@ -104,18 +111,28 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     };
 
     float T = 1.0f;
-    float C[NUM_CHANNELS];
+    float2 C[NUM_CHANNELS / 2];   // channel pairs: blended with packed FFMA2 (sm_100 fma.rn.f32x2)
 #pragma unroll
-    for (int ch = 0; ch < NUM_CHANNELS; ch++) C[ch] = 0.0f;
+    for (int ch = 0; ch < NUM_CHANNELS / 2; ch++) C[ch] = make_float2(0.0f, 0.0f);
     float D = 0.0f;
     uint32_t last_contributor = 0;
     bool done = !inside;
     bool warp_done = false;
     uint32_t phase = 0;   // bit s = parity to wait for on full_bar[s]
 
-    uint32_t mask_cur = nchunks > 0 ? prefetch(0) : 0u;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    uint32_t id_next = load_id(0);
+    uint32_t id_nn = load_id(1);
+    load_rec(id_next, a0, a1);
+    uint32_t mask_cur = stage_chunk(0, id_next, a0, a1);
+    id_next = id_nn;
+    load_rec(id_next, a0, a1);
+    id_nn = load_id(2);
     for (int c = 0; c < nchunks; c++) {
-        const uint32_t mask_next = (c + 1 < nchunks) ? prefetch(c + 1) : 0u;
+        const uint32_t mask_next = (c + 1 < nchunks) ? stage_chunk(c + 1, id_next, a0, a1) : 0u;
+        id_next = id_nn;
+        load_rec(id_next, a0, a1);
+        id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
             tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
@@ -141,14 +158,13 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 if (take && test_T < 0.0001f) { done = true; take = false; }
                 if (__any_sync(0xffffffffu, take)) {
                     const float w = take ? fmul(alpha, T) : 0.0f;
+                    const float2 w2 = make_float2(w, w);
                     const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[slot][0]);
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
                         const float4 f = f4[q];
-                        C[4 * q + 0] = fmaf(w, f.x, C[4 * q + 0]);
-                        C[4 * q + 1] = fmaf(w, f.y, C[4 * q + 1]);
-                        C[4 * q + 2] = fmaf(w, f.z, C[4 * q + 2]);
-                        C[4 * q + 3] = fmaf(w, f.w, C[4 * q + 3]);
+                        C[2 * q + 0] = __ffma2_rn(w2, make_float2(f.x, f.y), C[2 * q + 0]);
+                        C[2 * q + 1] = __ffma2_rn(w2, make_float2(f.z, f.w), C[2 * q + 1]);
                     }
                     D = fmaf(w, r1.z, D);
                     if (take) { T = test_T; last_contributor = (uint32_t)((c << 5) + jl + 1); }
@@ -174,7 +190,10 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         const float* __restrict__ bg = in.background + (size_t)v * NUM_CHANNELS;
         float* __restrict__ oc = out_color + (size_t)v * NUM_CHANNELS * HW + pix;
 #pragma unroll
-        for (int ch = 0; ch < NUM_CHANNELS; ch++) oc[(size_t)ch * HW] = fmaf(T, bg[ch], C[ch]);
+        for (int ch = 0; ch < NUM_CHANNELS / 2; ch++) {
+            oc[(size_t)(2 * ch) * HW] = fmaf(T, bg[2 * ch], C[ch].x);
+            oc[(size_t)(2 * ch + 1) * HW] = fmaf(T, bg[2 * ch + 1], C[ch].y);
+        }
         if (out_invdepth != nullptr) out_invdepth[(size_t)v * HW + pix] = D;
     }
 }
