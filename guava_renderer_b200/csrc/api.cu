@@ -127,7 +127,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->final_T = o;      o = align_up(o + npix * 4);
     L->n_contrib = o;    o = align_up(o + npix * 4);
     L->ranges = o;       o = align_up(o + tiles * 8);
-    L->tile_cursor = o;  o = align_up(o + tiles * 4);
+    L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE);
     L->num_rendered = o; o = align_up(o + 16);
     L->image_bytes = o;
     o = 0;
@@ -196,7 +196,7 @@ __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uin
                                     uint32_t* __restrict__ num_rendered, unsigned long long capacity)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) cursor[i] = ranges[i].x;
+    if (i < n) cursor[(size_t)i * CURSOR_STRIDE] = ranges[i].x;
     if (i == 0) num_rendered[1] = ((unsigned long long)num_rendered[0] > capacity) ? 1u : 0u;
 }
 
@@ -260,7 +260,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     const int total_tiles = in.V * in.tiles;
     StageTimer timer(stream);
     timer.begin(0);
-    GUAVA_CUDA(cudaMemsetAsync(im.tile_cursor, 0, (size_t)total_tiles * 4, stream));
+    GUAVA_CUDA(cudaMemsetAsync(im.tile_cursor, 0, (size_t)total_tiles * 4 * CURSOR_STRIDE, stream));
     launch_preprocess_forward(in, g, im, radii, stream);
     timer.end();
     GUAVA_STAGE("preprocess", debug);

@@ -33,7 +33,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     const int ipt = (n + 1023) / 1024;
     const int begin = min(n, tid * ipt), end = min(n, begin + ipt);
     uint32_t local = 0;
-    for (int k = begin; k < end; k++) local += cursor[k];
+    for (int k = begin; k < end; k++) local += cursor[(size_t)k * CURSOR_STRIDE];
     // block-wide exclusive scan of `local`
     uint32_t incl = local;
 #pragma unroll
@@ -55,10 +55,10 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     __syncthreads();
     uint32_t run = incl - local + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
     for (int k = begin; k < end; k++) {
-        const uint32_t c = cursor[k];
+        const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
         // untouched tiles keep (0,0), as the reference's memset leaves them
         ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-        cursor[k] = run;
+        cursor[(size_t)k * CURSOR_STRIDE] = run;
         run += c;
     }
     if (tid == 1023) {
@@ -77,26 +77,63 @@ void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapp
 }
 
 // -------------------------------------------------------------------- scatter
-// One thread per (view, Gaussian): claim a slot in every touched tile's bucket.
-// Slot order inside a bucket is arbitrary (atomics); the tile sort fixes it.
+// Warp-cooperative: the 32 (view, Gaussian) entries of a warp are expanded to
+// their (entry, tile) instances with a warp prefix sum, and every lane claims
+// ONE bucket slot per round, so all of a warp's atomics are in flight together
+// (the reference's duplicateWithKeys walks each rect serially in one thread,
+// rasterizer_impl.cu:98-108).  Slot order inside a bucket is arbitrary
+// (atomics); the tile sort fixes it.
 __global__ void __launch_bounds__(256)
 scatter_kernel(const Inputs in, const GeomPtrs g, const uint32_t* __restrict__ num_rendered,
                uint32_t* __restrict__ cursor, uint64_t* __restrict__ keys, unsigned long long capacity)
 {
     if (num_rendered[1]) return;   // capacity overflow: the host re-runs with a larger buffer
+    const size_t n = (size_t)in.V * in.P;
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (gid >= (size_t)in.V * in.P) return;
-    const ushort4 rc = g.rects[gid];
-    if (rc.z <= rc.x || rc.w <= rc.y) return;
-    const int v = (int)(gid / in.P);
-    const uint32_t i = (uint32_t)(gid - (size_t)v * in.P);
-    const uint64_t key = ((uint64_t)__float_as_uint(g.depths[gid]) << 32) | i;
-    uint32_t* cur = cursor + (size_t)v * in.tiles;
-    for (uint32_t y = rc.y; y < rc.w; y++)
-        for (uint32_t x = rc.x; x < rc.z; x++) {
-            const uint32_t pos = atomicAdd(cur + y * in.gx + x, 1u);
-            if (pos < capacity) keys[pos] = key;
+    const int lane = threadIdx.x & 31;
+    uint32_t rx = 0, ry = 0, w = 0, cnt = 0, v = 0, klo = 0, khi = 0;
+    if (gid < n) {
+        const ushort4 rc = g.rects[gid];
+        if (rc.z > rc.x && rc.w > rc.y) {
+            rx = rc.x; ry = rc.y; w = (uint32_t)(rc.z - rc.x);
+            cnt = w * (uint32_t)(rc.w - rc.y);
+            v = (uint32_t)(gid / in.P);
+            klo = (uint32_t)(gid - (size_t)v * in.P);
+            khi = __float_as_uint(g.depths[gid]);
         }
+    }
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t excl = incl - cnt;
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t t = base + lane;
+        // owner = last lane whose exclusive offset is <= t (binary search over the warp)
+        int owner = 0;
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const uint32_t e = __shfl_sync(0xffffffffu, excl, owner + step);
+            if (e <= t) owner += step;
+        }
+        const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, owner);
+        const uint32_t o_w = __shfl_sync(0xffffffffu, w, owner);
+        const uint32_t o_rx = __shfl_sync(0xffffffffu, rx, owner);
+        const uint32_t o_ry = __shfl_sync(0xffffffffu, ry, owner);
+        const uint32_t o_v = __shfl_sync(0xffffffffu, v, owner);
+        const uint32_t o_klo = __shfl_sync(0xffffffffu, klo, owner);
+        const uint32_t o_khi = __shfl_sync(0xffffffffu, khi, owner);
+        if (t < total) {
+            const uint32_t local = t - o_excl;
+            const uint32_t yy = local / o_w, xx = local - yy * o_w;
+            const size_t tile = (size_t)o_v * in.tiles + (size_t)(o_ry + yy) * in.gx + (o_rx + xx);
+            const uint32_t pos = atomicAdd(cursor + tile * CURSOR_STRIDE, 1u);
+            if (pos < capacity) keys[pos] = ((uint64_t)o_khi << 32) | o_klo;
+        }
+    }
 }
 
 void launch_scatter(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
@@ -171,30 +208,46 @@ tile_sort_smem_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     }
 }
 
-// Buckets too long for shared memory: same network, in place in global memory
-// (L2-resident), one block per tile.
-__global__ void __launch_bounds__(1024)
-tile_sort_global_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
-                        uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                        uint64_t* __restrict__ keys_sorted, int tiles_per_view, uint32_t lo)
-{
-    if (num_rendered[1]) return;
-    const uint2 r = ranges[blockIdx.x];
-    const uint32_t n = r.y - r.x;
-    if (n <= lo) return;
-    const int tid = threadIdx.x;
-    volatile uint64_t* seg = keys + r.x;
-    bitonic_sort_ascending(seg, n, next_pow2(n), tid, 1024);
-    const uint64_t tile_hi = (uint64_t)(blockIdx.x % tiles_per_view) << 32;
-    for (uint32_t k = tid; k < n; k += 1024) {
-        const uint64_t key = seg[k];
-        point_list[r.x + k] = (uint32_t)key;
-        if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
-    }
-}
-
+// Buckets longer than SORT_SMALL are rare (none at the GUAVA shapes): one persistent
+// 1024-thread CTA per SM walks the tile table and sorts them -- in 128 KB of shared
+// memory up to SORT_LARGE keys, beyond that with the same network in place in global
+// memory (L2-resident).  When there is nothing to do the launch costs a few microseconds.
 static constexpr uint32_t SORT_SMALL = 2048;    // 16 KB of keys, 256 threads
 static constexpr uint32_t SORT_LARGE = 16384;   // 128 KB of keys, 1024 threads
+
+__global__ void __launch_bounds__(1024)
+tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
+                       uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
+{
+    extern __shared__ uint64_t skeys[];
+    if (num_rendered[1]) return;
+    const int tid = threadIdx.x;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const uint2 r = ranges[tile];
+        const uint32_t n = r.y - r.x;
+        if (n <= SORT_SMALL) continue;   // block-uniform
+        const uint64_t tile_hi = (uint64_t)(tile % tiles_per_view) << 32;
+        if (n <= SORT_LARGE) {
+            for (uint32_t k = tid; k < n; k += 1024) skeys[k] = keys[r.x + k];
+            bitonic_sort_ascending(skeys, n, next_pow2(n), tid, 1024);
+            for (uint32_t k = tid; k < n; k += 1024) {
+                const uint64_t key = skeys[k];
+                point_list[r.x + k] = (uint32_t)key;
+                if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
+            }
+        } else {
+            volatile uint64_t* seg = keys + r.x;
+            bitonic_sort_ascending(seg, n, next_pow2(n), tid, 1024);
+            for (uint32_t k = tid; k < n; k += 1024) {
+                const uint64_t key = seg[k];
+                point_list[r.x + k] = (uint32_t)key;
+                if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
+            }
+        }
+        __syncthreads();   // skeys is reused by the next tile
+    }
+}
 
 void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs& b, uint64_t* global_scratch, cudaStream_t s)
 {
@@ -203,17 +256,16 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
     if (total_tiles == 0) return;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(tile_sort_smem_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         attr_set = true;
     }
     tile_sort_smem_kernel<256><<<total_tiles, 256, SORT_SMALL * sizeof(uint64_t), s>>>(
         img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, 0u, SORT_SMALL);
-    tile_sort_smem_kernel<1024><<<total_tiles, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
-        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, SORT_SMALL, SORT_LARGE);
-    tile_sort_global_kernel<<<total_tiles, 1024, 0, s>>>(
-        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, SORT_LARGE);
-    count_launch(3);
+    const int big_grid = total_tiles < 148 ? total_tiles : 148;
+    tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
+        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
+    count_launch(2);
 }
 
 }  // namespace guava

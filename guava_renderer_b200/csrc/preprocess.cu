@@ -194,10 +194,10 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
     // rasterizer_impl.cu:280: offsets are taken per tile, so tile ranges fall
     // out of one scan over tiles and num_rendered never has to visit the host
     // before the instance buffers can be filled).
-    uint32_t* tc = tile_count + (size_t)v * in.tiles;
+    uint32_t* tc = tile_count + (size_t)v * in.tiles * CURSOR_STRIDE;
     for (uint32_t y = miny; y < maxy; y++)
         for (uint32_t x = minx; x < maxx; x++)
-            atomicAdd(tc + y * in.gx + x, 1u);
+            atomicAdd(tc + (size_t)(y * in.gx + x) * CURSOR_STRIDE, 1u);
 }
 
 void launch_preprocess_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, int* radii, cudaStream_t s)

@@ -60,6 +60,7 @@ CASES = [
     dict(P=20_000, H=128, W=256, seed=33, scale_mult=3.0),              # long per-tile lists (> 2048)
     dict(P=1, H=64, W=64, seed=4, scale_mult=0.02),                     # single Gaussian
     dict(P=257, H=17, W=33, seed=5, scale_mult=0.2),                    # tiny odd image
+    dict(P=40_000, H=32, W=32, seed=44, scale_mult=1.0),                # 4 tiles, > 16384 instances per tile
 ]
 
 
