@@ -41,7 +41,7 @@ GUAVA_ERR_UNSUPPORTED = 4
 class Layout(Structure):
     _fields_ = [(n, c_size_t) for n in (
         "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched", "grad_geo",
-        "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "num_rendered",
+        "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "tile_order", "num_rendered",
         "binning_bytes", "point_list", "keys_unsorted", "keys_sorted")]
 
 

@@ -128,6 +128,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->n_contrib = o;    o = align_up(o + npix * 4);
     L->ranges = o;       o = align_up(o + tiles * 8);
     L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE);
+    L->tile_order = o;   o = align_up(o + tiles * 4);
     L->num_rendered = o; o = align_up(o + 16);
     L->image_bytes = o;
     o = 0;
@@ -197,7 +198,10 @@ __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uin
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) cursor[(size_t)i * CURSOR_STRIDE] = ranges[i].x;
-    if (i == 0) num_rendered[1] = ((unsigned long long)num_rendered[0] > capacity) ? 1u : 0u;
+    if (i == 0) {
+        num_rendered[1] = ((unsigned long long)num_rendered[0] > capacity) ? 1u : 0u;
+        num_rendered[2] = 0u;
+    }
 }
 
 // ------------------------------------------------------------------- forward
@@ -251,6 +255,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
     im.ranges = (uint2*)(img + L.ranges);
     im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
+    im.tile_order = (uint32_t*)(img + L.tile_order);
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
 
     const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
@@ -368,6 +373,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
     im.ranges = (uint2*)(img + L.ranges);
     im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
+    im.tile_order = (uint32_t*)(img + L.tile_order);
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
     BinningPtrs b;
     b.point_list = (uint32_t*)(bin + L.point_list);   // offset 0 for every capacity

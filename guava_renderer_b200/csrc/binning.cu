@@ -25,15 +25,25 @@ namespace guava {
 
 // ------------------------------------------------------------ scan over tiles
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges,
+tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
 {
     __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t bins[256];
     const int tid = threadIdx.x;
     const int ipt = (n + 1023) / 1024;
     const int begin = min(n, tid * ipt), end = min(n, begin + ipt);
     uint32_t local = 0;
-    for (int k = begin; k < end; k++) local += cursor[(size_t)k * CURSOR_STRIDE];
+    if (tid < 256) bins[tid] = 0u;
+    __syncthreads();
+    // Besides the scan: a longest-list-first order of the tiles (counting sort on 255 - len/8),
+    // in which the persistent compositing kernels pull their work so that the long lists --
+    // each a serial chain through one warp -- start first and the short ones fill the tail.
+    for (int k = begin; k < end; k++) {
+        const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
+        local += c;
+        atomicAdd(&bins[255u - min(c >> 3, 255u)], 1u);
+    }
     // block-wide exclusive scan of `local`
     uint32_t incl = local;
 #pragma unroll
@@ -53,9 +63,15 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         warp_sums[tid] = w;
     }
     __syncthreads();
+    if (tid == 0) {   // 256 bins: serial exclusive scan is cheap enough
+        uint32_t acc = 0;
+        for (int b = 0; b < 256; b++) { const uint32_t c = bins[b]; bins[b] = acc; acc += c; }
+    }
+    __syncthreads();
     uint32_t run = incl - local + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
     for (int k = begin; k < end; k++) {
         const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
+        tile_order[atomicAdd(&bins[255u - min(c >> 3, 255u)], 1u)] = (uint32_t)k;
         // untouched tiles keep (0,0), as the reference's memset leaves them
         ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
         cursor[(size_t)k * CURSOR_STRIDE] = run;
@@ -65,13 +81,15 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         const uint32_t total = warp_sums[31];
         num_rendered[0] = total;
         num_rendered[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
+        num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
+        num_rendered[3] = 0u;
         if (host_R != nullptr) { *host_R = total; __threadfence_system(); }
     }
 }
 
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity, cudaStream_t s)
 {
-    tile_scan_kernel<<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.num_rendered,
+    tile_scan_kernel<<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.tile_order, img.num_rendered,
                                         host_mapped_R, (unsigned long long)capacity);
     count_launch();
 }

@@ -72,39 +72,59 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 template <int VEC_RED>
 __global__ void __launch_bounds__(32, 16)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
-                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                       const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                       const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
-                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo)
+                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ work_counter)
 {
     __shared__ BwdStage stage[2];
     __shared__ __align__(8) uint64_t full_bar[2];
     __shared__ __align__(16) float wbuf[2][32];
 
     const int lane = threadIdx.x;
-    const int v = blockIdx.y;
-    const int tile = blockIdx.x >> 3, sub = blockIdx.x & 7;
-    const int tile_x = tile % in.gx, tile_y = tile / in.gx;
-    const uint32_t bx = tile_x * TILE_X + (sub & 1) * 8, by = tile_y * TILE_Y + (sub >> 1) * 4;
-    if (bx >= (uint32_t)in.W || by >= (uint32_t)in.H) return;
-    const uint32_t px = bx + (lane & 7), py = by + (lane >> 3);
-    const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
-    const float pxf = (float)px, pyf = (float)py;
-    const float wx0 = (float)bx, wy0 = (float)by;
-    const size_t HW = (size_t)in.H * in.W;
-    const size_t pix = (size_t)py * in.W + px;
-
-    const uint32_t last_contributor = inside ? n_contrib[(size_t)v * HW + pix] : 0u;
-    const int total = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // list entries this block walks
-    if (total == 0) return;
-    const int nchunks = (total + 31) >> 5;
-    const uint2 range = ranges[(size_t)v * in.tiles + tile];
-
     if (lane == 0) {
         tma::mbar_init(&full_bar[0], 1);
         tma::mbar_init(&full_bar[1], 1);
         tma::fence_mbar_init();
     }
+    __syncwarp();
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const size_t HW = (size_t)in.H * in.W;
+    const float ddelx_dx = 0.5f * in.W, ddely_dy = 0.5f * in.H;
+    uint32_t parity = 0;   // which half of wbuf the next exchange uses
+    uint32_t phase = 0;    // bit s = parity to wait for on full_bar[s]
+
+    // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
+    const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
+    const uint32_t total_work = blocks_per_view * (uint32_t)in.V;
+    auto fetch_work = [&]() -> uint32_t {
+        uint32_t wk = 0;
+        if (lane == 0) wk = atomicAdd(work_counter, 1u);
+        return __shfl_sync(0xffffffffu, wk, 0);
+    };
+
+  uint32_t work = fetch_work();
+  while (work < total_work) {
+    const uint32_t work_next = fetch_work();
+    const uint32_t gtile = tile_order[work >> 3];   // longest lists first
+    const int sub = (int)(work & 7u);
+    work = work_next;
+    const int v = (int)(gtile / (uint32_t)in.tiles);
+    const int tile = (int)(gtile - (uint32_t)v * (uint32_t)in.tiles);
+    const int tile_x = tile % in.gx, tile_y = tile / in.gx;
+    const uint32_t bx = tile_x * TILE_X + (sub & 1) * 8, by = tile_y * TILE_Y + (sub >> 1) * 4;
+    if (bx >= (uint32_t)in.W || by >= (uint32_t)in.H) continue;
+    const uint32_t px = bx + (lane & 7), py = by + (lane >> 3);
+    const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float wx0 = (float)bx, wy0 = (float)by;
+    const size_t pix = (size_t)py * in.W + px;
+
+    const uint32_t last_contributor = inside ? n_contrib[(size_t)v * HW + pix] : 0u;
+    const int total = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // list entries this block walks
+    if (total == 0) continue;
+    const int nchunks = (total + 31) >> 5;
+    const uint2 range = ranges[(size_t)v * in.tiles + tile];
 
     // upstream gradients of this pixel, all channels (row of the block's 32x32 matrix) ...
     float2 g[NUM_CHANNELS / 2];   // channel pairs, for packed FFMA2 (sm_100 fma.rn.f32x2)
@@ -145,7 +165,6 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
-    const uint32_t lt_mask = (1u << lane) - 1u;
 
     constexpr uint32_t NO_ID = 0xffffffffu;
     // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front); same software
@@ -181,12 +200,9 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         return mask;
     };
 
-    const float ddelx_dx = 0.5f * in.W, ddely_dy = 0.5f * in.H;
     float T = T_final;
     float A = 0.0f, last_alpha = 0.0f, last_d = 0.0f;
     const size_t gbase = (size_t)v * in.P;
-    uint32_t parity = 0;   // which half of wbuf the next exchange uses
-    uint32_t phase = 0;
 
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     uint32_t id_cur = load_id(0);
@@ -296,6 +312,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         id_cur = id_after;
         __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
     }
+  }
 }
 
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
@@ -303,13 +320,18 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
                             cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
-    dim3 grid(in.tiles * 8, in.V);
+    const long long total = (long long)in.tiles * 8 * in.V;
+    const unsigned grid = (unsigned)(total < 148 * 16 ? total : 148 * 16);
+    // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
     if (vec_red)
-        render_backward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T, img.n_contrib,
-                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo);
+        render_backward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T, img.n_contrib,
+                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,
+                                                      img.num_rendered + 3);
     else
-        render_backward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.final_T, img.n_contrib,
-                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo);
+        render_backward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T, img.n_contrib,
+                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,
+                                                      img.num_rendered + 3);
+    cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();
 }
 

@@ -37,8 +37,8 @@ struct __align__(128) FwdStage {
 
 __global__ void __launch_bounds__(32, 20)
 render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
-                      const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                      const uint32_t* __restrict__ num_rendered,
+                      const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                      const uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
@@ -47,11 +47,37 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
     if (num_rendered[1]) return;   // binning overflowed; the host re-runs
     const int lane = threadIdx.x;
-    const int v = blockIdx.y;
-    const int tile = blockIdx.x >> 3, sub = blockIdx.x & 7;
+    if (lane == 0) {
+        tma::mbar_init(&full_bar[0], 1);
+        tma::mbar_init(&full_bar[1], 1);
+        tma::fence_mbar_init();
+    }
+    __syncwarp();
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t phase = 0;   // bit s = parity to wait for on full_bar[s]
+
+    // Persistent warps: the grid is sized to fill the machine once and every warp pulls
+    // 8x4 pixel blocks from a global work counter (num_rendered[2], zeroed by the tile
+    // scan), so SM slots never idle between blocks and empty tiles cost one atomic.
+    const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
+    const uint32_t total_work = blocks_per_view * (uint32_t)in.V;
+    auto fetch_work = [&]() -> uint32_t {
+        uint32_t wk = 0;
+        if (lane == 0) wk = atomicAdd(&num_rendered[2], 1u);
+        return __shfl_sync(0xffffffffu, wk, 0);
+    };
+
+  uint32_t work = fetch_work();
+  while (work < total_work) {
+    const uint32_t work_next = fetch_work();   // in flight while this block is blended
+    const uint32_t gtile = tile_order[work >> 3];   // longest lists first
+    const int sub = (int)(work & 7u);
+    work = work_next;
+    const int v = (int)(gtile / (uint32_t)in.tiles);
+    const int tile = (int)(gtile - (uint32_t)v * (uint32_t)in.tiles);
     const int tile_x = tile % in.gx, tile_y = tile / in.gx;
     const uint32_t bx = tile_x * TILE_X + (sub & 1) * 8, by = tile_y * TILE_Y + (sub >> 1) * 4;
-    if (bx >= (uint32_t)in.W || by >= (uint32_t)in.H) return;   // block entirely outside the image
+    if (bx >= (uint32_t)in.W || by >= (uint32_t)in.H) continue;   // block entirely outside the image
     const uint32_t px = bx + (lane & 7), py = by + (lane >> 3);
     const bool inside = px < (uint32_t)in.W && py < (uint32_t)in.H;
     const float pxf = (float)px, pyf = (float)py;
@@ -61,16 +87,8 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const int len = (int)(range.y - range.x);
     const int nchunks = (len + 31) >> 5;
 
-    if (lane == 0) {
-        tma::mbar_init(&full_bar[0], 1);
-        tma::mbar_init(&full_bar[1], 1);
-        tma::fence_mbar_init();
-    }
-    __syncwarp();
-
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
-    const uint32_t lt_mask = (1u << lane) - 1u;
 
     constexpr uint32_t NO_ID = 0xffffffffu;
     // Software pipeline over 32-entry chunks of the tile list.  While chunk c is blended,
@@ -118,7 +136,6 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     uint32_t last_contributor = 0;
     bool done = !inside;
     bool warp_done = false;
-    uint32_t phase = 0;   // bit s = parity to wait for on full_bar[s]
 
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     uint32_t id_next = load_id(0);
@@ -174,8 +191,11 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             }
         }
         if (warp_done) {
-            // never exit with a bulk copy still in flight
-            if (mask_next != 0u) tma::mbar_wait(&full_bar[s ^ 1], (phase >> (s ^ 1)) & 1u);
+            // never leave the block with a bulk copy still in flight
+            if (mask_next != 0u) {
+                tma::mbar_wait(&full_bar[s ^ 1], (phase >> (s ^ 1)) & 1u);
+                phase ^= 1u << (s ^ 1);
+            }
             break;
         }
         mask_cur = mask_next;
@@ -196,14 +216,17 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         }
         if (out_invdepth != nullptr) out_invdepth[(size_t)v * HW + pix] = D;
     }
+    __syncwarp();   // the stages are reused by the next block
+  }
 }
 
 void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
                            float* out_color, float* out_invdepth, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
-    dim3 grid(in.tiles * 8, in.V);
-    render_forward_kernel<<<grid, 32, 0, s>>>(in, g.rec, img.ranges, b.point_list, img.num_rendered,
+    const long long total = (long long)in.tiles * 8 * in.V;
+    const unsigned grid = (unsigned)(total < 148 * 20 ? total : 148 * 20);
+    render_forward_kernel<<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
                                               img.final_T, img.n_contrib, out_color, out_invdepth);
     count_launch();
 }
