@@ -232,7 +232,8 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 // recomputed from scale/rotation (12 FFMA-chains) instead of being stored by
 // the forward pass and re-read here (24 B/Gaussian each way).
 __global__ void __launch_bounds__(256)
-preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const float* __restrict__ grad_geo,
+preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const SplatRec* __restrict__ recs,
+                           const float* __restrict__ grad_geo,
                            int has_invdepth, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
                            float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
@@ -241,9 +242,22 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (gid >= (size_t)in.V * in.P) return;
     if (!(radii[gid] > 0)) return;
-    // packed screen-space gradients accumulated by the backward compositing kernel
-    const float4 gg0 = reinterpret_cast<const float4*>(grad_geo)[2 * gid];       // mean2D.x, .y, conic.x, .y
-    const float4 gg1 = reinterpret_cast<const float4*>(grad_geo)[2 * gid + 1];   // conic.w, opacity, invdepth, -
+    // Per-Gaussian sums written by the backward compositing kernel: moments of s = dL/dG * G about
+    // the pixel offset d = mean2D - pixel, (sum s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2), then
+    // sum G*dL/dalpha and sum w*dL/dinvdepth.  backward.cu:612-635 in terms of them:
+    const float4 mo0 = reinterpret_cast<const float4*>(grad_geo)[2 * gid];
+    const float4 mo1 = reinterpret_cast<const float4*>(grad_geo)[2 * gid + 1];
+    const float4 rc0 = reinterpret_cast<const float4*>(recs)[2 * gid];       // x, y, conic.x, conic.y
+    const float4 rc1 = reinterpret_cast<const float4*>(recs)[2 * gid + 1];   // conic.z, ...
+    float4 gg0, gg1;
+    gg0.x = -(rc0.z * mo0.x + rc0.w * mo0.y) * (0.5f * in.W);   // dL/dmean2D.x (NDC units, :626)
+    gg0.y = -(rc1.x * mo0.y + rc0.w * mo0.x) * (0.5f * in.H);   // dL/dmean2D.y
+    gg0.z = -0.5f * mo0.z;                                       // dL/dconic.x
+    gg0.w = -0.5f * mo0.w;                                       // dL/dconic.y
+    gg1.x = -0.5f * mo1.x;                                       // dL/dconic.w
+    gg1.y = mo1.y;                                               // dL/dopacity (before antialias scaling)
+    gg1.z = mo1.z;                                               // dL/dinvdepth
+    gg1.w = 0.0f;
     // outputs the reference's binding returns / keeps (rasterize_points.cu:163-172)
     dL_dmean2D[3 * gid] = gg0.x;
     dL_dmean2D[3 * gid + 1] = gg0.y;
@@ -426,7 +440,7 @@ void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const int* 
     const size_t n = (size_t)in.V * in.P;
     if (n == 0) return;
     preprocess_backward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
-        in, radii, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
+        in, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
         dL_dscale, dL_drot);
     count_launch();
 }

@@ -40,24 +40,9 @@ struct __align__(128) BwdStage {
     SplatRec rec[32];               // 1 KB
 };
 static_assert(sizeof(BwdStage) >= 32 * 32 * sizeof(float), "a stage doubles as the transpose scratch");
-
-// After the call lane 4*k holds in v[0] the warp-wide sum of element k.
-__device__ __forceinline__ void warp_transpose_reduce8(float (&v)[8], int lane)
-{
-    int mask = 16;
-#pragma unroll
-    for (int half = 4; half >= 1; half >>= 1, mask >>= 1) {
-        const bool upper = (lane & mask) != 0;
-#pragma unroll
-        for (int i = 0; i < half; i++) {
-            const float send = upper ? v[i] : v[i + half];
-            const float keep = upper ? v[i + half] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
-        }
-    }
-    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
-    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
-}
+// row stride of the exchange buffer: 32 pixels + 4 floats of padding, so that the 8-lane phases of
+// the row-sum LDS.128 (lanes 4k..4k+3 read row k) fall on distinct banks
+constexpr int EX_STRIDE = 36;
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
 {
@@ -79,7 +64,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 {
     __shared__ BwdStage stage[2];
     __shared__ __align__(8) uint64_t full_bar[2];
-    __shared__ __align__(16) float wbuf[2][32];
+    __shared__ __align__(16) float ex[2][8][EX_STRIDE];   // per-survivor exchange, double buffered
 
     const int lane = threadIdx.x;
     if (lane == 0) {
@@ -90,8 +75,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     __syncwarp();
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
-    const float ddelx_dx = 0.5f * in.W, ddely_dy = 0.5f * in.H;
-    uint32_t parity = 0;   // which half of wbuf the next exchange uses
+    uint32_t parity = 0;   // which half of ex the next exchange uses
     uint32_t phase = 0;    // bit s = parity to wait for on full_bar[s]
 
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
@@ -223,16 +207,16 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
             phase ^= 1u << s;
             __syncwarp();
-            const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            const float4* __restrict__ recp = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
+            const uint32_t pos0 = (uint32_t)(total - 1 - (c << 5));   // list position of chunk lane 0
             uint32_t m = mask_cur;
-            int slot = -1;
-            while (m != 0u) {
+            for (; m != 0u; recp += 2, featp += NUM_CHANNELS / 4) {
                 const int jl = __ffs(m) - 1;
                 m &= m - 1;
-                slot++;
-                const uint32_t pos = (uint32_t)(total - 1 - ((c << 5) + jl));
-                const float4 r0 = rec4[2 * slot];      // x, y, cx, cy
-                const float4 r1 = rec4[2 * slot + 1];  // cz, op, rdepth, aux
+                const uint32_t pos = pos0 - (uint32_t)jl;
+                const float4 r0 = recp[0];   // x, y, cx, cy
+                const float4 r1 = recp[1];   // cz, op, rdepth, aux
                 const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
                 const float t1 = fmul(dy, fmul(dy, r1.x));
                 const float sq = ffma(dx, fmul(dx, r0.z), t1);
@@ -242,46 +226,49 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 const bool take = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 if (!__any_sync(0xffffffffu, take)) continue;
 
-                float w = 0.0f;
-                float geo[8];
-#pragma unroll
-                for (int k = 0; k < 8; k++) geo[k] = 0.0f;
+                // Per-pixel partials of this splat: the blending weight w and six moments of
+                // s = dL/dG * G about the pixel offset d (the conic / mean2D / opacity gradients
+                // are linear in them; backward.cu:612-635 is finished per Gaussian by the
+                // backward preprocess kernel).
+                float w = 0.0f, m_x = 0.0f, m_y = 0.0f, m_xx = 0.0f, m_xy = 0.0f, m_yy = 0.0f, m_o = 0.0f;
                 if (take) {
-                    const float om = 1.0f - alpha;
-                    T = __fdividef(T, om);
+                    const float inv_om = __fdividef(1.0f, 1.0f - alpha);
+                    T *= inv_om;
                     w = alpha * T;
-                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[slot][0]);
                     float2 d01 = make_float2(0.0f, 0.0f), d23 = d01;
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
-                        const float4 f = f4[q];
+                        const float4 f = featp[q];
                         d01 = __ffma2_rn(make_float2(f.x, f.y), g[2 * q + 0], d01);
                         d23 = __ffma2_rn(make_float2(f.z, f.w), g[2 * q + 1], d23);
                     }
                     const float d = fmaf(r1.z, g_inv, (d01.x + d01.y) + (d23.x + d23.y));
-                    A = last_alpha * last_d + (1.0f - last_alpha) * A;
+                    A = fmaf(last_alpha, last_d - A, A);   // last_alpha*last_d + (1-last_alpha)*A
                     last_d = d;
-                    float dL_dalpha = (d - A) * T;
                     last_alpha = alpha;
-                    dL_dalpha += __fdividef(-T_final, om) * bgdot;
-                    const float dL_dG = r1.y * dL_dalpha;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
-                    const float dG_ddely = -gdy * r1.x - gdx * r0.w;
-                    geo[0] = dL_dG * dG_ddelx * ddelx_dx;
-                    geo[1] = dL_dG * dG_ddely * ddely_dy;
-                    geo[2] = -0.5f * gdx * dx * dL_dG;
-                    geo[3] = -0.5f * gdx * dy * dL_dG;
-                    geo[4] = -0.5f * gdy * dy * dL_dG;
-                    geo[5] = G * dL_dalpha;
-                    geo[6] = w * g_inv;
+                    const float dL_dalpha = fmaf(d - A, T, -(T_final * inv_om) * bgdot);
+                    m_o = G * dL_dalpha;             // -> dL/dopacity
+                    const float sg = r1.y * m_o;     // dL/dG * G
+                    m_x = sg * dx;
+                    m_y = sg * dy;
+                    m_xx = m_x * dx;
+                    m_xy = m_x * dy;
+                    m_yy = m_y * dy;
                 }
-                // exchange the block's 32 weights, then lane c accumulates column c
-                float* wb = &wbuf[parity][0];
+                // Exchange through shared memory: row k of ex holds partial k of all 32 pixels.
+                float* exb = &ex[parity][0][0];
                 parity ^= 1u;
-                wb[lane] = w;
+                exb[0 * EX_STRIDE + lane] = m_x;
+                exb[1 * EX_STRIDE + lane] = m_y;
+                exb[2 * EX_STRIDE + lane] = m_xx;
+                exb[3 * EX_STRIDE + lane] = m_xy;
+                exb[4 * EX_STRIDE + lane] = m_yy;
+                exb[5 * EX_STRIDE + lane] = m_o;
+                exb[6 * EX_STRIDE + lane] = w * g_inv;
+                exb[7 * EX_STRIDE + lane] = w;
                 __syncwarp();
-                const float4* __restrict__ w4 = reinterpret_cast<const float4*>(wb);
+                // (a) lane c accumulates channel c of dL/dcolor: 32 weights x its column of g
+                const float4* __restrict__ w4 = reinterpret_cast<const float4*>(exb + 7 * EX_STRIDE);
                 float2 c01 = make_float2(0.0f, 0.0f), c23 = c01;
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
@@ -290,22 +277,23 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     c23 = __ffma2_rn(make_float2(ww.z, ww.w), gT[2 * q + 1], c23);
                 }
                 const float col = (c01.x + c01.y) + (c23.x + c23.y);
-                warp_transpose_reduce8(geo, lane);
+                // (b) lanes 4k..4k+3 sum row k (8 pixels each), two shuffles finish it
+                const float4* __restrict__ e4 = reinterpret_cast<const float4*>(exb + (lane >> 2) * EX_STRIDE + (lane & 3) * 8);
+                const float4 ea = e4[0], eb = e4[1];
+                float mom = ((ea.x + ea.y) + (ea.z + ea.w)) + ((eb.x + eb.y) + (eb.z + eb.w));
+                mom += __shfl_xor_sync(0xffffffffu, mom, 1);
+                mom += __shfl_xor_sync(0xffffffffu, mom, 2);
 
                 const size_t gi = gbase + __shfl_sync(0xffffffffu, id_cur, jl);
                 if (VEC_RED) {
                     const float a1 = __shfl_down_sync(0xffffffffu, col, 1);
                     const float a2 = __shfl_down_sync(0xffffffffu, col, 2);
                     const float a3 = __shfl_down_sync(0xffffffffu, col, 3);
-                    const float b1 = __shfl_down_sync(0xffffffffu, geo[0], 4);
-                    const float b2 = __shfl_down_sync(0xffffffffu, geo[0], 8);
-                    const float b3 = __shfl_down_sync(0xffffffffu, geo[0], 12);
                     if ((lane & 3) == 0) red_add_v4(dL_dcolor + gi * NUM_CHANNELS + lane, col, a1, a2, a3);
-                    if ((lane & 15) == 0) red_add_v4(grad_geo + gi * 8 + (lane >> 2), geo[0], b1, b2, b3);
                 } else {
                     atomicAdd(dL_dcolor + gi * NUM_CHANNELS + lane, col);
-                    if ((lane & 3) == 0) atomicAdd(grad_geo + gi * 8 + (lane >> 2), geo[0]);
                 }
+                if ((lane & 3) == 0 && lane < 28) atomicAdd(grad_geo + gi * 8 + (lane >> 2), mom);
             }
         }
         mask_cur = mask_next;

@@ -215,8 +215,9 @@ typedef struct guava_layout {
     size_t depths;         /* float per g (view-space z) */
     size_t rects;          /* uint16[4] per g: tile rect min.x, min.y, max.x, max.y */
     size_t tiles_touched;  /* uint32 per g */
-    size_t grad_geo;       /* float[8] per g, backward scratch (zeroed and filled by backward):
-                              dL/d mean2D.x, mean2D.y, conic.x, conic.y, conic.w, opacity, invdepth, 0 */
+    size_t grad_geo;       /* float[8] per g, backward scratch (zeroed and filled by backward): sums over
+                              contributing pixels of s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2 (s = dL/dG * G,
+                              d = mean2D - pixel), G*dL/dalpha, w*dL/dinvdepth, 0 */
     /* image buffer */
     size_t image_bytes;
     size_t final_T;        /* float per pixel  [V*H*W] */
