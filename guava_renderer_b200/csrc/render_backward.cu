@@ -32,6 +32,7 @@
 //    backward preprocess kernel consumes.
 #include "internal.cuh"
 #include "tma.cuh"
+#include <cstdlib>
 
 namespace guava {
 
@@ -309,7 +310,8 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
-    const unsigned grid = (unsigned)(total < 148 * 16 ? total : 148 * 16);
+    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
+    const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
     if (vec_red)
         render_backward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T, img.n_contrib,

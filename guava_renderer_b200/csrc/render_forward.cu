@@ -27,6 +27,7 @@
 //    (pixel, Gaussian) pair (forward.cu:371-372).
 #include "internal.cuh"
 #include "tma.cuh"
+#include <cstdlib>
 
 namespace guava {
 
@@ -35,7 +36,7 @@ struct __align__(128) FwdStage {
     SplatRec rec[32];               // 1 KB
 };
 
-__global__ void __launch_bounds__(32, 20)
+__global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
@@ -155,39 +156,65 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
             phase ^= 1u << s;
             __syncwarp();   // the staging lanes' SplatRec stores are visible to every lane
-            const float4* __restrict__ rec4 = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            const float4* __restrict__ recp = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
+            const uint32_t pos_base = (uint32_t)(c << 5) + 1u;
             uint32_t m = mask_cur;
-            int slot = 0;
-            while (m != 0u && !warp_done) {
-                const int jl = __ffs(m) - 1;
+            // Survivors are walked two at a time: the state-independent half of each pair
+            // (SplatRec load, power, exp, alpha) is evaluated side by side to overlap its
+            // latency chain; the transmittance updates then run strictly in list order, so
+            // every pixel sees exactly the reference's sequence of operations.
+            for (; m != 0u && !warp_done; recp += 4, featp += 2 * (NUM_CHANNELS / 4)) {
+                const int jl0 = __ffs(m) - 1;
                 m &= m - 1;
-                const float4 r0 = rec4[2 * slot];      // x, y, cx, cy
-                const float4 r1 = rec4[2 * slot + 1];  // cz, op, rdepth, aux
+                const bool has1 = m != 0u;
+                const int jl1 = has1 ? __ffs(m) - 1 : jl0;
+                m &= m - 1;
+                const float4 p0 = recp[0], p1 = recp[1];   // x, y, cx, cy | cz, op, rdepth, aux
+                const float4 q0 = recp[2], q1 = recp[3];   // second of the pair (stale data if !has1)
                 // SASS order of forward.cu:350-353
-                const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
-                const float t1 = fmul(dy, fmul(dy, r1.x));
-                const float sq = ffma(dx, fmul(dx, r0.z), t1);
-                const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
-                bool take = !done && !(power > 0.0f);
-                const float alpha = fminf(fmul(r1.y, expf(power)), 0.99f);
-                take = take && !(alpha < 1.0f / 255.0f);
-                const float test_T = fmul(T, fsub(1.0f, alpha));
-                if (take && test_T < 0.0001f) { done = true; take = false; }
-                if (__any_sync(0xffffffffu, take)) {
-                    const float w = take ? fmul(alpha, T) : 0.0f;
-                    const float2 w2 = make_float2(w, w);
-                    const float4* __restrict__ f4 = reinterpret_cast<const float4*>(&stage[s].feat[slot][0]);
+                const float dx0 = fsub(p0.x, pxf), dy0 = fsub(p0.y, pyf);
+                const float dx1 = fsub(q0.x, pxf), dy1 = fsub(q0.y, pyf);
+                const float pw0 = ffma(ffma(dx0, fmul(dx0, p0.z), fmul(dy0, fmul(dy0, p1.x))), -0.5f,
+                                       -fmul(dy0, fmul(dx0, p0.w)));
+                const float pw1 = ffma(ffma(dx1, fmul(dx1, q0.z), fmul(dy1, fmul(dy1, q1.x))), -0.5f,
+                                       -fmul(dy1, fmul(dx1, q0.w)));
+                const float alpha0 = fminf(fmul(p1.y, expf(pw0)), 0.99f);
+                const float alpha1 = fminf(fmul(q1.y, expf(pw1)), 0.99f);
+                const bool ok0 = !(pw0 > 0.0f) && !(alpha0 < 1.0f / 255.0f);
+                const bool ok1 = has1 && !(pw1 > 0.0f) && !(alpha1 < 1.0f / 255.0f);
+                // in list order
+                bool take0 = !done && ok0;
+                const float test_T0 = fmul(T, fsub(1.0f, alpha0));
+                if (take0 && test_T0 < 0.0001f) { done = true; take0 = false; }
+                const float w0 = take0 ? fmul(alpha0, T) : 0.0f;
+                if (take0) { T = test_T0; last_contributor = pos_base + (uint32_t)jl0; }
+                bool take1 = !done && ok1;
+                const float test_T1 = fmul(T, fsub(1.0f, alpha1));
+                if (take1 && test_T1 < 0.0001f) { done = true; take1 = false; }
+                const float w1 = take1 ? fmul(alpha1, T) : 0.0f;
+                if (take1) { T = test_T1; last_contributor = pos_base + (uint32_t)jl1; }
+                if (__any_sync(0xffffffffu, take0)) {
+                    const float2 w2 = make_float2(w0, w0);
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
-                        const float4 f = f4[q];
+                        const float4 f = featp[q];
                         C[2 * q + 0] = __ffma2_rn(w2, make_float2(f.x, f.y), C[2 * q + 0]);
                         C[2 * q + 1] = __ffma2_rn(w2, make_float2(f.z, f.w), C[2 * q + 1]);
                     }
-                    D = fmaf(w, r1.z, D);
-                    if (take) { T = test_T; last_contributor = (uint32_t)((c << 5) + jl + 1); }
+                    D = fmaf(w0, p1.z, D);
+                }
+                if (__any_sync(0xffffffffu, take1)) {
+                    const float2 w2 = make_float2(w1, w1);
+#pragma unroll
+                    for (int q = 0; q < NUM_CHANNELS / 4; q++) {
+                        const float4 f = featp[NUM_CHANNELS / 4 + q];
+                        C[2 * q + 0] = __ffma2_rn(w2, make_float2(f.x, f.y), C[2 * q + 0]);
+                        C[2 * q + 1] = __ffma2_rn(w2, make_float2(f.z, f.w), C[2 * q + 1]);
+                    }
+                    D = fmaf(w1, q1.z, D);
                 }
                 if (__all_sync(0xffffffffu, done)) warp_done = true;
-                slot++;
             }
         }
         if (warp_done) {
@@ -225,7 +252,8 @@ void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs&
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
-    const unsigned grid = (unsigned)(total < 148 * 20 ? total : 148 * 20);
+    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_FWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
+    const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
     render_forward_kernel<<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
                                               img.final_T, img.n_contrib, out_color, out_invdepth);
     count_launch();
