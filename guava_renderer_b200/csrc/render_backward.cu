@@ -56,7 +56,7 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // VEC_RED: 1 = 16-byte vector reductions (red.global.add.v4.f32, 8 + 2 lanes per
 // (warp, Gaussian)); 0 = 4-byte reductions (32 + 8 lanes), for unaligned outputs.
 template <int VEC_RED>
-__global__ void __launch_bounds__(32, 16)
+__global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                        const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
@@ -65,7 +65,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 {
     __shared__ BwdStage stage[2];
     __shared__ __align__(8) uint64_t full_bar[2];
-    __shared__ __align__(16) float ex[2][8][EX_STRIDE];   // per-survivor exchange, double buffered
+    __shared__ __align__(16) float ex[4][8][EX_STRIDE];   // per-survivor exchange: two pairs in flight
 
     const int lane = threadIdx.x;
     if (lane == 0) {
@@ -76,7 +76,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     __syncwarp();
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
-    uint32_t parity = 0;   // which half of ex the next exchange uses
+    uint32_t parity = 0;   // ex buffers (parity, parity+1) & 3 are used by the next pair
+    float* const exbase = &ex[0][0][0];
     uint32_t phase = 0;    // bit s = parity to wait for on full_bar[s]
 
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
@@ -212,89 +213,145 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
             const uint32_t pos0 = (uint32_t)(total - 1 - (c << 5));   // list position of chunk lane 0
             uint32_t m = mask_cur;
-            for (; m != 0u; recp += 2, featp += NUM_CHANNELS / 4) {
-                const int jl = __ffs(m) - 1;
+            // Survivors are walked two at a time.  Everything that does not depend on the running
+            // transmittance -- SplatRec loads, alpha, the 32-channel dot product -- is evaluated for
+            // both side by side (independent latency chains); the T / accum recurrences then run in
+            // list order; the exchange, the two matrix-vector products and the reductions are again
+            // independent.
+            for (; m != 0u; recp += 4, featp += 2 * (NUM_CHANNELS / 4)) {
+                const int jl0 = __ffs(m) - 1;
                 m &= m - 1;
-                const uint32_t pos = pos0 - (uint32_t)jl;
-                const float4 r0 = recp[0];   // x, y, cx, cy
-                const float4 r1 = recp[1];   // cz, op, rdepth, aux
-                const float dx = fsub(r0.x, pxf), dy = fsub(r0.y, pyf);
-                const float t1 = fmul(dy, fmul(dy, r1.x));
-                const float sq = ffma(dx, fmul(dx, r0.z), t1);
-                const float power = ffma(sq, -0.5f, -fmul(dy, fmul(dx, r0.w)));
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, fmul(r1.y, G));
-                const bool take = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (!__any_sync(0xffffffffu, take)) continue;
+                const bool has1 = m != 0u;
+                const int jl1 = has1 ? __ffs(m) - 1 : jl0;
+                m &= m - 1;
+                const float4 p0 = recp[0], p1 = recp[1];   // x, y, cx, cy | cz, op, rdepth, aux
+                const float4 q0 = recp[2], q1 = recp[3];   // second of the pair (stale data if !has1)
+                const float dx0 = fsub(p0.x, pxf), dy0 = fsub(p0.y, pyf);
+                const float dx1 = fsub(q0.x, pxf), dy1 = fsub(q0.y, pyf);
+                const float pw0 = ffma(ffma(dx0, fmul(dx0, p0.z), fmul(dy0, fmul(dy0, p1.x))), -0.5f,
+                                       -fmul(dy0, fmul(dx0, p0.w)));
+                const float pw1 = ffma(ffma(dx1, fmul(dx1, q0.z), fmul(dy1, fmul(dy1, q1.x))), -0.5f,
+                                       -fmul(dy1, fmul(dx1, q0.w)));
+                const float G0 = expf(pw0), G1 = expf(pw1);
+                const float alpha0 = fminf(0.99f, fmul(p1.y, G0));
+                const float alpha1 = fminf(0.99f, fmul(q1.y, G1));
+                const bool take0 = ((pos0 - (uint32_t)jl0) < last_contributor) && !(pw0 > 0.0f) && !(alpha0 < 1.0f / 255.0f);
+                const bool take1 = has1 && ((pos0 - (uint32_t)jl1) < last_contributor) && !(pw1 > 0.0f) &&
+                                   !(alpha1 < 1.0f / 255.0f);
+                const bool any0 = __any_sync(0xffffffffu, take0);
+                const bool any1 = __any_sync(0xffffffffu, take1);
+                if (!(any0 || any1)) continue;
 
-                // Per-pixel partials of this splat: the blending weight w and six moments of
-                // s = dL/dG * G about the pixel offset d (the conic / mean2D / opacity gradients
-                // are linear in them; backward.cu:612-635 is finished per Gaussian by the
-                // backward preprocess kernel).
-                float w = 0.0f, m_x = 0.0f, m_y = 0.0f, m_xx = 0.0f, m_xy = 0.0f, m_yy = 0.0f, m_o = 0.0f;
-                if (take) {
-                    const float inv_om = __fdividef(1.0f, 1.0f - alpha);
-                    T *= inv_om;
-                    w = alpha * T;
-                    float2 d01 = make_float2(0.0f, 0.0f), d23 = d01;
+                // <features, dL/dpixel> of both splats
+                float2 da = make_float2(0.0f, 0.0f), db = da, dc = da, dd = da;
 #pragma unroll
-                    for (int q = 0; q < NUM_CHANNELS / 4; q++) {
-                        const float4 f = featp[q];
-                        d01 = __ffma2_rn(make_float2(f.x, f.y), g[2 * q + 0], d01);
-                        d23 = __ffma2_rn(make_float2(f.z, f.w), g[2 * q + 1], d23);
-                    }
-                    const float d = fmaf(r1.z, g_inv, (d01.x + d01.y) + (d23.x + d23.y));
-                    A = fmaf(last_alpha, last_d - A, A);   // last_alpha*last_d + (1-last_alpha)*A
-                    last_d = d;
-                    last_alpha = alpha;
-                    const float dL_dalpha = fmaf(d - A, T, -(T_final * inv_om) * bgdot);
-                    m_o = G * dL_dalpha;             // -> dL/dopacity
-                    const float sg = r1.y * m_o;     // dL/dG * G
-                    m_x = sg * dx;
-                    m_y = sg * dy;
-                    m_xx = m_x * dx;
-                    m_xy = m_x * dy;
-                    m_yy = m_y * dy;
+                for (int q = 0; q < NUM_CHANNELS / 4; q++) {
+                    const float4 f = featp[q];
+                    const float4 h = featp[NUM_CHANNELS / 4 + q];
+                    da = __ffma2_rn(make_float2(f.x, f.y), g[2 * q + 0], da);
+                    db = __ffma2_rn(make_float2(f.z, f.w), g[2 * q + 1], db);
+                    dc = __ffma2_rn(make_float2(h.x, h.y), g[2 * q + 0], dc);
+                    dd = __ffma2_rn(make_float2(h.z, h.w), g[2 * q + 1], dd);
                 }
-                // Exchange through shared memory: row k of ex holds partial k of all 32 pixels.
-                float* exb = &ex[parity][0][0];
-                parity ^= 1u;
-                exb[0 * EX_STRIDE + lane] = m_x;
-                exb[1 * EX_STRIDE + lane] = m_y;
-                exb[2 * EX_STRIDE + lane] = m_xx;
-                exb[3 * EX_STRIDE + lane] = m_xy;
-                exb[4 * EX_STRIDE + lane] = m_yy;
-                exb[5 * EX_STRIDE + lane] = m_o;
-                exb[6 * EX_STRIDE + lane] = w * g_inv;
-                exb[7 * EX_STRIDE + lane] = w;
+                const float d0 = fmaf(p1.z, g_inv, (da.x + da.y) + (db.x + db.y));
+                const float d1 = fmaf(q1.z, g_inv, (dc.x + dc.y) + (dd.x + dd.y));
+
+                // Per-pixel partials: the blending weight w and moments of s = dL/dG * G about the
+                // pixel offset d (the conic / mean2D / opacity gradients are linear in them;
+                // backward.cu:612-635 is finished per Gaussian by the backward preprocess kernel).
+                // In list order: first splat ...
+                float w0 = 0.0f, mo0 = 0.0f, w1 = 0.0f, mo1 = 0.0f;
+                {
+                    const float inv_om = __fdividef(1.0f, 1.0f - alpha0);
+                    const float Tn = T * inv_om;
+                    const float An = fmaf(last_alpha, last_d - A, A);   // last_alpha*last_d + (1-last_alpha)*A
+                    const float dLda = fmaf(d0 - An, Tn, -(T_final * inv_om) * bgdot);
+                    if (take0) {
+                        T = Tn; A = An; last_d = d0; last_alpha = alpha0;
+                        w0 = alpha0 * Tn;
+                        mo0 = G0 * dLda;             // -> dL/dopacity
+                    }
+                }
+                // ... then the second
+                {
+                    const float inv_om = __fdividef(1.0f, 1.0f - alpha1);
+                    const float Tn = T * inv_om;
+                    const float An = fmaf(last_alpha, last_d - A, A);
+                    const float dLda = fmaf(d1 - An, Tn, -(T_final * inv_om) * bgdot);
+                    if (take1) {
+                        T = Tn; A = An; last_d = d1; last_alpha = alpha1;
+                        w1 = alpha1 * Tn;
+                        mo1 = G1 * dLda;
+                    }
+                }
+                const float sx0 = (p1.y * mo0) * dx0, sy0 = (p1.y * mo0) * dy0;   // s*dx, s*dy
+                const float sx1 = (q1.y * mo1) * dx1, sy1 = (q1.y * mo1) * dy1;
+                // Exchange through shared memory: row k of an ex buffer holds partial k of all 32 pixels.
+                float* exb0 = exbase + (parity & 3u) * (8 * EX_STRIDE);
+                float* exb1 = exbase + ((parity + 1u) & 3u) * (8 * EX_STRIDE);
+                parity += 2u;
+                exb0[0 * EX_STRIDE + lane] = sx0;
+                exb0[1 * EX_STRIDE + lane] = sy0;
+                exb0[2 * EX_STRIDE + lane] = sx0 * dx0;
+                exb0[3 * EX_STRIDE + lane] = sx0 * dy0;
+                exb0[4 * EX_STRIDE + lane] = sy0 * dy0;
+                exb0[5 * EX_STRIDE + lane] = mo0;
+                exb0[6 * EX_STRIDE + lane] = w0 * g_inv;
+                exb0[7 * EX_STRIDE + lane] = w0;
+                exb1[0 * EX_STRIDE + lane] = sx1;
+                exb1[1 * EX_STRIDE + lane] = sy1;
+                exb1[2 * EX_STRIDE + lane] = sx1 * dx1;
+                exb1[3 * EX_STRIDE + lane] = sx1 * dy1;
+                exb1[4 * EX_STRIDE + lane] = sy1 * dy1;
+                exb1[5 * EX_STRIDE + lane] = mo1;
+                exb1[6 * EX_STRIDE + lane] = w1 * g_inv;
+                exb1[7 * EX_STRIDE + lane] = w1;
                 __syncwarp();
                 // (a) lane c accumulates channel c of dL/dcolor: 32 weights x its column of g
-                const float4* __restrict__ w4 = reinterpret_cast<const float4*>(exb + 7 * EX_STRIDE);
-                float2 c01 = make_float2(0.0f, 0.0f), c23 = c01;
+                const float4* __restrict__ wa = reinterpret_cast<const float4*>(exb0 + 7 * EX_STRIDE);
+                const float4* __restrict__ wb = reinterpret_cast<const float4*>(exb1 + 7 * EX_STRIDE);
+                float2 ca = make_float2(0.0f, 0.0f), cb = ca, cc = ca, cd = ca;
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
-                    const float4 ww = w4[q];
-                    c01 = __ffma2_rn(make_float2(ww.x, ww.y), gT[2 * q + 0], c01);
-                    c23 = __ffma2_rn(make_float2(ww.z, ww.w), gT[2 * q + 1], c23);
+                    const float4 u = wa[q];
+                    const float4 x = wb[q];
+                    ca = __ffma2_rn(make_float2(u.x, u.y), gT[2 * q + 0], ca);
+                    cb = __ffma2_rn(make_float2(u.z, u.w), gT[2 * q + 1], cb);
+                    cc = __ffma2_rn(make_float2(x.x, x.y), gT[2 * q + 0], cc);
+                    cd = __ffma2_rn(make_float2(x.z, x.w), gT[2 * q + 1], cd);
                 }
-                const float col = (c01.x + c01.y) + (c23.x + c23.y);
+                const float col0 = (ca.x + ca.y) + (cb.x + cb.y);
+                const float col1 = (cc.x + cc.y) + (cd.x + cd.y);
                 // (b) lanes 4k..4k+3 sum row k (8 pixels each), two shuffles finish it
-                const float4* __restrict__ e4 = reinterpret_cast<const float4*>(exb + (lane >> 2) * EX_STRIDE + (lane & 3) * 8);
-                const float4 ea = e4[0], eb = e4[1];
-                float mom = ((ea.x + ea.y) + (ea.z + ea.w)) + ((eb.x + eb.y) + (eb.z + eb.w));
-                mom += __shfl_xor_sync(0xffffffffu, mom, 1);
-                mom += __shfl_xor_sync(0xffffffffu, mom, 2);
+                const int eoff = (lane >> 2) * EX_STRIDE + (lane & 3) * 8;
+                const float4* __restrict__ e0 = reinterpret_cast<const float4*>(exb0 + eoff);
+                const float4* __restrict__ e1 = reinterpret_cast<const float4*>(exb1 + eoff);
+                const float4 ea = e0[0], eb = e0[1], ec = e1[0], ed = e1[1];
+                float mom0 = ((ea.x + ea.y) + (ea.z + ea.w)) + ((eb.x + eb.y) + (eb.z + eb.w));
+                float mom1 = ((ec.x + ec.y) + (ec.z + ec.w)) + ((ed.x + ed.y) + (ed.z + ed.w));
+                mom0 += __shfl_xor_sync(0xffffffffu, mom0, 1);
+                mom1 += __shfl_xor_sync(0xffffffffu, mom1, 1);
+                mom0 += __shfl_xor_sync(0xffffffffu, mom0, 2);
+                mom1 += __shfl_xor_sync(0xffffffffu, mom1, 2);
 
-                const size_t gi = gbase + __shfl_sync(0xffffffffu, id_cur, jl);
+                const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
+                const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
+                const bool geo_lane = (lane & 3) == 0 && lane < 28;
                 if (VEC_RED) {
-                    const float a1 = __shfl_down_sync(0xffffffffu, col, 1);
-                    const float a2 = __shfl_down_sync(0xffffffffu, col, 2);
-                    const float a3 = __shfl_down_sync(0xffffffffu, col, 3);
-                    if ((lane & 3) == 0) red_add_v4(dL_dcolor + gi * NUM_CHANNELS + lane, col, a1, a2, a3);
+                    const float a1 = __shfl_down_sync(0xffffffffu, col0, 1);
+                    const float a2 = __shfl_down_sync(0xffffffffu, col0, 2);
+                    const float a3 = __shfl_down_sync(0xffffffffu, col0, 3);
+                    const float b1 = __shfl_down_sync(0xffffffffu, col1, 1);
+                    const float b2 = __shfl_down_sync(0xffffffffu, col1, 2);
+                    const float b3 = __shfl_down_sync(0xffffffffu, col1, 3);
+                    if (any0 && (lane & 3) == 0) red_add_v4(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
+                    if (any1 && (lane & 3) == 0) red_add_v4(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
                 } else {
-                    atomicAdd(dL_dcolor + gi * NUM_CHANNELS + lane, col);
+                    if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
+                    if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
                 }
-                if ((lane & 3) == 0 && lane < 28) atomicAdd(grad_geo + gi * 8 + (lane >> 2), mom);
+                if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
+                if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
             }
         }
         mask_cur = mask_next;
@@ -310,7 +367,7 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
-    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
+    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 12; }();   // tuning knob
     const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
     if (vec_red)
