@@ -143,7 +143,7 @@ def run_own(args, rank, world, device):
         sets_dev.append(e)
     gbuf = torch.zeros(P, 43, device=device)
 
-    def step_resident(i):
+    def step_resident_eager(i):
         s = sets_dev[i % len(sets_dev)]
         leaves = [s[k].detach().requires_grad_(True) for k in ("xyz", "sc", "rot", "op", "feat")]
         st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, s["vm"], s["pm"])
@@ -153,6 +153,22 @@ def run_own(args, rank, world, device):
         sharding.pack_gradients([leaves[0].grad, leaves[1].grad, leaves[2].grad, leaves[3].grad, leaves[4].grad], out=gbuf)
         sharding.allreduce_gradients(gbuf)
         return color
+
+    # The product's step call: the whole launch chain (forward, loss, backward, gradient packing) of one
+    # input set captured once as a CUDA graph (guava_renderer_b200.GraphedRenderStep) and replayed.
+    def settings_of(vm, pm):
+        return grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, vm, pm)
+
+    graphed = not args.eager
+    if graphed:
+        g_res = [grb.GraphedRenderStep(s["xyz"], s["feat"], s["op"], s["sc"], s["rot"], settings_of(s["vm"], s["pm"]),
+                                       dL_dcolor=dL, packed_out=gbuf) for s in sets_dev]
+
+    def step_resident(i):
+        if not graphed:
+            return step_resident_eager(i)
+        g_res[i % len(g_res)].replay()
+        sharding.allreduce_gradients(gbuf)
 
     # host-input arm for `e2e`: double-buffered H2D on a copy stream
     copy_stream = torch.cuda.Stream(device=device)
@@ -172,9 +188,24 @@ def run_own(args, rank, world, device):
                 b[k].copy_(s[k], non_blocking=True)
             b["ev"].record(copy_stream)
 
+    if graphed:
+        for i, b in enumerate(stage):      # valid contents while the steps are captured
+            for k in TENSOR_KEYS + ("cams",):
+                b[k].copy_(sets_host[i % len(sets_host)][k])
+        g_e2e = [grb.GraphedRenderStep(b["xyz"], b["feat"], b["op"], b["sc"], b["rot"],
+                                       settings_of(b["cams"][:, :16].reshape(V, 4, 4), b["cams"][:, 16:].reshape(V, 4, 4)),
+                                       dL_dcolor=dL, packed_out=gbuf) for b in stage]
+
     def step_e2e(i, last):
         b = stage[i % 2]
         torch.cuda.current_stream(device).wait_event(b["ev"])
+        if graphed:
+            g = g_e2e[i % 2]
+            g.replay()
+            sharding.allreduce_gradients(gbuf)
+            res = torch.stack([g.loss, gbuf.abs().sum()])
+            result_host.copy_(res, non_blocking=True)
+            return res
         leaves = [b[k].detach().requires_grad_(True) for k in TENSOR_KEYS]
         st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, b["cams"][:, :16].reshape(V, 4, 4),
                                             b["cams"][:, 16:].reshape(V, 4, 4))
@@ -212,6 +243,8 @@ def run_own(args, rank, world, device):
     e1.record()
     barrier()
     launches = grb.launch_count() - n0
+    if graphed:   # replays do not pass through the library's launch counter: count what each replay launches
+        launches = sum(g_res[(args.warmup + i) % len(g_res)].launches_per_replay for i in range(args.steps))
     ms_res = e0.elapsed_time(e1)
 
     # ---- e2e timing (host inputs)
@@ -228,6 +261,7 @@ def run_own(args, rank, world, device):
         prefetch(k + 1)                       # next step's H2D overlaps this step's kernels
         step_e2e(k, i == args.steps - 1)
     e3.record()
+    t_enq = (time.perf_counter() - t_wall0) * 1e3   # host time to enqueue the timed steps
     barrier()
     _ = float(result_host[0])                 # the D2H result is consumed on the host
     t_wall = (time.perf_counter() - t_wall0) * 1e3
@@ -239,8 +273,11 @@ def run_own(args, rank, world, device):
     grb._lib_mod.stage_times_reset()
     prof_steps = 5
     for i in range(prof_steps):
-        step_resident(i)
+        step_resident_eager(i)
     torch.cuda.synchronize(device)
+    if graphed:
+        for g in g_res + g_e2e:
+            g.check()      # no replay overflowed its captured binning capacity
     grb.set_option("profile_stages", 0)
     stages = grb._lib_mod.stage_times()
     roof = roofline_object(stages, sets_dev[0], tanfov, bg, dL, P, H, W, V, device)
@@ -252,7 +289,7 @@ def run_own(args, rank, world, device):
     pix = V * world * H * W * args.steps
     return dict(ms_res=ms_res, ms_e2e=ms_e2e, pix=pix, launches=int(launches), clocks=clk, roofline=roof,
                 h2d=h2d_bytes, d2h=d2h_bytes, stages={k: (v[0] / max(v[1], 1)) for k, v in stages.items()},
-                wall_ms_e2e=t_wall)
+                wall_ms_e2e=t_wall, enqueue_ms_e2e=t_enq)
 
 
 def roofline_object(stages, s, tanfov, bg, dL, P, H, W, V, device):
@@ -443,6 +480,7 @@ def main():
     ap.add_argument("--views-per-gpu", type=int, default=VIEWS_PER_GPU)
     ap.add_argument("--view-sets", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="enqueue every step op by op instead of replaying CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -475,9 +513,11 @@ def main():
             "config": {"workload": workload_name(args), "P": args.P, "H": args.H, "W": args.W,
                        "views_per_gpu": args.views_per_gpu, "global_views_per_step": args.views_per_gpu * world,
                        "parallelism": f"view-sharded x{world}",
+                       "step_call": "eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)",
                        "l2": f"inputs rotate over {args.view_sets} distinct view sets; per-step working set ~230 MB > 126 MB L2"},
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "ms_per_step": round(r["ms_e2e"] / args.steps, 4)},
+                    "ms_per_step": round(r["ms_e2e"] / args.steps, 4),
+                    "host_enqueue_ms_per_step": round(r["enqueue_ms_e2e"] / args.steps, 4)},
             "gpu_launches": r["launches"],
             "clocks": r["clocks"],
             "roofline": r["roofline"],

@@ -1,0 +1,122 @@
+"""CUDA-graph capture of a fixed-shape render step (forward [+ loss + backward + gradient packing]).
+
+At GUAVA sizes one batched forward+backward is < 1 ms of GPU work, i.e. the same order as the host
+time PyTorch needs to enqueue it (~60 tensor ops); the reference additionally blocks on a device->host
+copy per view (rasterizer_impl.cu:284).  `GraphedRenderStep` records the whole launch chain once -- the
+C-ABI forward in its no-host-wait mode (option "async_forward"), the loss, the C-ABI backward and the
+packing of the per-Gaussian gradients -- and replays it with one call, so the step costs what its kernels
+cost.  Inputs are STATIC device tensors (the graph reads their storage on every replay; refresh them
+with `copy_`), exactly as for torch.cuda.graphs whole-network capture.
+
+The binning buffer of a captured forward has a fixed capacity (learnt from eager warm-up runs on the
+same inputs, +25 %).  Every replay copies the library's overflow flag to pinned host memory;
+`check()` raises if a replay ever needed more, after which the step must be re-captured.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Optional
+
+import torch
+
+from . import _lib
+from . import rasterizer as _rz
+from .rasterizer import BatchRasterizationSettings, rasterize_gaussians_batch
+from .sharding import pack_gradients
+
+
+class GraphedRenderStep:
+    """color, radii, invdepth = rasterize_gaussians_batch(...) [; loss; backward; pack] as one CUDA graph.
+
+    means3D [V,P,3] | colors_precomp [V,P,32] | opacities [V,P,1] | scales [V,P,3] | rotations [V,P,4]
+    (or [P,...] shared by all views), `settings` as for rasterize_gaussians_batch -- all static.
+    Training mode: give `dL_dcolor` [V,32,H,W] (upstream gradient; loss = <color, dL_dcolor>) or
+    `loss_fn(color, invdepth) -> scalar`.  After `replay()`:
+        .color .radii .invdepth          forward outputs
+        .loss                            scalar tensor (training mode)
+        .grads                           dict xyz / scaling / rotation / opacity / features (per view)
+        .packed                          [P,43] sum over views, the all-reduce payload (sharding.py)
+    """
+
+    def __init__(self, means3D, colors_precomp, opacities, scales, rotations, settings: BatchRasterizationSettings,
+                 dL_dcolor: Optional[torch.Tensor] = None,
+                 loss_fn: Optional[Callable[[torch.Tensor, torch.Tensor], torch.Tensor]] = None,
+                 packed_out: Optional[torch.Tensor] = None, warmup: int = 2):
+        if not means3D.is_cuda:
+            raise RuntimeError("GraphedRenderStep needs CUDA tensors (there is no CPU path)")
+        self.inputs = dict(xyz=means3D, features=colors_precomp, opacity=opacities, scaling=scales, rotation=rotations)
+        self.settings = settings
+        self.dL_dcolor = dL_dcolor
+        self.loss_fn = loss_fn
+        self.training = dL_dcolor is not None or loss_fn is not None
+        self.device = means3D.device
+        self.packed = packed_out
+        self.color = self.radii = self.invdepth = self.loss = None
+        self.grads: Dict[str, torch.Tensor] = {}
+        self._flag_dev = None
+        self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.graph = torch.cuda.CUDAGraph()
+
+        # eager warm-up on a side stream: loads kernels, sets function attributes, learns the capacity
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._step()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+
+        prev = _lib.get_option("async_forward")
+        _lib.set_option("async_forward", 1)
+        try:
+            n0 = _lib.launch_count()
+            with torch.cuda.graph(self.graph):
+                self._step()
+                self._flag_host.copy_(self._flag_dev, non_blocking=True)
+            # kernels of libguava_rasterizer_b200.so that one replay launches
+            self.launches_per_replay = _lib.launch_count() - n0
+        finally:
+            _lib.set_option("async_forward", prev)
+
+    # one step, eager or under capture
+    def _step(self):
+        i = self.inputs
+        V = int(self.settings.viewmatrix.shape[0])
+        P = int(i["xyz"].shape[-2])
+        if self.training:
+            leaf = {k: v.detach().requires_grad_(True) for k, v in i.items()}
+        else:
+            leaf = i
+        m2 = torch.zeros(V, P, 3, device=self.device, requires_grad=self.training)
+        with torch.set_grad_enabled(self.training):
+            color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
+                                                           leaf["scaling"], leaf["rotation"], self.settings)
+        bufs = _rz._tls.last_buffers
+        L = _lib.buffer_layout(V, P, int(self.settings.image_width), int(self.settings.image_height), 0)
+        self._flag_dev = bufs[2][L.num_rendered + 4:L.num_rendered + 8].view(torch.int32)
+        self.color, self.radii, self.invdepth = color, radii, invd
+        if not self.training:
+            return
+        if self.loss_fn is not None:
+            loss = self.loss_fn(color, invd)
+            loss.backward()
+            self.loss = loss.detach()
+        else:
+            # loss = <color, dL_dcolor>: one dot-product kernel for the value, and the upstream
+            # gradient handed straight to the rasterizer's backward (no product tensor is materialised)
+            self.loss = torch.dot(color.detach().reshape(-1), self.dL_dcolor.reshape(-1))
+            color.backward(self.dL_dcolor)
+        self.grads = {k: v.grad for k, v in leaf.items()}
+        self.viewspace_grad = m2.grad
+        order = ("xyz", "scaling", "rotation", "opacity", "features")
+        self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
+
+    def replay(self):
+        self.graph.replay()
+        return self
+
+    def check(self):
+        """Synchronise and raise if any replay so far overflowed the captured binning capacity."""
+        torch.cuda.current_stream(self.device).synchronize()
+        if int(self._flag_host[0]) != 0:
+            raise RuntimeError("GraphedRenderStep: a replay needed more binning capacity than was captured; "
+                               "re-create the step (or raise option 'capacity_hint')")

@@ -381,6 +381,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                 int(bool(st.antialiasing)), _ptr(radii), int(bool(st.debug)), _stream_ptr(dev),
                 ctypes.byref(rendered))
             _tls.call = None
+            _tls.last_buffers = bufs.bufs      # (geometry, binning, image) of the most recent batched forward
             _check(rc)
         ctx.settings = st
         ctx.num_rendered = int(rendered.value)
