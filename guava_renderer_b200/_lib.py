@@ -21,6 +21,7 @@ EXPORTS = (
     "guava_rasterizer_mark_visible",
     "guava_rasterizer_forward_batch",
     "guava_rasterizer_backward_batch",
+    "guava_pack_view_gradients",
     "guava_buffer_layout",
     "guava_set_option",
     "guava_get_option",
@@ -93,6 +94,8 @@ def load() -> ctypes.CDLL:
         P, P, P, P, P, P, P, P, P,
         P, P, P, P, P, P, P, P, P,
         c_int, c_int, P]
+    lib.guava_pack_view_gradients.restype = c_int
+    lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]
     lib.guava_buffer_layout.restype = c_int
     lib.guava_buffer_layout.argtypes = [c_int, c_int, c_int, c_int, c_size_t, POINTER(Layout)]
     lib.guava_set_option.restype = c_int

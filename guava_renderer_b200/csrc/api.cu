@@ -204,6 +204,28 @@ __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uin
     }
 }
 
+// One thread per element of the packed [P,43] row: sum over the V views of the source column.
+__global__ void __launch_bounds__(256)
+pack_view_gradients_kernel(int V, int P, const float* __restrict__ g_xyz, const float* __restrict__ g_sc,
+                           const float* __restrict__ g_rot, const float* __restrict__ g_op,
+                           const float* __restrict__ g_feat, float* __restrict__ packed)
+{
+    const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (size_t)P * 43) return;
+    const size_t p = idx / 43;
+    const int j = (int)(idx - p * 43);
+    const float* src;
+    int w, c;
+    if (j < 3) { src = g_xyz; w = 3; c = j; }
+    else if (j < 6) { src = g_sc; w = 3; c = j - 3; }
+    else if (j < 10) { src = g_rot; w = 4; c = j - 6; }
+    else if (j < 11) { src = g_op; w = 1; c = 0; }
+    else { src = g_feat; w = 32; c = j - 11; }
+    float acc = 0.0f;
+    for (int v = 0; v < V; v++) acc += src[((size_t)v * P + p) * w + c];
+    packed[idx] = acc;
+}
+
 // ------------------------------------------------------------------- forward
 static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
                         guava_alloc_fn binningBuffer, void* binning_user,
@@ -527,6 +549,23 @@ int guava_rasterizer_backward_batch(
     return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, dL_dmean2D,
                          dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dscale,
                          dL_drot, debug, (cudaStream_t)stream);
+}
+
+int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const float* dL_dscales,
+                              const float* dL_drotations, const float* dL_dopacity, const float* dL_dcolors,
+                              float* packed, void* stream)
+{
+    if (V < 0 || P < 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if (P == 0) return GUAVA_OK;
+    if (!dL_dmeans3D || !dL_dscales || !dL_drotations || !dL_dopacity || !dL_dcolors || !packed)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    const size_t n = (size_t)P * 43;
+    pack_view_gradients_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        V, P, dL_dmeans3D, dL_dscales, dL_drotations, dL_dopacity, dL_dcolors, packed);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
+    return GUAVA_OK;
 }
 
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout* out)

@@ -28,6 +28,25 @@ def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
 
 def pack_gradients(grads: Sequence[torch.Tensor], out: torch.Tensor = None) -> torch.Tensor:
     """Sum each [V,P,w] (or [P,w]) gradient over its local views and concatenate into [P,43]."""
+    if grads[0].is_cuda:
+        # one kernel of libguava_rasterizer_b200.so instead of five reductions and a concatenation
+        import ctypes
+        from . import _lib
+        P = int(grads[0].shape[-2])
+        V = int(grads[0].shape[0]) if grads[0].dim() == 3 else 1
+        gs = []
+        for g, w in zip(grads, GRAD_WIDTHS):
+            if g.shape[-1] != w or g.numel() != V * P * w or g.dtype != torch.float32:
+                raise ValueError(f"expected float32 [{V},{P},{w}], got {tuple(g.shape)}")
+            gs.append(g if g.is_contiguous() else g.contiguous())
+        if out is None:
+            out = torch.empty(P, sum(GRAD_WIDTHS), dtype=torch.float32, device=grads[0].device)
+        stream = ctypes.c_void_p(torch.cuda.current_stream(grads[0].device).cuda_stream)
+        rc = _lib.load().guava_pack_view_gradients(V, P, *[g.data_ptr() for g in gs], out.data_ptr(), stream)
+        if rc != _lib.GUAVA_OK:
+            raise RuntimeError(_lib.last_error())
+        return out
+    # host tensors: the gloo-backed multi-process tests of the sharding logic (no compute path)
     cols = []
     for g, w in zip(grads, GRAD_WIDTHS):
         if g.dim() == 3:

@@ -204,6 +204,17 @@ int guava_rasterizer_backward_batch(
     int debug,
     void *stream);
 
+/* Training-side helper: sum the per-view per-Gaussian parameter gradients over the
+ * V local views and pack them as one [P,43] fp32 row per Gaussian = (means3D 3, scales 3, rotations 4,
+ * opacity 1, features 32) -- the payload of the one all-reduce that mirrors the reference trainer's DDP
+ * step (main/trainer.py:40-43,95).  Inputs are [V,P,w] contiguous. */
+int guava_pack_view_gradients(
+    int V, int P,
+    const float *dL_dmeans3D, const float *dL_dscales, const float *dL_drotations,
+    const float *dL_dopacity, const float *dL_dcolors,
+    float *packed,                      /* [P,43] */
+    void *stream);
+
 /* Byte offsets of the arrays inside the three opaque buffers, so that tests
  * and tools can inspect the intermediates the reference keeps in
  * GeometryState / BinningState / ImageState (rasterizer_impl.h:33-66). */

@@ -336,3 +336,38 @@ def test_cuda_path_against_committed_reference_golden(path):
                  rotation="dL_drotations", means2D="dL_dmeans2D")
     for k, n in names.items():
         assert util.rel_err(g[k], z[n].reshape(g[k].shape)) <= 1e-4, (k, util.rel_err(g[k], z[n].reshape(g[k].shape)))
+
+
+def test_pack_view_gradients_and_graphed_step():
+    """The fused [V,P,*] -> [P,43] packing kernel equals sum+cat, and a CUDA-graph replay of the whole
+    step equals the eager batched call (forward bitwise; gradients to atomic-order tolerance)."""
+    from guava_renderer_b200 import sharding
+    V, P, H, W = 2, 6000, 96, 128
+    views = [util.inputs_for(P, H, W, seed=900 + v, view=v, num_views=V, scale_mult=1.2) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    g = torch.Generator().manual_seed(2)
+    dL = torch.randn(V, 32, H, W, generator=g).to(DEV)
+    tanfov = torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=DEV), 1.0,
+                                        stack("viewmatrix"), stack("projmatrix"))
+    grb.set_option("capacity_hint", 0)
+    keys = ("xyz", "scaling", "rotation", "opacity", "features")
+    leaf = {k: stack(k).requires_grad_(True) for k in keys}
+    m2 = torch.zeros(V, P, 3, device=DEV, requires_grad=True)
+    color, radii, invd = grb.rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
+                                                       leaf["scaling"], leaf["rotation"], st)
+    color.backward(dL)
+    grads = [leaf[k].grad for k in keys]
+    packed = sharding.pack_gradients(grads)
+    ref = torch.cat([x.sum(0) for x in grads], dim=1)
+    assert packed.shape == (P, 43) and torch.allclose(packed, ref, rtol=1e-6, atol=1e-7 * float(ref.abs().max()))
+
+    step = grb.GraphedRenderStep(stack("xyz"), stack("features"), stack("opacity"), stack("scaling"),
+                                 stack("rotation"), st, dL_dcolor=dL)
+    for _ in range(2):
+        step.replay()
+    step.check()
+    assert step.launches_per_replay >= 9
+    assert torch.equal(step.color, color.detach()) and torch.equal(step.radii, radii)
+    assert util.rel_err(step.packed.cpu().numpy(), ref.cpu().numpy()) <= 1e-4
+    assert abs(float(step.loss) - float((color.detach() * dL).sum())) <= 1e-3 * abs(float(step.loss)) + 1e-3
