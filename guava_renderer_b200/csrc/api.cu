@@ -129,7 +129,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->ranges = o;       o = align_up(o + tiles * 8);
     L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE);
     L->tile_order = o;   o = align_up(o + tiles * 4);
-    L->num_rendered = o; o = align_up(o + 16);
+    L->num_rendered = o; o = align_up(o + 32);
     L->image_bytes = o;
     o = 0;
     L->point_list = o;    o = align_up(o + capacity * 4);

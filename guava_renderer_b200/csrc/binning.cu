@@ -30,20 +30,26 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
+    __shared__ uint32_t longest;
     const int tid = threadIdx.x;
     const int ipt = (n + 1023) / 1024;
     const int begin = min(n, tid * ipt), end = min(n, begin + ipt);
     uint32_t local = 0;
     if (tid < 256) bins[tid] = 0u;
+    if (tid == 0) longest = 0u;
     __syncthreads();
+    uint32_t my_max = 0;
     // Besides the scan: a longest-list-first order of the tiles (counting sort on 255 - len/8),
     // in which the persistent compositing kernels pull their work so that the long lists --
     // each a serial chain through one warp -- start first and the short ones fill the tail.
     for (int k = begin; k < end; k++) {
         const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
         local += c;
+        my_max = max(my_max, c);
         atomicAdd(&bins[255u - min(c >> 3, 255u)], 1u);
     }
+    my_max = __reduce_max_sync(0xffffffffu, my_max);
+    if ((tid & 31) == 0 && my_max != 0u) atomicMax(&longest, my_max);
     // block-wide exclusive scan of `local`
     uint32_t incl = local;
 #pragma unroll
@@ -83,6 +89,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         num_rendered[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
+        num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
         if (host_R != nullptr) { *host_R = total; __threadfence_system(); }
     }
 }
@@ -204,26 +211,94 @@ __device__ __forceinline__ uint32_t next_pow2(uint32_t n)
     return n <= 1 ? 1u : 1u << (32 - __clz(n - 1));
 }
 
-template <int THREADS>
-__global__ void __launch_bounds__(THREADS)
-tile_sort_smem_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
-                      const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                      uint64_t* __restrict__ keys_sorted, int tiles_per_view, uint32_t lo, uint32_t hi)
+// Buckets up to SORT_SMALL keys: bitonic network with the keys in REGISTERS.  256 threads hold
+// E consecutive keys each (N = 256*E slots, missing keys = +inf).  A compare-exchange at distance j
+// is register-to-register for j < E, a warp shuffle for j < 32*E, and goes through shared memory
+// (transposed layout, conflict-free) only for the few steps with j >= 32*E -- 6 of 55 steps at
+// N = 1024 -- where the first version synchronised the block after every step.
+template <int E>
+__device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__ src, uint32_t n, uint64_t* skeys,
+                                                    uint32_t* __restrict__ point_list, uint64_t* __restrict__ keys_sorted,
+                                                    uint64_t tile_hi, int tid)
 {
-    extern __shared__ uint64_t skeys[];
+    constexpr int N = 256 * E;
+    uint64_t key[E];
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const uint32_t i = (uint32_t)(tid * E + e);
+        key[e] = i < n ? src[i] : ~0ull;
+    }
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j >= 1; j >>= 1) {
+            if (j < E) {
+#pragma unroll
+                for (int e = 0; e < E; e++) {
+                    if ((e & j) == 0) {
+                        const bool asc = (((tid * E + e) & k) == 0);
+                        const uint64_t a = key[e], b = key[e | j];
+                        const bool sw = (a > b) == asc;
+                        key[e] = sw ? b : a;
+                        key[e | j] = sw ? a : b;
+                    }
+                }
+            } else if (j < 32 * E) {
+                const int tj = j / E;   // partner thread distance, within the warp
+                const bool lower = (tid & tj) == 0;
+#pragma unroll
+                for (int e = 0; e < E; e++) {
+                    const bool asc = (((tid * E + e) & k) == 0);
+                    const uint64_t other = __shfl_xor_sync(0xffffffffu, key[e], tj);
+                    const bool keep_min = lower == asc;
+                    const bool take_other = keep_min ? (other < key[e]) : (other > key[e]);
+                    key[e] = take_other ? other : key[e];
+                }
+            } else {
+                const int tj = j / E;
+                const bool lower = (tid & tj) == 0;
+                __syncthreads();
+#pragma unroll
+                for (int e = 0; e < E; e++) skeys[e * 256 + tid] = key[e];
+                __syncthreads();
+#pragma unroll
+                for (int e = 0; e < E; e++) {
+                    const bool asc = (((tid * E + e) & k) == 0);
+                    const uint64_t other = skeys[e * 256 + (tid ^ tj)];
+                    const bool keep_min = lower == asc;
+                    const bool take_other = keep_min ? (other < key[e]) : (other > key[e]);
+                    key[e] = take_other ? other : key[e];
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const uint32_t i = (uint32_t)(tid * E + e);
+        if (i < n) {
+            point_list[i] = (uint32_t)key[e];
+            if (keys_sorted != nullptr) keys_sorted[i] = tile_hi | (key[e] >> 32);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+tile_sort_small_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
+                       const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view)
+{
+    __shared__ uint64_t skeys[2048];
     if (num_rendered[1]) return;
     const uint2 r = ranges[blockIdx.x];
     const uint32_t n = r.y - r.x;
-    if (n <= lo || n > hi) return;
+    if (n == 0 || n > 2048) return;   // block-uniform; longer buckets: tile_sort_large_kernel
     const int tid = threadIdx.x;
-    for (uint32_t k = tid; k < n; k += THREADS) skeys[k] = keys[r.x + k];
-    bitonic_sort_ascending(skeys, n, next_pow2(n), tid, THREADS);
     const uint64_t tile_hi = (uint64_t)(blockIdx.x % tiles_per_view) << 32;
-    for (uint32_t k = tid; k < n; k += THREADS) {
-        const uint64_t key = skeys[k];
-        point_list[r.x + k] = (uint32_t)key;
-        if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
-    }
+    uint64_t* ks = keys_sorted != nullptr ? keys_sorted + r.x : nullptr;
+    if (n <= 256) tile_sort_registers<1>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else if (n <= 512) tile_sort_registers<2>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else if (n <= 1024) tile_sort_registers<4>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else tile_sort_registers<8>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
 }
 
 // Buckets longer than SORT_SMALL are rare (none at the GUAVA shapes): one persistent
@@ -239,7 +314,7 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                        uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
 {
     extern __shared__ uint64_t skeys[];
-    if (num_rendered[1]) return;
+    if (num_rendered[1] || num_rendered[4] <= SORT_SMALL) return;
     const int tid = threadIdx.x;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const uint2 r = ranges[tile];
@@ -278,8 +353,8 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         attr_set = true;
     }
-    tile_sort_smem_kernel<256><<<total_tiles, 256, SORT_SMALL * sizeof(uint64_t), s>>>(
-        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, 0u, SORT_SMALL);
+    tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.ranges, img.num_rendered, b.keys_unsorted, b.point_list,
+                                                       b.keys_sorted, in.tiles);
     const int big_grid = total_tiles < 148 ? total_tiles : 148;
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
         img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
