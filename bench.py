@@ -162,13 +162,28 @@ def run_own(args, rank, world, device):
     graphed = not args.eager
     if graphed:
         g_res = [grb.GraphedRenderStep(s["xyz"], s["feat"], s["op"], s["sc"], s["rot"], settings_of(s["vm"], s["pm"]),
-                                       dL_dcolor=dL, packed_out=gbuf) for s in sets_dev]
+                                       dL_dcolor=dL) for s in sets_dev]      # each step owns its [P,43] buffer
+
+    # N > 1: the all-reduce of step k is issued asynchronously (NCCL's stream) and joined one step later,
+    # so it runs under the binning kernels of step k+1 ("overlap with the next
+    # micro-batch's forward").  Everything is drained inside the timed region.
+    pending = []
+
+    def join(keep):
+        while len(pending) > keep:
+            h, fin = pending.pop(0)
+            if h is not None:
+                h.wait()
+            if fin is not None:
+                fin()
 
     def step_resident(i):
         if not graphed:
             return step_resident_eager(i)
-        g_res[i % len(g_res)].replay()
-        sharding.allreduce_gradients(gbuf)
+        g = g_res[i % len(g_res)]
+        g.replay()
+        pending.append((sharding.allreduce_gradients(g.packed, async_op=True), None))
+        join(1)
 
     # host-input arm for `e2e`: double-buffered H2D on a copy stream
     copy_stream = torch.cuda.Stream(device=device)
@@ -194,7 +209,7 @@ def run_own(args, rank, world, device):
                 b[k].copy_(sets_host[i % len(sets_host)][k])
         g_e2e = [grb.GraphedRenderStep(b["xyz"], b["feat"], b["op"], b["sc"], b["rot"],
                                        settings_of(b["cams"][:, :16].reshape(V, 4, 4), b["cams"][:, 16:].reshape(V, 4, 4)),
-                                       dL_dcolor=dL, packed_out=gbuf) for b in stage]
+                                       dL_dcolor=dL) for b in stage]
 
     def step_e2e(i, last):
         b = stage[i % 2]
@@ -202,10 +217,12 @@ def run_own(args, rank, world, device):
         if graphed:
             g = g_e2e[i % 2]
             g.replay()
-            sharding.allreduce_gradients(gbuf)
-            res = torch.stack([g.loss, gbuf.abs().sum()])
-            result_host.copy_(res, non_blocking=True)
-            return res
+
+            def finish(g=g):      # the step's result: loss + checksum of the reduced gradients -> host
+                result_host.copy_(torch.stack([g.loss, g.packed.abs().sum()]), non_blocking=True)
+            pending.append((sharding.allreduce_gradients(g.packed, async_op=True), finish))
+            join(1)
+            return None
         leaves = [b[k].detach().requires_grad_(True) for k in TENSOR_KEYS]
         st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, b["cams"][:, :16].reshape(V, 4, 4),
                                             b["cams"][:, 16:].reshape(V, 4, 4))
@@ -227,6 +244,7 @@ def run_own(args, rank, world, device):
     # ---- resident timing
     for i in range(args.warmup):
         step_resident(i)
+    join(0)
     barrier()
     cvd = os.environ.get("CUDA_VISIBLE_DEVICES", "")
     try:
@@ -240,6 +258,7 @@ def run_own(args, rank, world, device):
     e0.record()
     for i in range(args.steps):
         step_resident(args.warmup + i)
+    join(0)
     e1.record()
     barrier()
     launches = grb.launch_count() - n0
@@ -252,6 +271,7 @@ def run_own(args, rank, world, device):
     for i in range(args.warmup):
         prefetch(i + 1)
         step_e2e(i, False)
+    join(0)
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.perf_counter()
@@ -260,6 +280,7 @@ def run_own(args, rank, world, device):
         k = args.warmup + i
         prefetch(k + 1)                       # next step's H2D overlaps this step's kernels
         step_e2e(k, i == args.steps - 1)
+    join(0)
     e3.record()
     t_enq = (time.perf_counter() - t_wall0) * 1e3   # host time to enqueue the timed steps
     barrier()
