@@ -371,3 +371,41 @@ def test_pack_view_gradients_and_graphed_step():
     assert torch.equal(step.color, color.detach()) and torch.equal(step.radii, radii)
     assert util.rel_err(step.packed.cpu().numpy(), ref.cpu().numpy()) <= 1e-4
     assert abs(float(step.loss) - float((color.detach() * dL).sum())) <= 1e-3 * abs(float(step.loss)) + 1e-3
+
+
+BIG = [
+    dict(name="C4", P=300_000, H=1024, W=1024, seed=4000, scale_mult=1.0),    # BASELINE config 4 (one frame)
+    dict(name="C5", P=1_000_000, H=1080, W=1920, seed=5000, scale_mult=4.0),  # BASELINE config 5
+]
+
+
+@pytest.mark.parametrize("case", BIG, ids=lambda c: c["name"])
+def test_full_size_configs_vs_reference_build(ref, case):
+    """BASELINE configs 4 and 5 at full size against the unmodified reference build: the bit-exact set
+    (keys, lists, ranges, radii, n_contrib, final_T), the image tolerances and all gradients."""
+    cap = 1 << 24
+    grb.set_option("capacity_hint", cap)
+    P, H, W = case["P"], case["H"], case["W"]
+    inp = util.inputs_for(P, H, W, case["seed"], scale_mult=case["scale_mult"])
+    R, color, radii, geom, binning, img, invd = util.c_forward(ours, inp, DEV)
+    torch.cuda.synchronize()
+    o = util.decode_ours(geom, binning, img, 1, P, W, H, cap)
+    Rr, color_r, radii_r, geom_r, binning_r, img_r, invd_r = util.c_forward(ref, inp, DEV)
+    torch.cuda.synchronize()
+    r = util.decode_reference(geom_r, binning_r, img_r, P, H, W, Rr)
+    assert R == Rr and R > 2 * P
+    assert torch.equal(radii, radii_r)
+    assert np.array_equal(o["keys"], r["keys"])
+    assert np.array_equal(o["point_list"], r["point_list"])
+    assert np.array_equal(o["ranges"], r["ranges"])
+    assert np.array_equal(o["n_contrib"], r["n_contrib"])
+    assert np.array_equal(_bits(o["final_T"]), _bits(r["final_T"]))
+    assert float((color - color_r).abs().max()) <= 1e-5
+    assert float((invd - invd_r).abs().max()) <= 1e-5
+    del o, r, geom, binning, img, geom_r, binning_r, img_r
+    from guava_renderer_b200 import synthetic
+    dc, _ = synthetic.upstream_grads(H, W, 77)
+    _, go = _run_autograd(ours, inp, dc * 1e4, None)
+    _, gr = _run_autograd(ref, inp, dc * 1e4, None)
+    for k in gr:
+        assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
