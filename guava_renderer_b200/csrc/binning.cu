@@ -24,6 +24,33 @@
 namespace guava {
 
 // ------------------------------------------------------------ scan over tiles
+// One 1024-thread block.  Tiles are visited in chunks of 1024 (thread t <-> tile chunk*1024 + t), so the
+// loads of a chunk are independent and in flight together; a running carry links the chunks.
+__device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t x, uint32_t* warp_sums, int tid, uint32_t& total)
+{
+    uint32_t incl = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += t;
+    }
+    __syncthreads();   // warp_sums may still be read from the previous call
+    if ((tid & 31) == 31) warp_sums[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        uint32_t w = warp_sums[tid];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (tid >= o) w += t;
+        }
+        warp_sums[tid] = w;
+    }
+    __syncthreads();
+    total = warp_sums[31];
+    return incl - x + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
+}
+
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
@@ -32,65 +59,61 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     __shared__ uint32_t bins[256];
     __shared__ uint32_t longest;
     const int tid = threadIdx.x;
-    const int ipt = (n + 1023) / 1024;
-    const int begin = min(n, tid * ipt), end = min(n, begin + ipt);
-    uint32_t local = 0;
     if (tid < 256) bins[tid] = 0u;
     if (tid == 0) longest = 0u;
     __syncthreads();
+    // Pass 1: a longest-list-first order of the tiles (counting sort on 255 - len/8), in which the
+    // persistent compositing kernels pull their work so that the long lists -- each a serial chain
+    // through one warp -- start first and the short ones fill the tail; and the longest list.
     uint32_t my_max = 0;
-    // Besides the scan: a longest-list-first order of the tiles (counting sort on 255 - len/8),
-    // in which the persistent compositing kernels pull their work so that the long lists --
-    // each a serial chain through one warp -- start first and the short ones fill the tail.
-    for (int k = begin; k < end; k++) {
+    for (int k = tid; k < n; k += 1024) {
         const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
-        local += c;
         my_max = max(my_max, c);
-        atomicAdd(&bins[255u - min(c >> 3, 255u)], 1u);
+        // warp-aggregated: most tiles of a frame are empty and would all hit one counter
+        const uint32_t bin = 255u - min(c >> 3, 255u);
+        const uint32_t peers = __match_any_sync(__activemask(), bin);
+        if ((uint32_t)(tid & 31) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&bins[bin], (uint32_t)__popc(peers));
     }
     my_max = __reduce_max_sync(0xffffffffu, my_max);
     if ((tid & 31) == 0 && my_max != 0u) atomicMax(&longest, my_max);
-    // block-wide exclusive scan of `local`
-    uint32_t incl = local;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((tid & 31) >= o) incl += t;
-    }
-    if ((tid & 31) == 31) warp_sums[tid >> 5] = incl;
     __syncthreads();
-    if (tid < 32) {
-        uint32_t w = warp_sums[tid];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-            if (tid >= o) w += t;
+    {
+        uint32_t dummy;
+        const uint32_t mine = tid < 256 ? bins[tid] : 0u;
+        const uint32_t ex = block_exclusive_scan_1024(mine, warp_sums, tid, dummy);
+        if (tid < 256) bins[tid] = ex;
+    }
+    __syncthreads();
+    // Pass 2: exclusive scan of the counts = tile ranges (identifyTileRanges) and bucket cursors.
+    uint32_t carry = 0;
+    for (int base = 0; base < n; base += 1024) {
+        const int k = base + tid;
+        const uint32_t c = k < n ? cursor[(size_t)k * CURSOR_STRIDE] : 0u;
+        uint32_t chunk_total;
+        const uint32_t run = carry + block_exclusive_scan_1024(c, warp_sums, tid, chunk_total);
+        if (k < n) {
+            // untouched tiles keep (0,0), as the reference's memset leaves them
+            ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+            cursor[(size_t)k * CURSOR_STRIDE] = run;
         }
-        warp_sums[tid] = w;
+        {
+            const uint32_t bin = k < n ? 255u - min(c >> 3, 255u) : 256u;   // 256: no tile
+            const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+            const int leader = __ffs(peers) - 1;
+            uint32_t pos = 0;
+            if ((tid & 31) == leader && bin < 256u) pos = atomicAdd(&bins[bin], (uint32_t)__popc(peers));
+            pos = __shfl_sync(0xffffffffu, pos, leader);
+            if (bin < 256u) tile_order[pos + __popc(peers & ((1u << (tid & 31)) - 1u))] = (uint32_t)k;
+        }
+        carry += chunk_total;
     }
-    __syncthreads();
-    if (tid == 0) {   // 256 bins: serial exclusive scan is cheap enough
-        uint32_t acc = 0;
-        for (int b = 0; b < 256; b++) { const uint32_t c = bins[b]; bins[b] = acc; acc += c; }
-    }
-    __syncthreads();
-    uint32_t run = incl - local + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
-    for (int k = begin; k < end; k++) {
-        const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
-        tile_order[atomicAdd(&bins[255u - min(c >> 3, 255u)], 1u)] = (uint32_t)k;
-        // untouched tiles keep (0,0), as the reference's memset leaves them
-        ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-        cursor[(size_t)k * CURSOR_STRIDE] = run;
-        run += c;
-    }
-    if (tid == 1023) {
-        const uint32_t total = warp_sums[31];
-        num_rendered[0] = total;
-        num_rendered[1] = ((unsigned long long)total > capacity) ? 1u : 0u;
+    if (tid == 0) {
+        num_rendered[0] = carry;
+        num_rendered[1] = ((unsigned long long)carry > capacity) ? 1u : 0u;
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
-        if (host_R != nullptr) { *host_R = total; __threadfence_system(); }
+        if (host_R != nullptr) { *host_R = carry; __threadfence_system(); }
     }
 }
 
