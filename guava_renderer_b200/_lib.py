@@ -43,7 +43,8 @@ class Layout(Structure):
     _fields_ = [(n, c_size_t) for n in (
         "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched", "grad_geo",
         "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "tile_order", "num_rendered",
-        "binning_bytes", "point_list", "keys_unsorted", "keys_sorted")]
+        "binning_bytes", "point_list", "keys_unsorted", "keys_sorted",
+        "point_offsets", "os_vals_alt", "os_scratch")]
 
 
 class GuavaLibraryError(RuntimeError):

@@ -33,6 +33,7 @@ static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_async_forward{0};
 static std::atomic<long long> g_opt_scalar_red{0};
+static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
 static int fail(int code, const std::string& msg)
 {
@@ -110,7 +111,7 @@ struct StageTimer {
     }
 };
 
-static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emit_keys, guava_layout* L)
+static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emit_keys, guava_layout* L, int sort_mode = 0)
 {
     const size_t n = (size_t)V * P;
     const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
@@ -122,6 +123,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->rects = o;         o = align_up(o + n * 8);
     L->tiles_touched = o; o = align_up(o + n * 4);
     L->grad_geo = o;      o = align_up(o + n * 32);
+    L->point_offsets = o; o = align_up(o + (sort_mode == 1 ? n * 4 : 0));
     L->geom_bytes = o;
     o = 0;
     L->final_T = o;      o = align_up(o + npix * 4);
@@ -134,7 +136,9 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     o = 0;
     L->point_list = o;    o = align_up(o + capacity * 4);
     L->keys_unsorted = o; o = align_up(o + capacity * 8);
-    L->keys_sorted = o;   o = align_up(o + (emit_keys ? capacity * 8 : 0));
+    L->keys_sorted = o;   o = align_up(o + ((emit_keys || sort_mode == 1) ? capacity * 8 : 0));
+    L->os_vals_alt = o;   o = align_up(o + (sort_mode == 1 ? capacity * 4 : 0));
+    L->os_scratch = o;    o = align_up(o + (sort_mode == 1 ? onesweep_scratch_bytes(n, capacity, (int)tiles) : 0));
     L->binning_bytes = o;
 }
 
@@ -153,7 +157,7 @@ static cudaError_t ensure_slots()
 {
     std::call_once(g_slots_once, [] {
         void* h = nullptr;
-        g_slots_err = cudaHostAlloc(&h, HostSlots::N * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
+        g_slots_err = cudaHostAlloc(&h, HostSlots::N * 2 * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
         if (g_slots_err != cudaSuccess) return;
         g_slots.host = (uint32_t*)h;
         void* d = nullptr;
@@ -164,7 +168,7 @@ static cudaError_t ensure_slots()
 }
 
 // --------------------------------------------------------- capacity estimates
-struct CapEntry { size_t n; int W, H; size_t cap; };
+struct CapEntry { size_t n; int W, H; size_t cap; uint32_t longest; };
 static CapEntry g_caps[16];
 static unsigned g_caps_next = 0;
 static std::mutex g_caps_mu;
@@ -180,7 +184,15 @@ static size_t capacity_estimate(size_t n, int W, int H)
     if (c < (1u << 20)) c = 1u << 20;
     return c;
 }
-static void capacity_record(size_t n, int W, int H, size_t R)
+// longest tile list the last call of this shape produced (0 = shape not seen yet)
+static uint32_t longest_estimate(size_t n, int W, int H)
+{
+    std::lock_guard<std::mutex> lk(g_caps_mu);
+    for (auto& e : g_caps)
+        if (e.n == n && e.W == W && e.H == H && e.cap) return e.longest;
+    return 0;
+}
+static void capacity_record(size_t n, int W, int H, size_t R, uint32_t longest)
 {
     std::lock_guard<std::mutex> lk(g_caps_mu);
     const size_t want = R + R / 4 + 4096;
@@ -188,9 +200,10 @@ static void capacity_record(size_t n, int W, int H, size_t R)
         if (e.n == n && e.W == W && e.H == H && e.cap) {
             // grow immediately, shrink slowly
             e.cap = want > e.cap ? want : (e.cap * 15 + want) / 16;
+            e.longest = longest;
             return;
         }
-    g_caps[g_caps_next++ % 16] = CapEntry{n, W, H, want};
+    g_caps[g_caps_next++ % 16] = CapEntry{n, W, H, want, longest};
 }
 
 __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
@@ -255,11 +268,16 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     const bool emit_keys = g_opt_emit_sorted_keys.load() != 0;
     const bool exact = g_opt_exact_binning.load() != 0;
     const bool async_fwd = g_opt_async_forward.load() != 0 && !exact;
+    // "sort_mode": 0 = tile buckets, 1 = global onesweep sort, -1 (default) = by the longest tile list the
+    // previous call of this shape produced: lists beyond the register-resident bucket sort (2048) are where
+    // the onesweep passes win (measured: profiles/r01_v9_sort_modes.jsonl).  Results are identical.
+    int sort_mode = (int)g_opt_sort_mode.load();
+    if (sort_mode < 0) sort_mode = longest_estimate((size_t)in.V * in.P, in.W, in.H) > 2048u ? 1 : 0;
     GUAVA_CUDA(ensure_slots());
 
     guava_layout L;
     size_t cap = capacity_estimate(n, in.W, in.H);
-    compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+    compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
     char* geom = geometryBuffer(geometry_user, L.geom_bytes);
     char* img = imageBuffer(image_user, L.image_bytes);
     if (!geom || !img) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
@@ -281,7 +299,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
 
     const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
-    volatile uint32_t* hslot = g_slots.host + slot;
+    volatile uint32_t* hslot = g_slots.host + 2 * slot;   // [0] = R, [1] = longest tile list
     *hslot = 0xFFFFFFFFu;
 
     const int total_tiles = in.V * in.tiles;
@@ -292,7 +310,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     timer.end();
     GUAVA_STAGE("preprocess", debug);
     timer.begin(1);
-    launch_tile_scan(total_tiles, im, g_slots.dev + slot, exact ? (size_t)-1 : cap, stream);
+    launch_tile_scan(total_tiles, im, g_slots.dev + 2 * slot, exact ? (size_t)-1 : cap, stream);
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 
@@ -320,7 +338,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         if (rc) return rc;
         have_R = true;
         cap = R;
-        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
     }
     char* bin = binningBuffer(binning_user, L.binning_bytes ? L.binning_bytes : 256);
     if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
@@ -331,6 +349,15 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         b.keys_unsorted = (uint64_t*)(bin + L.keys_unsorted);
         b.keys_sorted = emit_keys ? (uint64_t*)(bin + L.keys_sorted) : nullptr;
         b.capacity = cap;
+        if (sort_mode == 1) {
+            if (cap >= (1u << 30)) return fail(GUAVA_ERR_INVALID_ARGUMENT, "sort_mode 1 supports < 2^30 instances");
+            timer.begin(3);
+            launch_onesweep_binning(in, g, im, (uint32_t*)(geom + L.point_offsets), (uint64_t*)(bin + L.keys_sorted),
+                                    b.point_list, b.keys_unsorted, (uint32_t*)(bin + L.os_vals_alt),
+                                    (uint32_t*)(bin + L.os_scratch), cap, stream);
+            timer.end();
+            GUAVA_STAGE("onesweep", debug);
+        } else {
         timer.begin(2);
         launch_scatter(in, g, im, b, radii, stream);
         timer.end();
@@ -339,6 +366,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         launch_tile_sort(in, im, b, nullptr, stream);
         timer.end();
         GUAVA_STAGE("tile_sort", debug);
+        }
         timer.begin(4);
         launch_render_forward(in, g, im, b, out_color, out_invdepth, stream);
         timer.end();
@@ -352,14 +380,14 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         if ((size_t)R <= cap) break;
         // estimate too small: every kernel after the scan skipped itself
         cap = (size_t)R;
-        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L);
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
         bin = binningBuffer(binning_user, L.binning_bytes);
         if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
         reset_cursor_kernel<<<(total_tiles + 255) / 256, 256, 0, stream>>>(total_tiles, im.ranges, im.tile_cursor,
                                                                            im.num_rendered, (unsigned long long)cap);
         count_launch();
     }
-    if (!async_fwd) capacity_record(n, in.W, in.H, R);
+    if (!async_fwd) capacity_record(n, in.W, in.H, R, hslot[1]);
     if (num_rendered) *num_rendered = async_fwd ? -1 : (int)R;
     return GUAVA_OK;
 }
@@ -571,7 +599,7 @@ int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const floa
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout* out)
 {
     if (!out || V < 0 || P < 0 || width <= 0 || height <= 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "bad layout query");
-    compute_layout(V, P, width, height, capacity, g_opt_emit_sorted_keys.load() != 0, out);
+    compute_layout(V, P, width, height, capacity, g_opt_emit_sorted_keys.load() != 0, out, (int)g_opt_sort_mode.load());
     return GUAVA_OK;
 }
 
@@ -584,6 +612,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "async_forward")) return &g_opt_async_forward;
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
     if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
+    if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;
     return nullptr;
 }
 

@@ -113,7 +113,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
-        if (host_R != nullptr) { *host_R = carry; __threadfence_system(); }
+        if (host_R != nullptr) { host_R[1] = longest; __threadfence_system(); host_R[0] = carry; __threadfence_system(); }
     }
 }
 

@@ -242,7 +242,13 @@ typedef struct guava_layout {
     size_t point_list;     /* uint32 per instance: Gaussian index within its view, sorted */
     size_t keys_unsorted;  /* uint64 per instance: depth_bits<<32 | index (tile-bucketed) */
     size_t keys_sorted;    /* uint64 per instance: tile<<32 | depth_bits; only written when
-                              guava_set_option("emit_sorted_keys", 1) */
+                              guava_set_option("emit_sorted_keys", 1) or "sort_mode" 1 (there the high
+                              word is view*tiles + tile) */
+    /* only with guava_set_option("sort_mode", 1) (global onesweep sort), else zero-sized */
+    size_t point_offsets;  /* geometry buffer: uint32 per g, inclusive sums of tiles_touched
+                              (GeometryState::point_offsets, rasterizer_impl.cu:280) */
+    size_t os_vals_alt;    /* binning buffer: uint32 per instance, alternate value buffer of the sort */
+    size_t os_scratch;     /* binning buffer: tickets, scan state, digit histograms, look-back state */
 } guava_layout;
 
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout *out);
@@ -255,7 +261,13 @@ int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, gu
  * set to -1 and a capacity overflow is only visible in the image buffer's
  * num_rendered[1] flag -- for CUDA-graph capture),
  * "profile_stages" (0/1, default 0: time every kernel with CUDA events, see
- * guava_stage_time). Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
+ * guava_stage_time),
+ * "sort_mode" (0: per-tile buckets sorted in shared memory; 1: the reference's chain rebuilt --
+ * chained scan + duplicateWithKeys + onesweep LSD radix sort of the 64-bit tile|depth keys +
+ * identifyTileRanges, rasterizer_impl.cu:280-320; identical keys, values and ranges; -1 (default): 1 when
+ * the previous call of the same shape produced a tile list longer than 2048 instances, else 0;
+ * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes).
+ * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);
 

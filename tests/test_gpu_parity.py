@@ -92,12 +92,24 @@ def test_forward_vs_cpu_oracle(case, antialiasing):
     assert np.mean(np.abs(o["invdepth"] - f["invdepth"]) > 1e-5) < 2e-3
 
 
+@pytest.fixture(params=[0, 1], ids=["tile_buckets", "onesweep"])
+def sort_mode(request):
+    """Both binning paths must give the reference's keys, values and ranges: 0 = per-tile buckets sorted
+    in shared memory (binning.cu), 1 = scan + duplicateWithKeys + onesweep radix sort + identifyTileRanges
+    (onesweep.cu; the reference's own chain, rasterizer_impl.cu:280-320)."""
+    grb.set_option("sort_mode", request.param)
+    yield request.param
+    grb.set_option("sort_mode", -1)   # default: chosen per shape from the previous call's longest tile list
+
+
 @pytest.mark.parametrize("case", CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
 @pytest.mark.parametrize("antialiasing", [False, True])
-def test_forward_vs_reference_build(ref, case, antialiasing):
+def test_forward_vs_reference_build(ref, case, antialiasing, sort_mode):
     inp = util.inputs_for(**case)
     inp["bg"] = torch.linspace(-1, 1, 32)
     o = _ours_forward(inp, antialiasing)
+    if sort_mode == 1:   # GeometryState::point_offsets = InclusiveSum(tiles_touched), rasterizer_impl.cu:280
+        assert np.array_equal(o["point_offsets"], np.cumsum(o["tiles_touched"], dtype=np.uint64).astype(np.uint32))
     R, color, radii, geom, binning, img, invd = util.c_forward(ref, inp, DEV, antialiasing)
     torch.cuda.synchronize()
     r = util.decode_reference(geom, binning, img, inp["xyz"].shape[0], inp["H"], inp["W"], R)
@@ -172,7 +184,7 @@ def test_backward_vs_cpu_oracle(antialiasing):
         assert e <= 1e-3, (k, e)
 
 
-def test_batched_entry_equals_per_view_loop():
+def test_batched_entry_equals_per_view_loop(sort_mode):
     """One launch chain over V views == V single-view calls (bitwise forward, tolerance backward)."""
     V, P, H, W = 3, 5000, 160, 176
     views = [util.inputs_for(P, H, W, seed=700 + v, view=v, num_views=V, scale_mult=1.3) for v in range(V)]
@@ -203,7 +215,7 @@ def test_batched_entry_equals_per_view_loop():
         assert util.rel_err(out["viewspace_points"].grad[v].cpu().numpy(), gv["means2D"]) <= 1e-4
 
 
-def test_capacity_overflow_is_recovered():
+def test_capacity_overflow_is_recovered(sort_mode):
     inp = util.inputs_for(**CASES[1])
     a = _ours_forward(inp)
     grb.set_option("capacity_hint", 512)          # far below num_rendered: forces the re-run path
@@ -299,6 +311,16 @@ def test_full_size_properties():
     assert lens.sum() == o["R"] == int(o["tiles_touched"].sum())         # a checksum of checksums
     same = keys[1:] == keys[:-1]
     assert np.all(o["point_list"][1:][same] > o["point_list"][:-1][same])  # ties keep index order
+    # the global onesweep sort gives the same keys, values, ranges and image at full size
+    grb.set_option("sort_mode", 0)
+    o = _ours_forward(inp)
+    grb.set_option("sort_mode", 1)
+    try:
+        o1 = _ours_forward(inp)
+    finally:
+        grb.set_option("sort_mode", -1)
+    for k in ("keys", "point_list", "ranges", "n_contrib", "color"):
+        assert np.array_equal(o1[k], o[k]), k
 
 
 import glob as _glob
@@ -308,7 +330,7 @@ _GOLDENS = sorted(_glob.glob(_os.path.join(_os.path.dirname(__file__), "golden",
 
 
 @pytest.mark.parametrize("path", _GOLDENS, ids=[_os.path.basename(p) for p in _GOLDENS])
-def test_cuda_path_against_committed_reference_golden(path):
+def test_cuda_path_against_committed_reference_golden(path, sort_mode):
     """The committed outputs of the unmodified reference build (tests/golden/make_golden.py): the same
     gates as test_forward_vs_reference_build / test_backward_vs_reference_build, without needing oracle/_ref."""
     from guava_renderer_b200 import synthetic
@@ -380,7 +402,7 @@ BIG = [
 
 
 @pytest.mark.parametrize("case", BIG, ids=lambda c: c["name"])
-def test_full_size_configs_vs_reference_build(ref, case):
+def test_full_size_configs_vs_reference_build(ref, case, sort_mode):
     """BASELINE configs 4 and 5 at full size against the unmodified reference build: the bit-exact set
     (keys, lists, ranges, radii, n_contrib, final_T), the image tolerances and all gradients."""
     cap = 1 << 24

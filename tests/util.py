@@ -77,12 +77,15 @@ def decode_ours(geom, binning, img, V, P, W, H, capacity=None):
     )
     R = out["num_rendered"]
     out["point_list"] = b[0:R * 4].view(np.uint32).copy()
-    if capacity is not None and grb.get_option("emit_sorted_keys"):
+    if grb.get_option("sort_mode") == 1:
+        out["point_offsets"] = g[L.point_offsets:L.point_offsets + n * 4].view(np.uint32).copy()
+    if capacity is not None and (grb.get_option("emit_sorted_keys") or grb.get_option("sort_mode") == 1):
         cap = max(int(capacity), R) if R > int(capacity) else int(capacity)
         if R > int(capacity):
             cap = R
         Lc = grb.buffer_layout(V, P, W, H, cap)
-        if Lc.binning_bytes == b.size:
+        # same offset in both sort modes (the onesweep scratch lies behind it)
+        if Lc.keys_sorted + R * 8 <= b.size and (Lc.binning_bytes == b.size or grb.get_option("sort_mode") != 0):
             out["keys"] = b[Lc.keys_sorted:Lc.keys_sorted + R * 8].view(np.uint64).copy()
     return out
 
