@@ -104,13 +104,29 @@ def build_inputs(config_id, P, H, W, views, num_views, n_sets, pin):
         d = synthetic.make_views(config_id * 10 + s, P, H, W, views, num_views)
         cams = torch.cat([d["viewmatrix"].reshape(len(views), 16), d["projmatrix"].reshape(len(views), 16)], 1).contiguous()
         e = dict(xyz=d["xyz"], sc=d["scaling"], rot=d["rotation"], op=d["opacity"], feat=d["features_color"], cams=cams)
-        if pin:
-            e = {k: v.pin_memory() for k, v in e.items()}
+        if pin:   # one pinned block per set (feat first: its rows must stay 16-byte aligned) -> one H2D copy per step
+            packed = torch.empty(sum(v.numel() for v in e.values())).pin_memory()
+            e = carve(packed, len(views), P, fill=e)
+            e["packed"] = packed
         e.update(tanfovx=d["tanfovx"], tanfovy=d["tanfovy"], campos=d["campos"])
         sets.append(e)
     return sets
 
 
+def carve(packed, V, P, fill=None):
+    """Views [V,P,w] (and cams [V,32]) into one flat float buffer, in PACK_ORDER."""
+    out, o = {}, 0
+    for k in PACK_ORDER:
+        shape = (V, 32) if k == "cams" else (V, P, WIDTHS[k])
+        n = shape[0] * shape[1] * (shape[2] if len(shape) == 3 else 1)
+        out[k] = packed[o:o + n].view(shape)
+        if fill is not None:
+            out[k].copy_(fill[k].reshape(shape))
+        o += n
+    return out
+
+
+PACK_ORDER = ("feat", "xyz", "sc", "rot", "op", "cams")
 TENSOR_KEYS = ("xyz", "sc", "rot", "op", "feat")      # [V,P,3|3|4|1|32] = 43 floats per Gaussian
 WIDTHS = dict(xyz=3, sc=3, rot=4, op=1, feat=32)
 
@@ -187,8 +203,10 @@ def run_own(args, rank, world, device):
 
     # host-input arm for `e2e`: double-buffered H2D on a copy stream
     copy_stream = torch.cuda.Stream(device=device)
-    stage = [dict({k: torch.empty(V, P, WIDTHS[k], device=device) for k in TENSOR_KEYS},
-                  cams=torch.empty(V, 32, device=device), ev=torch.cuda.Event()) for _ in range(2)]
+    stage = []
+    for _ in range(2):
+        packed = torch.empty(V * P * 43 + V * 32, device=device)
+        stage.append(dict(carve(packed, V, P), packed=packed, ev=torch.cuda.Event()))
     result_host = torch.empty(2, dtype=torch.float32).pin_memory()
     h2d_bytes = V * P * 43 * 4 + V * 32 * 4
     d2h_bytes = 8
@@ -199,14 +217,12 @@ def run_own(args, rank, world, device):
         compute = torch.cuda.current_stream(device)
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_stream(compute)   # buffer i%2 is free once step i-2 (already enqueued) is done
-            for k in TENSOR_KEYS + ("cams",):
-                b[k].copy_(s[k], non_blocking=True)
+            b["packed"].copy_(s["packed"], non_blocking=True)   # the step's [V,P,43] Gaussians + cameras
             b["ev"].record(copy_stream)
 
     if graphed:
         for i, b in enumerate(stage):      # valid contents while the steps are captured
-            for k in TENSOR_KEYS + ("cams",):
-                b[k].copy_(sets_host[i % len(sets_host)][k])
+            b["packed"].copy_(sets_host[i % len(sets_host)]["packed"])
         g_e2e = [grb.GraphedRenderStep(b["xyz"], b["feat"], b["op"], b["sc"], b["rot"],
                                        settings_of(b["cams"][:, :16].reshape(V, 4, 4), b["cams"][:, 16:].reshape(V, 4, 4)),
                                        dL_dcolor=dL) for b in stage]
@@ -507,6 +523,7 @@ def main():
     ap.add_argument("--views-per-gpu", type=int, default=VIEWS_PER_GPU)
     ap.add_argument("--view-sets", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to its GPU's NUMA node")
     ap.add_argument("--eager", action="store_true", help="enqueue every step op by op instead of replaying CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -525,6 +542,8 @@ def main():
         raise SystemExit("bench.py (own arm) needs a CUDA device: the product has no CPU path")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    from guava_renderer_b200 import sharding
+    numa_cpus = sharding.bind_host_to_gpu(local_rank) if world > 1 and not args.no_numa_bind else None
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -540,6 +559,7 @@ def main():
             "config": {"workload": workload_name(args), "P": args.P, "H": args.H, "W": args.W,
                        "views_per_gpu": args.views_per_gpu, "global_views_per_step": args.views_per_gpu * world,
                        "parallelism": f"view-sharded x{world}",
+                       "host_numa_bind": (f"rank 0 pinned to {len(numa_cpus)} CPUs local to its GPU" if numa_cpus else "none"),
                        "step_call": "eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)",
                        "l2": f"inputs rotate over {args.view_sets} distinct view sets; per-step working set ~230 MB > 126 MB L2"},
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
@@ -549,7 +569,7 @@ def main():
             "clocks": r["clocks"],
             "roofline": r["roofline"],
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:   # rank 0 at N = 1 only
             line["cpu_baseline"] = cpu_baseline(args.P, args.H, args.W, max_views=2)
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -26,6 +26,39 @@ def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
     return list(range(start, start + base + (1 if rank < rem else 0)))
 
 
+def _parse_cpulist(text: str) -> List[int]:
+    cpus: List[int] = []
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.extend(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_host_to_gpu(device_index: int, sysfs: str = "/sys/bus/pci/devices"):
+    """Pin this process (one per GPU) to the CPUs of the NUMA node its GPU hangs off, so that the pinned
+    staging buffers allocated afterwards are first-touched on that node and the per-step host->device copies
+    of the ranks do not all cross one socket's memory controller.  Returns the CPU list applied, or None when
+    the topology cannot be read (containers without sysfs, a single node): nothing is changed then."""
+    import os
+    try:
+        bus = torch.cuda.get_device_properties(device_index).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(device_index), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(device_index), "pci_device_id", 0)
+        path = os.path.join(sysfs, f"{dom:04x}:{bus:02x}:{dev:02x}.0", "local_cpulist")
+        with open(path) as f:
+            cpus = _parse_cpulist(f.read())
+        allowed = os.sched_getaffinity(0)
+        cpus = sorted(set(cpus) & allowed)
+        if not cpus or len(cpus) == len(allowed):
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        return None
+
+
 def pack_gradients(grads: Sequence[torch.Tensor], out: torch.Tensor = None) -> torch.Tensor:
     """Sum each [V,P,w] (or [P,w]) gradient over its local views and concatenate into [P,43]."""
     if grads[0].is_cuda:
