@@ -7,6 +7,7 @@ Only what the hot path needs lives here:
   _lib.py        ctypes binding of the C ABI (no fallback: raises if the .so is missing)
   rasterizer.py  host-side mirror of the reference's `_C` module and Python surface
   renderer.py    batched replacement for GaussianRenderer's per-view loop
+  deform.py      fused deformation -> rasterizer inputs (the step before the path)
   graphed.py     CUDA-graph capture of a fixed-shape render (+ loss + backward) step
   synthetic.py   seeded synthetic clouds / cameras of the benchmark shapes
 """
@@ -24,6 +25,7 @@ from .rasterizer import (  # noqa: F401
 )
 from .renderer import render_views  # noqa: F401
 from .graphed import GraphedRenderStep  # noqa: F401
+from .deform import deform_gaussians  # noqa: F401
 
 # importing the package must fail loudly when the CUDA library is absent
 from . import _lib as _lib_mod

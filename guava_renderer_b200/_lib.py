@@ -22,6 +22,8 @@ EXPORTS = (
     "guava_rasterizer_forward_batch",
     "guava_rasterizer_backward_batch",
     "guava_pack_view_gradients",
+    "guava_deform_gaussians_forward",
+    "guava_deform_gaussians_backward",
     "guava_buffer_layout",
     "guava_set_option",
     "guava_get_option",
@@ -97,6 +99,10 @@ def load() -> ctypes.CDLL:
         c_int, c_int, P]
     lib.guava_pack_view_gradients.restype = c_int
     lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]
+    lib.guava_deform_gaussians_forward.restype = c_int
+    lib.guava_deform_gaussians_forward.argtypes = [c_int] * 4 + [P] * 21
+    lib.guava_deform_gaussians_backward.restype = c_int
+    lib.guava_deform_gaussians_backward.argtypes = [c_int] * 4 + [P] * 12
     lib.guava_buffer_layout.restype = c_int
     lib.guava_buffer_layout.argtypes = [c_int, c_int, c_int, c_int, c_size_t, POINTER(Layout)]
     lib.guava_set_option.restype = c_int

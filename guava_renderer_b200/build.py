@@ -20,7 +20,7 @@ OBJDIR = os.path.join(LIBDIR, "obj")
 SO = os.path.join(LIBDIR, "libguava_rasterizer_b200.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "onesweep.cu", "render_forward.cu", "render_backward.cu"]
+SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "onesweep.cu", "render_forward.cu", "render_backward.cu", "deform.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",

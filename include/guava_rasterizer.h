@@ -280,6 +280,34 @@ unsigned long long guava_launch_count(void);
 int guava_stage_time(const char *stage, double *total_ms, unsigned long long *calls);
 void guava_stage_time_reset(void);
 
+/* ---- the step immediately before the rasterizer ------------------------
+ * Fused deformation of GUAVA's two Gaussian groups into the concatenated [B, Nv+N, *] tensors the
+ * rasterizer reads.  Replaces models/UbodyAvatar/ubody_gaussian.py:245-289 (Ubody_Gaussian.forward:
+ * compute_face_orientation, utils/graphics_utils.py:61-80; roma 1.5.3 rotmat_to_unitquat / quat_product)
+ * and its autograd backward for the per-Gaussian attributes.  All pointers are device pointers, fp32
+ * unless noted; quaternions are wxyz; `face_frames` is a [B,F,16] float scratch written by forward and
+ * read by backward (R row-major, scale, quat wxyz, 2 pad); `out_features` may be NULL (no concatenation).
+ * Returns GUAVA_OK / GUAVA_ERR_INVALID_ARGUMENT / GUAVA_ERR_CUDA. */
+int guava_deform_gaussians_forward(
+    int B, int Nv, int N, int F,
+    const float *vertices /* [B,Nv,3] deformed mesh */, const float *ver_transform /* [B,Nv,4,4] */,
+    const int *faces /* [F,3] int32 */, const int *uv_binding_face /* [N] int32 */,
+    const float *uv_face_bary /* [N,3] */,
+    const float *smplx_rotation /* [B,Nv,4] */, const float *smplx_scaling /* [B,Nv,3] */,
+    const float *smplx_opacity /* [B,Nv,1] */, const float *smplx_features /* [B,Nv,32] */,
+    const float *uv_local_xyz /* [B,N,3] */, const float *uv_rotation /* [B,N,4] */,
+    const float *uv_scaling /* [B,N,3] */, const float *uv_opacity /* [B,N,1] */,
+    const float *uv_features /* [B,N,32] */,
+    float *face_frames, float *out_xyz, float *out_rotation, float *out_scaling, float *out_opacity,
+    float *out_features, void *stream);
+int guava_deform_gaussians_backward(
+    int B, int Nv, int N, int F, const float *ver_transform, const int *uv_binding_face,
+    const float *smplx_rotation, const float *face_frames,
+    const float *dL_dxyz /* [B,Nv+N,3] */, const float *dL_drotation /* [B,Nv+N,4] */,
+    const float *dL_dscaling /* [B,Nv+N,3] */,
+    float *dL_dsmplx_rotation /* [B,Nv,4] */, float *dL_duv_local_xyz /* [B,N,3] */,
+    float *dL_duv_rotation /* [B,N,4] */, float *dL_duv_scaling /* [B,N,3] */, void *stream);
+
 const char *guava_last_error(void);
 const char *guava_version(void);
 

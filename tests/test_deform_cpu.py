@@ -1,0 +1,51 @@
+"""CPU checks of the deformation oracle (oracle/deform_oracle.py): the restated roma helpers satisfy the
+identities their published definitions imply, and the restatement of ubody_gaussian.py:245-289 is
+self-consistent.  (roma itself is not installed: see the oracle header.)"""
+import numpy as np
+import torch
+
+from oracle import deform_oracle as do
+
+
+def test_rotmat_to_unitquat_roundtrip_all_branches():
+    g = torch.Generator().manual_seed(0)
+    q = torch.nn.functional.normalize(torch.randn(4000, 4, generator=g, dtype=torch.float64), dim=-1)
+    # force every decision branch: large x, y, z or w component
+    for k in range(4):
+        q[k * 500:(k + 1) * 500, k] += 3.0
+    q = torch.nn.functional.normalize(q, dim=-1)
+    R = do.unitquat_to_rotmat(q)
+    q2 = do.rotmat_to_unitquat(R)
+    assert torch.allclose(q2.norm(dim=-1), torch.ones(4000, dtype=torch.float64))
+    sign = torch.sign((q * q2).sum(-1, keepdim=True))
+    assert torch.allclose(q2 * sign, q, atol=1e-12)
+    assert torch.allclose(do.unitquat_to_rotmat(q2), R, atol=1e-12)
+
+
+def test_quat_product_is_rotation_composition():
+    g = torch.Generator().manual_seed(1)
+    p = torch.nn.functional.normalize(torch.randn(100, 4, generator=g, dtype=torch.float64), dim=-1)
+    q = torch.nn.functional.normalize(torch.randn(100, 4, generator=g, dtype=torch.float64), dim=-1)
+    R = do.unitquat_to_rotmat(do.quat_product(p, q))
+    assert torch.allclose(R, do.unitquat_to_rotmat(p) @ do.unitquat_to_rotmat(q), atol=1e-12)
+    w = do.quat_xyzw_to_wxyz(p)
+    assert torch.equal(do.quat_wxyz_to_xyzw(w), p) and torch.equal(w[:, 0], p[:, 3])
+
+
+def test_face_frames_are_orthonormal_and_deform_is_rigid_per_face():
+    a = do.synthetic_avatar(2, 300, 500, 2000, seed=3)
+    R, s = do.compute_face_orientation(a["vertices"], a["faces"])
+    eye = torch.eye(3).expand_as(R)
+    assert torch.allclose(R.transpose(-1, -2) @ R, eye, atol=1e-4)
+    assert (s > 0).all() and s.shape == (2, 500, 1)
+    out = do.deform(**a)
+    P = 300 + 2000
+    assert out["xyz"].shape == (2, P, 3) and out["rotation"].shape == (2, P, 4)
+    assert out["features_color"].shape == (2, P, 32) and out["opacity"].shape == (2, P, 1)
+    # zero local offset puts a UV Gaussian at the barycentric point of its face
+    a0 = dict(a, uv_local_xyz=torch.zeros_like(a["uv_local_xyz"]))
+    c = do.deform(**a0)["xyz"][:, 300:]
+    fv = a["vertices"][:, a["faces"].long()][:, a["uv_binding_face"].long()]
+    assert torch.allclose(c, (a["uv_face_bary"][None, :, :, None] * fv).sum(2), atol=1e-6)
+    # unit input quaternions stay unit
+    assert torch.allclose(out["rotation"].norm(dim=-1), torch.ones(2, P), atol=1e-5)
