@@ -22,6 +22,7 @@ EXPORTS = (
     "guava_rasterizer_forward_batch",
     "guava_rasterizer_backward_batch",
     "guava_pack_view_gradients",
+    "guava_rasterizer_set_refiner_output",
     "guava_deform_gaussians_forward",
     "guava_deform_gaussians_backward",
     "guava_buffer_layout",
@@ -99,6 +100,8 @@ def load() -> ctypes.CDLL:
         c_int, c_int, P]
     lib.guava_pack_view_gradients.restype = c_int
     lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]
+    lib.guava_rasterizer_set_refiner_output.restype = c_int
+    lib.guava_rasterizer_set_refiner_output.argtypes = [P]
     lib.guava_deform_gaussians_forward.restype = c_int
     lib.guava_deform_gaussians_forward.argtypes = [c_int] * 4 + [P] * 21
     lib.guava_deform_gaussians_backward.restype = c_int

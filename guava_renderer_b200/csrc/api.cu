@@ -35,6 +35,8 @@ static std::atomic<long long> g_opt_async_forward{0};
 static std::atomic<long long> g_opt_scalar_red{0};
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
+static thread_local void* t_refiner_output = nullptr;   // consumed by the next forward call of this thread
+
 static int fail(int code, const std::string& msg)
 {
     t_last_error = msg;
@@ -247,6 +249,10 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
                         int debug, cudaStream_t stream, int* num_rendered)
 {
     if (num_rendered) *num_rendered = 0;
+    in.aux_nhwc_bf16 = t_refiner_output;
+    t_refiner_output = nullptr;
+    if (((uintptr_t)in.aux_nhwc_bf16 & 15) != 0)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "refiner output must be 16-byte aligned");
     if (in.V < 0 || in.P < 0 || in.W <= 0 || in.H <= 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
     if ((size_t)in.V * in.P == 0) return GUAVA_OK;   // rasterize_points.cu:88: outputs stay as allocated
@@ -593,6 +599,12 @@ int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const floa
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
+    return GUAVA_OK;
+}
+
+int guava_rasterizer_set_refiner_output(void* out_color_nhwc_bf16)
+{
+    t_refiner_output = out_color_nhwc_bf16;
     return GUAVA_OK;
 }
 

@@ -27,6 +27,7 @@
 //    (pixel, Gaussian) pair (forward.cu:371-372).
 #include "internal.cuh"
 #include "tma.cuh"
+#include <cuda_bf16.h>
 #include <cstdlib>
 
 namespace guava {
@@ -242,6 +243,25 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             oc[(size_t)(2 * ch + 1) * HW] = fmaf(T, bg[2 * ch + 1], C[ch].y);
         }
         if (out_invdepth != nullptr) out_invdepth[(size_t)v * HW + pix] = D;
+        // Refiner hand-off (gaussian_render.py:70-73): the same 32 values once more as one 64-byte
+        // channels-last bf16 pixel, so the refiner's first convolution reads its preferred layout
+        // without a separate permute + cast pass over the image.
+        if (in.aux_nhwc_bf16 != nullptr) {
+            uint4* ap = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(in.aux_nhwc_bf16) +
+                                                 ((size_t)v * HW + pix) * NUM_CHANNELS);
+#pragma unroll
+            for (int q = 0; q < NUM_CHANNELS / 8; q++) {
+                uint32_t w[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int ch = 4 * q + k;
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(fmaf(T, bg[2 * ch], C[ch].x),
+                                                                   fmaf(T, bg[2 * ch + 1], C[ch].y));
+                    w[k] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                ap[q] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
     }
     __syncwarp();   // the stages are reused by the next block
   }

@@ -372,6 +372,14 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
             bufs = _CallBuffers(dev)
             _tls.call = bufs
             rendered = ctypes.c_int(0)
+            aux = getattr(_tls, "refiner_output", None)     # set by renderer.render_views(refiner_input=True)
+            _tls.refiner_output = None
+            if aux is not None:
+                if aux.dtype != torch.bfloat16 or tuple(aux.shape) != (V, H, W, NUM_CHANNELS) or not aux.is_contiguous():
+                    raise ValueError("refiner output must be a contiguous bfloat16 [V,H,W,32] tensor")
+                if V * P == 0:
+                    aux.zero_()
+                _check(lib.guava_rasterizer_set_refiner_output(_ptr(aux)))
             rc = lib.guava_rasterizer_forward_batch(
                 _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
                 V, P, _ptr(bg), W, H,

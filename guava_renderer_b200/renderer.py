@@ -8,7 +8,9 @@ in Python, builds one `GaussianRasterizationSettings` and one
 produces the same output dictionary from ONE launch chain over all views,
 writing straight into the stacked [B,32,H,W] tensor.  The neural refiner
 (StyleUNet, :73) is outside the hot path; pass it as `refiner` to get
-"renders", otherwise that key is omitted.
+"renders", otherwise that key is omitted.  `raw_renders` / `extra_renders` are views of the stacked
+image (no copies, as in :71,:83); `refiner_input=True` adds "refiner_input": the same image as a
+channels-last bf16 tensor written by the compositing kernel itself.
 """
 from __future__ import annotations
 
@@ -28,7 +30,8 @@ def _as_float_list(x, B):
 
 def render_views(gaussian_assets: Dict[str, torch.Tensor], cam_params: Dict[str, torch.Tensor], bg=None,
                  scaling_modifier: float = 1.0, antialiasing: bool = False,
-                 refiner: Optional[Callable[[torch.Tensor], torch.Tensor]] = None) -> Dict[str, torch.Tensor]:
+                 refiner: Optional[Callable[[torch.Tensor], torch.Tensor]] = None,
+                 refiner_input: bool = False) -> Dict[str, torch.Tensor]:
     mean_3d = gaussian_assets['xyz']
     opacity = gaussian_assets['opacity']
     scales = gaussian_assets['scaling']
@@ -59,6 +62,13 @@ def render_views(gaussian_assets: Dict[str, torch.Tensor], cam_params: Dict[str,
         image_height=H, image_width=W, tanfov=tanfov, bg=bg_t, scale_modifier=float(scaling_modifier),
         viewmatrix=cam_params['world_view_transform'], projmatrix=cam_params['full_proj_transform'],
         debug=False, antialiasing=bool(antialiasing))
+    aux = None
+    if refiner_input:
+        # refiner hand-off: the compositing kernel's epilogue also writes the image as
+        # channels-last bf16, the layout/precision a tensor-core first convolution of the refiner wants
+        from . import rasterizer as _rz
+        aux = torch.empty(B, H, W, features_color.shape[-1], dtype=torch.bfloat16, device=device)
+        _rz._tls.refiner_output = aux
     rendered_images, radiis, depth_images = rasterize_gaussians_batch(
         mean_3d, mean_2d, features_color, opacity, scales, rotations, settings)
 
@@ -70,6 +80,9 @@ def render_views(gaussian_assets: Dict[str, torch.Tensor], cam_params: Dict[str,
         "extra_renders": rendered_images[:, 3:4],
         "rendered_images": rendered_images,
     }
+    if aux is not None:
+        # [B,32,H,W] view with channels_last strides: no copy; detached (inference hand-off)
+        out["refiner_input"] = aux.permute(0, 3, 1, 2)
     if refiner is not None:
         out["renders"] = refiner(rendered_images)
     return out

@@ -280,6 +280,15 @@ unsigned long long guava_launch_count(void);
 int guava_stage_time(const char *stage, double *total_ms, unsigned long long *calls);
 void guava_stage_time_reset(void);
 
+/* ---- the step immediately after the rasterizer ---------------------------
+ * Refiner hand-off.  GUAVA feeds the stacked 32-channel image to its neural refiner
+ * (models/UbodyAvatar/gaussian_render.py:70-73).  The NEXT forward call (single-view or batch) made by
+ * the calling thread additionally writes the image as channels-last bf16, [V,H,W,32] (64 bytes per
+ * pixel, round-to-nearest-even of the fp32 values, device pointer, 16-byte aligned), from the
+ * compositing kernel's epilogue -- no separate permute/cast pass.  The setting is consumed by that call;
+ * pass NULL to cancel.  Where P == 0 the image is not written (as for out_color, rasterize_points.cu:88). */
+int guava_rasterizer_set_refiner_output(void *out_color_nhwc_bf16);
+
 /* ---- the step immediately before the rasterizer ------------------------
  * Fused deformation of GUAVA's two Gaussian groups into the concatenated [B, Nv+N, *] tensors the
  * rasterizer reads.  Replaces models/UbodyAvatar/ubody_gaussian.py:245-289 (Ubody_Gaussian.forward:

@@ -431,3 +431,30 @@ def test_full_size_configs_vs_reference_build(ref, case, sort_mode):
     _, gr = _run_autograd(ref, inp, dc * 1e4, None)
     for k in gr:
         assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+
+
+def test_refiner_handoff_is_the_same_image_in_channels_last_bf16():
+    """SURVEY 8(f) row 3 (gaussian_render.py:70-85): the epilogue's channels-last bf16 copy equals
+    permute + round-to-nearest-even cast of the fp32 image, bit for bit; raw/extra renders are views."""
+    V, P, H, W = 2, 6000, 136, 200
+    views = [util.inputs_for(P, H, W, seed=900 + v, view=v, num_views=V, scale_mult=1.2) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    cam = {"world_view_transform": stack("viewmatrix"), "full_proj_transform": stack("projmatrix"),
+           "tanfovx": torch.tensor([x["tanfovx"] for x in views]), "tanfovy": torch.tensor([x["tanfovy"] for x in views]),
+           "image_height": H, "image_width": W}
+    assets = dict(xyz=stack("xyz"), opacity=stack("opacity"), scaling=stack("scaling"), rotation=stack("rotation"),
+                  features_color=stack("features"))
+    out = grb.render_views(assets, cam, bg=0.5, refiner_input=True)
+    torch.cuda.synchronize()
+    img = out["rendered_images"]
+    ri = out["refiner_input"]
+    assert ri.shape == img.shape and ri.dtype == torch.bfloat16
+    assert ri.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(ri.view(torch.int16), img.to(torch.bfloat16).view(torch.int16))
+    assert out["raw_renders"].data_ptr() == img.data_ptr() and out["raw_renders"].shape == (V, 3, H, W)
+    assert out["extra_renders"].data_ptr() == img[:, 3:4].data_ptr()
+    # the request is consumed by one call: the next call must not write to the old buffer
+    ri.zero_()
+    out2 = grb.render_views(assets, cam, bg=0.5)
+    torch.cuda.synchronize()
+    assert "refiner_input" not in out2 and int(ri.view(torch.int16).abs().max()) == 0
