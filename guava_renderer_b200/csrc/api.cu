@@ -220,6 +220,9 @@ __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uin
 }
 
 // One thread per element of the packed [P,43] row: sum over the V views of the source column.
+// V is a template parameter for the common batch sizes so that the V loads of a thread are independent
+// and in flight together (VT == 0: runtime loop).
+template <int VT>
 __global__ void __launch_bounds__(256)
 pack_view_gradients_kernel(int V, int P, const float* __restrict__ g_xyz, const float* __restrict__ g_sc,
                            const float* __restrict__ g_rot, const float* __restrict__ g_op,
@@ -236,8 +239,18 @@ pack_view_gradients_kernel(int V, int P, const float* __restrict__ g_xyz, const 
     else if (j < 10) { src = g_rot; w = 4; c = j - 6; }
     else if (j < 11) { src = g_op; w = 1; c = 0; }
     else { src = g_feat; w = 32; c = j - 11; }
+    const float* q = src + p * w + c;
+    const size_t vs = (size_t)P * w;
     float acc = 0.0f;
-    for (int v = 0; v < V; v++) acc += src[((size_t)v * P + p) * w + c];
+    if (VT > 0) {
+        float x[VT > 0 ? VT : 1];
+#pragma unroll
+        for (int v = 0; v < VT; v++) x[v] = __ldcs(q + (size_t)v * vs);
+#pragma unroll
+        for (int v = 0; v < VT; v++) acc += x[v];
+    } else {
+        for (int v = 0; v < V; v++) acc += __ldcs(q + (size_t)v * vs);
+    }
     packed[idx] = acc;
 }
 
@@ -594,8 +607,16 @@ int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const floa
     if (!dL_dmeans3D || !dL_dscales || !dL_drotations || !dL_dopacity || !dL_dcolors || !packed)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
     const size_t n = (size_t)P * 43;
-    pack_view_gradients_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        V, P, dL_dmeans3D, dL_dscales, dL_drotations, dL_dopacity, dL_dcolors, packed);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+#define GUAVA_PACK(VT) pack_view_gradients_kernel<VT><<<grid, 256, 0, st>>>(V, P, dL_dmeans3D, dL_dscales, dL_drotations, \
+                                                                            dL_dopacity, dL_dcolors, packed)
+    if (V == 1) GUAVA_PACK(1);
+    else if (V == 2) GUAVA_PACK(2);
+    else if (V == 4) GUAVA_PACK(4);
+    else if (V == 8) GUAVA_PACK(8);
+    else GUAVA_PACK(0);
+#undef GUAVA_PACK
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
