@@ -32,9 +32,14 @@
 
 namespace guava {
 
+// Survivor records are staged PAIR-INTERLEAVED: pair k = survivors 2k, 2k+1 of the chunk, so that one
+// LDS.128 delivers a quantity of both as the two halves of packed f32x2 operands.
 struct __align__(128) FwdStage {
     float feat[32][NUM_CHANNELS];   // 4 KB
-    SplatRec rec[32];               // 1 KB
+    float4 xy[16];                  // x0 x1 y0 y1
+    float4 cab[16];                 // conic.x0 conic.x1 -conic.y0 -conic.y1
+    float4 cop[16];                 // conic.z0 conic.z1 opacity0 opacity1
+    float4 dpos[16];                // rdepth0 rdepth1 list-position0 list-position1 (positions as bits, 1-based)
 };
 
 __global__ void __launch_bounds__(32, 16)
@@ -101,12 +106,14 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         const int k = (c << 5) + lane;
         return k < len ? point_list[range.x + k] : NO_ID;
     };
+    // Unconditional (lanes past the end of the list re-read record 0 and are masked by `keep`): a predicated
+    // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
+    // those moves stalled the warp for the whole L2 round trip right after the load was issued
+    // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        if (id != NO_ID) {
-            const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + id);
-            c0 = rp[0];
-            c1 = rp[1];
-        }
+        const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + (id != NO_ID ? id : 0u));
+        c0 = rp[0];
+        c1 = rp[1];
     };
     // Test chunk c (one list entry per lane) and stage the survivors into stage[c & 1].
     // Returns the survivor mask (bit = lane = list offset within the chunk).
@@ -121,9 +128,12 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             __syncwarp();
             if (keep) {
                 const int slot = __popc(mask & lt_mask);
-                float4* dst = reinterpret_cast<float4*>(&st.rec[slot]);
-                dst[0] = c0;
-                dst[1] = c1;
+                const int o = (slot >> 1) * 4 + (slot & 1);
+                float* q;
+                q = &st.xy[0].x + o;   q[0] = c0.x; q[2] = c0.y;
+                q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
+                q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
+                q = &st.dpos[0].x + o; q[0] = c1.z; q[2] = __uint_as_float((uint32_t)(c << 5) + (uint32_t)lane + 1u);
                 tma::bulk_g2s(&st.feat[slot][0], vfeat + (size_t)id * NUM_CHANNELS, NUM_CHANNELS * sizeof(float), bar);
             }
         }
@@ -157,44 +167,48 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
             phase ^= 1u << s;
             __syncwarp();   // the staging lanes' SplatRec stores are visible to every lane
-            const float4* __restrict__ recp = reinterpret_cast<const float4*>(&stage[s].rec[0]);
-            const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
-            const uint32_t pos_base = (uint32_t)(c << 5) + 1u;
-            uint32_t m = mask_cur;
-            // Survivors are walked two at a time: the state-independent half of each pair
-            // (SplatRec load, power, exp, alpha) is evaluated side by side to overlap its
-            // latency chain; the transmittance updates then run strictly in list order, so
-            // every pixel sees exactly the reference's sequence of operations.
-            for (; m != 0u && !warp_done; recp += 4, featp += 2 * (NUM_CHANNELS / 4)) {
-                const int jl0 = __ffs(m) - 1;
-                m &= m - 1;
-                const bool has1 = m != 0u;
-                const int jl1 = has1 ? __ffs(m) - 1 : jl0;
-                m &= m - 1;
-                const float4 p0 = recp[0], p1 = recp[1];   // x, y, cx, cy | cz, op, rdepth, aux
-                const float4 q0 = recp[2], q1 = recp[3];   // second of the pair (stale data if !has1)
-                // SASS order of forward.cu:350-353
-                const float dx0 = fsub(p0.x, pxf), dy0 = fsub(p0.y, pyf);
-                const float dx1 = fsub(q0.x, pxf), dy1 = fsub(q0.y, pyf);
-                const float pw0 = ffma(ffma(dx0, fmul(dx0, p0.z), fmul(dy0, fmul(dy0, p1.x))), -0.5f,
-                                       -fmul(dy0, fmul(dx0, p0.w)));
-                const float pw1 = ffma(ffma(dx1, fmul(dx1, q0.z), fmul(dy1, fmul(dy1, q1.x))), -0.5f,
-                                       -fmul(dy1, fmul(dx1, q0.w)));
-                const float alpha0 = fminf(fmul(p1.y, expf(pw0)), 0.99f);
-                const float alpha1 = fminf(fmul(q1.y, expf(pw1)), 0.99f);
-                const bool ok0 = !(pw0 > 0.0f) && !(alpha0 < 1.0f / 255.0f);
-                const bool ok1 = has1 && !(pw1 > 0.0f) && !(alpha1 < 1.0f / 255.0f);
+            const FwdStage& st = stage[s];
+            const float4* __restrict__ featp = reinterpret_cast<const float4*>(&st.feat[0][0]);
+            const int nsurv = __popc(mask_cur);
+            // Survivors are walked two at a time.  The state-independent half of both alpha chains (offsets,
+            // power, exp, alpha, 1 - alpha) is evaluated with packed f32x2 instructions -- per half the very
+            // operations, in the very order, of forward.cu:350-358 as compiled -- the transmittance updates
+            // then run strictly in list order, so every pixel sees exactly the reference's sequence.
+            // ... and it is software-pipelined: the chain of pair k+1 (LDS -> offsets -> power -> exp -> alpha) is
+            // issued before the transmittance updates and the blends of pair k, whose FFMA2 stream hides its latency.
+            float2 pw_n, al_n, om_n;
+            float4 pd_n;
+            auto eval_pair = [&](int k) {
+                const float4 pa = st.xy[k], pb = st.cab[k], pc = st.cop[k];
+                pd_n = st.dpos[k];
+                const float2 dx = __fadd2_rn(f2(pa.x, pa.y), f2(-pxf));
+                const float2 dy = __fadd2_rn(f2(pa.z, pa.w), f2(-pyf));
+                const float2 qd = __ffma2_rn(dx, __fmul2_rn(dx, f2(pb.x, pb.y)), __fmul2_rn(dy, __fmul2_rn(dy, f2(pc.x, pc.y))));
+                pw_n = __ffma2_rn(qd, f2(-0.5f), __fmul2_rn(dy, __fmul2_rn(dx, f2(pb.z, pb.w))));   // pb.zw = -conic.y
+                const float2 ag = __fmul2_rn(f2(pc.z, pc.w), expf_pair(pw_n));
+                al_n = f2(fminf(ag.x, 0.99f), fminf(ag.y, 0.99f));
+                om_n = __ffma2_rn(al_n, f2(-1.0f), f2(1.0f));                                        // 1 - alpha
+            };
+            eval_pair(0);
+            for (int k = 0; 2 * k < nsurv && !warp_done; k++, featp += 2 * (NUM_CHANNELS / 4)) {
+                const bool has1 = 2 * k + 1 < nsurv;
+                const float2 pw = pw_n, om = om_n;
+                const float alpha0 = al_n.x, alpha1 = al_n.y;
+                const float4 pd = pd_n;
+                eval_pair(min(k + 1, 15));   // past the last pair: a harmless re-evaluation of staged (or stale) data
+                const bool ok0 = !(pw.x > 0.0f) && !(alpha0 < 1.0f / 255.0f);
+                const bool ok1 = has1 && !(pw.y > 0.0f) && !(alpha1 < 1.0f / 255.0f);
                 // in list order
                 bool take0 = !done && ok0;
-                const float test_T0 = fmul(T, fsub(1.0f, alpha0));
+                const float test_T0 = fmul(T, om.x);
                 if (take0 && test_T0 < 0.0001f) { done = true; take0 = false; }
                 const float w0 = take0 ? fmul(alpha0, T) : 0.0f;
-                if (take0) { T = test_T0; last_contributor = pos_base + (uint32_t)jl0; }
+                if (take0) { T = test_T0; last_contributor = __float_as_uint(pd.z); }
                 bool take1 = !done && ok1;
-                const float test_T1 = fmul(T, fsub(1.0f, alpha1));
+                const float test_T1 = fmul(T, om.y);
                 if (take1 && test_T1 < 0.0001f) { done = true; take1 = false; }
                 const float w1 = take1 ? fmul(alpha1, T) : 0.0f;
-                if (take1) { T = test_T1; last_contributor = pos_base + (uint32_t)jl1; }
+                if (take1) { T = test_T1; last_contributor = __float_as_uint(pd.w); }
                 if (__any_sync(0xffffffffu, take0)) {
                     const float2 w2 = make_float2(w0, w0);
 #pragma unroll
@@ -203,7 +217,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                         C[2 * q + 0] = __ffma2_rn(w2, make_float2(f.x, f.y), C[2 * q + 0]);
                         C[2 * q + 1] = __ffma2_rn(w2, make_float2(f.z, f.w), C[2 * q + 1]);
                     }
-                    D = fmaf(w0, p1.z, D);
+                    D = fmaf(w0, pd.x, D);
                 }
                 if (__any_sync(0xffffffffu, take1)) {
                     const float2 w2 = make_float2(w1, w1);
@@ -213,7 +227,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                         C[2 * q + 0] = __ffma2_rn(w2, make_float2(f.x, f.y), C[2 * q + 0]);
                         C[2 * q + 1] = __ffma2_rn(w2, make_float2(f.z, f.w), C[2 * q + 1]);
                     }
-                    D = fmaf(w1, q1.z, D);
+                    D = fmaf(w1, pd.y, D);
                 }
                 if (__all_sync(0xffffffffu, done)) warp_done = true;
             }
