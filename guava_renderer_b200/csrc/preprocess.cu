@@ -181,10 +181,10 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
     rec.x = px; rec.y = py; rec.cx = conx; rec.cy = cony; rec.cz = conz;
     rec.op = fmul(h_scale, opacity);
     rec.rdepth = __frcp_rn(depth);
-    rec.aux = lambda1;
+    rec.lthr = __logf(255.0f * rec.op) + 0.01f;   // culling threshold ln(255*opacity) + margin (splat_may_touch)
     float4* rp = reinterpret_cast<float4*>(g.rec + gid);
     rp[0] = make_float4(rec.x, rec.y, rec.cx, rec.cy);
-    rp[1] = make_float4(rec.cz, rec.op, rec.rdepth, rec.aux);
+    rp[1] = make_float4(rec.cz, rec.op, rec.rdepth, rec.lthr);
     g.depths[gid] = depth;
     radii[gid] = rad;
     g.rects[gid] = make_ushort4((unsigned short)minx, (unsigned short)miny, (unsigned short)maxx, (unsigned short)maxy);

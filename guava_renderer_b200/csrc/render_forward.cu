@@ -119,7 +119,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     // Returns the survivor mask (bit = lane = list offset within the chunk).
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
         const bool keep = id != NO_ID &&
-                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
+                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             FwdStage& st = stage[c & 1];

@@ -222,7 +222,7 @@ typedef struct guava_layout {
     /* geometry buffer (per Gaussian instance g = view*P + i) */
     size_t geom_bytes;
     size_t splat_rec;      /* float[8] per g: mean2D.x, mean2D.y, conic.x, conic.y, conic.z,
-                              opacity*h_scale, 1/depth (rcp.rn), reserved */
+                              opacity*h_scale, 1/depth (rcp.rn), ln(255*opacity*h_scale)+0.01 (culling threshold) */
     size_t depths;         /* float per g (view-space z) */
     size_t rects;          /* uint16[4] per g: tile rect min.x, min.y, max.x, max.y */
     size_t tiles_touched;  /* uint32 per g */
