@@ -27,6 +27,7 @@
 // replacement of the reference's CUB chain; at the GUAVA shapes the bucket path
 // moves 20 B per instance instead of ~150 B and stays the default.
 #include "internal.cuh"
+#include "tma.cuh"
 
 namespace guava {
 
@@ -178,8 +179,9 @@ onesweep_pass_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restric
                      const uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ ticket,
                      const uint32_t* __restrict__ hist, uint32_t* __restrict__ state, int shift, uint32_t mask)
 {
-    __shared__ uint64_t s_keys[OS_PART];
-    __shared__ uint32_t s_vals[OS_PART];
+    __shared__ __align__(128) uint64_t s_keys[OS_PART];
+    __shared__ __align__(128) uint32_t s_vals[OS_PART];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_whist[OS_WARPS][256];
     __shared__ uint32_t s_goff[256];    // global position of the digit's first pair of this partition, minus s_bexcl
     __shared__ uint32_t s_bexcl[256];   // first local (sorted) position of the digit
@@ -190,7 +192,11 @@ onesweep_pass_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restric
     const uint32_t R = num_rendered[0];
     const uint32_t nparts = (R + OS_PART - 1) / OS_PART;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_part = atomicAdd(ticket, 1u);
+    if (tid == 0) {
+        s_part = atomicAdd(ticket, 1u);
+        tma::mbar_init(&s_bar, 1);
+        tma::fence_mbar_init();
+    }
 #pragma unroll
     for (int k = 0; k < OS_WARPS; k++) s_whist[k][tid] = 0u;
     __syncthreads();
@@ -198,29 +204,41 @@ onesweep_pass_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restric
     if (part >= nparts) return;   // block-uniform
     const uint32_t base = part * OS_PART;
     const uint32_t nvalid = min((uint32_t)OS_PART, R - base);
+    // The partition is one contiguous, 16-byte aligned run of keys and one of values: two TMA bulk copies
+    // (cp.async.bulk, completion on an mbarrier transaction count) bring it into the shared-memory buffers
+    // that later hold the sorted order; sizes are rounded up to 16 bytes (the padding lies inside the
+    // 256-byte aligned allocation and is never used).
+    if (tid == 0) {   // issued first: the copies run under the histogram load and the constant-digit vote below
+        const uint32_t kb = ((nvalid * 8u) + 15u) & ~15u, vb = ((nvalid * 4u) + 15u) & ~15u;
+        tma::mbar_arrive_expect_tx(&s_bar, kb + vb);
+        tma::bulk_g2s(s_keys, kin + base, kb, &s_bar);
+        tma::bulk_g2s(s_vals, vin + base, vb, &s_bar);
+    }
 
     // A pass whose digit is the same for every key (e.g. the exponent byte of the depths) is the
     // identity permutation: copy the partition straight through, no ranking, no look-back.
     const uint32_t my_hist = hist[tid];
     if (__syncthreads_or(my_hist == R)) {
+        tma::mbar_wait(&s_bar, 0u);
 #pragma unroll
         for (int i = 0; i < OS_ITEMS; i++) {
             const uint32_t j = (uint32_t)(i * OS_THREADS + tid);
             if (j < nvalid) {
-                kout[base + j] = kin[base + j];
-                vout[base + j] = vin[base + j];
+                kout[base + j] = s_keys[j];
+                vout[base + j] = s_vals[j];
             }
         }
         return;
     }
 
+    tma::mbar_wait(&s_bar, 0u);
     uint64_t key[OS_ITEMS];
     uint32_t val[OS_ITEMS], rank[OS_ITEMS];
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; i++) {
         const uint32_t j = (uint32_t)(warp * (32 * OS_ITEMS) + i * 32 + lane);
-        key[i] = j < nvalid ? kin[base + j] : ~0ull;
-        val[i] = j < nvalid ? vin[base + j] : 0u;
+        key[i] = j < nvalid ? s_keys[j] : ~0ull;
+        val[i] = j < nvalid ? s_vals[j] : 0u;
     }
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t* wh = s_whist[warp];

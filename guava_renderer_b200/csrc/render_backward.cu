@@ -7,7 +7,7 @@
 // live per thread (173 registers).
 //
 // B200 design:
-//  * same TMA-staged, double-buffered instance batches as the forward kernel
+//  * same asynchronously staged, double-buffered instance batches as the forward kernel
 //    (SplatRec + 128-byte feature row per instance), walked in reverse;
 //  * warp-footprint culling (splat_may_touch, internal.cuh): each warp owns an
 //    8x4 pixel block and walks only the staged splats that can reach
@@ -64,21 +64,13 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ work_counter)
 {
     __shared__ BwdStage stage[2];
-    __shared__ __align__(8) uint64_t full_bar[2];
     __shared__ __align__(16) float ex[4][8][EX_STRIDE];   // per-survivor exchange: two pairs in flight
 
     const int lane = threadIdx.x;
-    if (lane == 0) {
-        tma::mbar_init(&full_bar[0], 1);
-        tma::mbar_init(&full_bar[1], 1);
-        tma::fence_mbar_init();
-    }
-    __syncwarp();
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
     uint32_t parity = 0;   // ex buffers (parity, parity+1) & 3 are used by the next pair
     float* const exbase = &ex[0][0][0];
-    uint32_t phase = 0;    // bit s = parity to wait for on full_bar[s]
 
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
     const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
@@ -145,8 +137,6 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             gT[p].y = scratch[(2 * p + 1) * 32 + (lane ^ (2 * p + 1))];
         }
     }
-    // generic-proxy accesses to the scratch are ordered before the async-proxy (TMA) writes
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
 
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
@@ -174,17 +164,23 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             BwdStage& st = stage[c & 1];
-            uint64_t* bar = &full_bar[c & 1];
-            if (lane == 0) tma::mbar_arrive_expect_tx(bar, (uint32_t)__popc(mask) * (NUM_CHANNELS * 4u));
-            __syncwarp();
             if (keep) {
                 const int slot = __popc(mask & lt_mask);
                 float4* dst = reinterpret_cast<float4*>(&st.rec[slot]);
                 dst[0] = c0;
                 dst[1] = c1;
-                tma::bulk_g2s(&st.feat[slot][0], vfeat + (size_t)id * NUM_CHANNELS, NUM_CHANNELS * sizeof(float), bar);
+                // the lane's own 128-byte feature row as eight 16-byte asynchronous copies, piece order rotated by
+                // the slot so that the lanes of one instruction fall on distinct bank groups (render_forward.cu)
+                const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
+                char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int piece = ((j + slot) & 7) * 16;
+                    tma::cp_async16(dstf + piece, src + piece);
+                }
             }
         }
+        tma::cp_async_commit();   // one group per chunk, empty or not: the waits count groups
         return mask;
     };
 
@@ -201,15 +197,16 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     uint32_t id_nn = load_id(2);
     for (int c = 0; c < nchunks; c++) {
         // id_cur: ids of chunk c (for the gradient addresses); id_next / a0,a1: chunk c+1
-        const uint32_t mask_next = (c + 1 < nchunks) ? stage_chunk(c + 1, id_next, a0, a1) : 0u;
+        uint32_t mask_next = 0u;
+        if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
+        else tma::cp_async_commit();
         const uint32_t id_after = id_next;
         id_next = id_nn;
         load_rec(id_next, a0, a1);
         id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
-            tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
-            phase ^= 1u << s;
+            tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
             __syncwarp();
             const float4* __restrict__ recp = reinterpret_cast<const float4*>(&stage[s].rec[0]);
             const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
@@ -360,6 +357,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         id_cur = id_after;
         __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
     }
+    tma::cp_async_wait<0>();
+    __syncwarp();   // nothing in flight when the next block reuses the stages
   }
 }
 

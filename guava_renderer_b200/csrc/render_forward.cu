@@ -20,11 +20,13 @@
 //    staged and blended.  The tile lists themselves (keys, order, ranges) stay
 //    exactly the reference's, so n_contrib keeps its meaning (list position).
 //  * Survivors are compacted into a double-buffered shared-memory stage: the
-//    32-byte SplatRec by the lane that tested it, the 128-byte feature row by a
-//    TMA bulk copy (cp.async.bulk + mbarrier transaction count) issued by that
-//    lane, so the next chunk's rows stream in while the current one is blended.
-//    The reference re-reads the 32 features from global memory for every
-//    (pixel, Gaussian) pair (forward.cu:371-372).
+//    record by the lane that tested it (pair-interleaved, see FwdStage), the
+//    128-byte feature row by eight 16-byte asynchronous copies of that lane
+//    (cp.async / LDGSTS, one commit group per chunk), so the next chunk's rows
+//    stream in while the current one is blended.  (First version: one TMA bulk
+//    copy per row; see tma.cuh for why that lost.)  The reference re-reads the
+//    32 features from global memory for every (pixel, Gaussian) pair
+//    (forward.cu:371-372).
 #include "internal.cuh"
 #include "tma.cuh"
 #include <cuda_bf16.h>
@@ -50,18 +52,10 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
     __shared__ FwdStage stage[2];
-    __shared__ __align__(8) uint64_t full_bar[2];
 
     if (num_rendered[1]) return;   // binning overflowed; the host re-runs
     const int lane = threadIdx.x;
-    if (lane == 0) {
-        tma::mbar_init(&full_bar[0], 1);
-        tma::mbar_init(&full_bar[1], 1);
-        tma::fence_mbar_init();
-    }
-    __syncwarp();
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint32_t phase = 0;   // bit s = parity to wait for on full_bar[s]
 
     // Persistent warps: the grid is sized to fill the machine once and every warp pulls
     // 8x4 pixel blocks from a global work counter (num_rendered[2], zeroed by the tile
@@ -123,9 +117,6 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             FwdStage& st = stage[c & 1];
-            uint64_t* bar = &full_bar[c & 1];
-            if (lane == 0) tma::mbar_arrive_expect_tx(bar, (uint32_t)__popc(mask) * (NUM_CHANNELS * 4u));
-            __syncwarp();
             if (keep) {
                 const int slot = __popc(mask & lt_mask);
                 const int o = (slot >> 1) * 4 + (slot & 1);
@@ -134,9 +125,18 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
                 q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
                 q = &st.dpos[0].x + o; q[0] = c1.z; q[2] = __uint_as_float((uint32_t)(c << 5) + (uint32_t)lane + 1u);
-                tma::bulk_g2s(&st.feat[slot][0], vfeat + (size_t)id * NUM_CHANNELS, NUM_CHANNELS * sizeof(float), bar);
+                // the lane's own 128-byte feature row as eight 16-byte asynchronous copies; the piece order is
+                // rotated by the slot so that the 32 lanes of one instruction fall on distinct bank groups
+                const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
+                char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int piece = ((j + slot) & 7) * 16;
+                    tma::cp_async16(dstf + piece, src + piece);
+                }
             }
         }
+        tma::cp_async_commit();   // one group per chunk, empty or not: the waits below count groups
         return mask;
     };
 
@@ -158,15 +158,16 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     load_rec(id_next, a0, a1);
     id_nn = load_id(2);
     for (int c = 0; c < nchunks; c++) {
-        const uint32_t mask_next = (c + 1 < nchunks) ? stage_chunk(c + 1, id_next, a0, a1) : 0u;
+        uint32_t mask_next = 0u;
+        if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
+        else tma::cp_async_commit();
         id_next = id_nn;
         load_rec(id_next, a0, a1);
         id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
-            tma::mbar_wait(&full_bar[s], (phase >> s) & 1u);
-            phase ^= 1u << s;
-            __syncwarp();   // the staging lanes' SplatRec stores are visible to every lane
+            tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+            __syncwarp();              // ... and the staging lanes' stores and copies are visible to every lane
             const FwdStage& st = stage[s];
             const float4* __restrict__ featp = reinterpret_cast<const float4*>(&st.feat[0][0]);
             const int nsurv = __popc(mask_cur);
@@ -233,11 +234,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             }
         }
         if (warp_done) {
-            // never leave the block with a bulk copy still in flight
-            if (mask_next != 0u) {
-                tma::mbar_wait(&full_bar[s ^ 1], (phase >> (s ^ 1)) & 1u);
-                phase ^= 1u << (s ^ 1);
-            }
+            tma::cp_async_wait<0>();   // never leave the block with a copy still in flight
             break;
         }
         mask_cur = mask_next;
@@ -277,6 +274,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             }
         }
     }
+    tma::cp_async_wait<0>();
     __syncwarp();   // the stages are reused by the next block
   }
 }

@@ -26,7 +26,7 @@
  * cov3D_precomp [P,6], viewmatrix / projmatrix [16] transposed as in
  * auxiliary.h:70-89, background [32], out_color [32,H,W], out_invdepth
  * [1,H,W], radii [P] int32).  `colors_precomp` must be 16-byte aligned (rows
- * are fetched with 128-byte TMA bulk copies).
+ * are fetched with 16-byte asynchronous copies).
  */
 #ifndef GUAVA_RASTERIZER_H_INCLUDED
 #define GUAVA_RASTERIZER_H_INCLUDED

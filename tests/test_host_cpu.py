@@ -33,12 +33,14 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert b"sm_100a" in lib.guava_version()
 
 
-def test_shared_object_contains_sm100a_tma_code():
+def test_shared_object_contains_sm100a_specific_code():
     from guava_renderer_b200 import _lib
     out = subprocess.run(["cuobjdump", "-lelf", _lib.SO_PATH], capture_output=True, text=True).stdout
     assert "sm_100a" in out
     sass = subprocess.run(["cuobjdump", "-sass", _lib.SO_PATH], capture_output=True, text=True).stdout
-    assert "UBLKCP" in sass and "SYNCS.ARRIVE.TRANS64" in sass      # cp.async.bulk + mbarrier tx-count
+    assert "UBLKCP" in sass and "SYNCS.ARRIVE.TRANS64" in sass      # cp.async.bulk + mbarrier tx-count (onesweep partitions)
+    assert "FFMA2" in sass and "FMUL2" in sass                      # packed f32x2 arithmetic (compositors), sm_100 only
+    assert "LDGSTS" in sass                                         # asynchronous feature-row staging
 
 
 def test_options_and_layout():
