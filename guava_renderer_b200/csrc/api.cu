@@ -132,7 +132,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->n_contrib = o;    o = align_up(o + npix * 4);
     L->ranges = o;       o = align_up(o + tiles * 8);
     L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE);
-    L->tile_order = o;   o = align_up(o + tiles * 4);
+    L->tile_order = o;   o = align_up(o + tiles * 16);
     L->num_rendered = o; o = align_up(o + 32);
     L->image_bytes = o;
     o = 0;
@@ -314,7 +314,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
     im.ranges = (uint2*)(img + L.ranges);
     im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
-    im.tile_order = (uint32_t*)(img + L.tile_order);
+    im.tile_order = (uint4*)(img + L.tile_order);
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
 
     const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
@@ -442,7 +442,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     im.n_contrib = (uint32_t*)(img + L.n_contrib);
     im.ranges = (uint2*)(img + L.ranges);
     im.tile_cursor = (uint32_t*)(img + L.tile_cursor);
-    im.tile_order = (uint32_t*)(img + L.tile_order);
+    im.tile_order = (uint4*)(img + L.tile_order);
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
     BinningPtrs b;
     b.point_list = (uint32_t*)(bin + L.point_list);   // offset 0 for every capacity

@@ -52,7 +52,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t x, uint32
 }
 
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
+tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint4* __restrict__ tile_order,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
 {
     __shared__ uint32_t warp_sums[32];
@@ -103,7 +103,9 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
             uint32_t pos = 0;
             if ((tid & 31) == leader && bin < 256u) pos = atomicAdd(&bins[bin], (uint32_t)__popc(peers));
             pos = __shfl_sync(0xffffffffu, pos, leader);
-            if (bin < 256u) tile_order[pos + __popc(peers & ((1u << (tid & 31)) - 1u))] = (uint32_t)k;
+            if (bin < 256u)
+                tile_order[pos + __popc(peers & ((1u << (tid & 31)) - 1u))] =
+                    c ? make_uint4((uint32_t)k, run, run + c, 0u) : make_uint4((uint32_t)k, 0u, 0u, 0u);
         }
         carry += chunk_total;
     }

@@ -58,7 +58,7 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 template <int VEC_RED>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
-                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                        const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ work_counter)
@@ -84,7 +84,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
   uint32_t work = fetch_work();
   while (work < total_work) {
     const uint32_t work_next = fetch_work();
-    const uint32_t gtile = tile_order[work >> 3];   // longest lists first
+    const uint4 item = tile_order[work >> 3];   // longest lists first: (tile, range.x, range.y)
+    const uint32_t gtile = item.x;
     const int sub = (int)(work & 7u);
     work = work_next;
     const int v = (int)(gtile / (uint32_t)in.tiles);
@@ -102,7 +103,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const int total = (int)__reduce_max_sync(0xffffffffu, last_contributor);   // list entries this block walks
     if (total == 0) continue;
     const int nchunks = (total + 31) >> 5;
-    const uint2 range = ranges[(size_t)v * in.tiles + tile];
+    const uint2 range = make_uint2(item.y, item.z);
 
     // upstream gradients of this pixel, all channels (row of the block's 32x32 matrix) ...
     float2 g[NUM_CHANNELS / 2];   // channel pairs, for packed FFMA2 (sm_100 fma.rn.f32x2)

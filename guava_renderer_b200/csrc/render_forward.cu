@@ -46,7 +46,7 @@ struct __align__(128) FwdStage {
 
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
-                      const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                      const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                       const uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
@@ -71,7 +71,11 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
   uint32_t work = fetch_work();
   while (work < total_work) {
     const uint32_t work_next = fetch_work();   // in flight while this block is blended
-    const uint32_t gtile = tile_order[work >> 3];   // longest lists first
+    // one 16-byte work item (tile, list range) instead of two dependent loads (tile order -> range); claiming
+    // two blocks ahead to hide this load as well measured 10 % slower (coarser dynamic balancing)
+    const uint4 item = tile_order[work >> 3];   // longest lists first
+    const uint32_t gtile = item.x;
+    const uint2 range = make_uint2(item.y, item.z);
     const int sub = (int)(work & 7u);
     work = work_next;
     const int v = (int)(gtile / (uint32_t)in.tiles);
@@ -84,7 +88,6 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const float pxf = (float)px, pyf = (float)py;
     const float wx0 = (float)bx, wy0 = (float)by;
 
-    const uint2 range = ranges[(size_t)v * in.tiles + tile];
     const int len = (int)(range.y - range.x);
     const int nchunks = (len + 31) >> 5;
 

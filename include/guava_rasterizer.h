@@ -235,7 +235,7 @@ typedef struct guava_layout {
     size_t n_contrib;      /* uint32 per pixel [V*H*W] */
     size_t ranges;         /* uint2 per tile   [V*tiles]; values are offsets into point_list */
     size_t tile_cursor;    /* uint32 per tile, one per 128-byte line (scratch) */
-    size_t tile_order;     /* uint32 per tile: tile indices, longest list first (work order) */
+    size_t tile_order;     /* uint32[4] per tile, longest list first (work order): tile index, range.x, range.y, 0 */
     size_t num_rendered;   /* uint32[8]: R, capacity-overflow flag, two work counters, longest tile list, - */
     /* binning buffer for a capacity of `capacity` instances */
     size_t binning_bytes;
