@@ -458,3 +458,23 @@ def test_refiner_handoff_is_the_same_image_in_channels_last_bf16():
     out2 = grb.render_views(assets, cam, bg=0.5)
     torch.cuda.synchronize()
     assert "refiner_input" not in out2 and int(ri.view(torch.int16).abs().max()) == 0
+
+
+def test_equal_depth_ties_keep_index_order(sort_mode):
+    """Gaussians with bit-identical depth in one tile must come out in ascending index order (the reference's
+    stable sort over an index-ascending emission).  Every Gaussian is duplicated three times, so every tile
+    list is full of ties, at list lengths that reach every size class of the per-tile sort."""
+    base = util.inputs_for(2500, 96, 128, seed=61, scale_mult=2.0)
+    inp = dict(base)
+    for k in ("xyz", "features", "opacity", "scaling", "rotation"):
+        inp[k] = torch.cat([base[k], base[k], base[k]], 0).contiguous()
+    o = _ours_forward(inp)
+    f = util.oracle_forward(inp)
+    lens = f["ranges"][:, 1].astype(np.int64) - f["ranges"][:, 0]
+    assert lens.max() > 256 and (lens > 256).sum() >= 4
+    assert np.array_equal(o["ranges"], f["ranges"])
+    assert np.array_equal(o["keys"], f["keys"])
+    assert np.array_equal(o["point_list"], f["point_list"])
+    k = o["keys"]
+    same = k[1:] == k[:-1]
+    assert same.mean() > 0.5 and np.all(o["point_list"][1:][same] > o["point_list"][:-1][same])
