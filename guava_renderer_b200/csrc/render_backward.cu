@@ -45,19 +45,9 @@ static_assert(sizeof(BwdStage) >= 32 * 32 * sizeof(float), "a stage doubles as t
 // the row-sum LDS.128 (lanes 4k..4k+3 read row k) fall on distinct banks
 constexpr int EX_STRIDE = 36;
 
-// Reductions under a PREDICATE, not a branch: which lanes reduce is lane-dependent ((lane & 3) == 0), and as
-// `if (...) red` the compiler brackets every one of them with BSSY / BSYNC reconvergence points -- 6 % of the
-// kernel's stall samples sat on those (profiles/r01_v14).
-__device__ __forceinline__ void red_add_v4_if(bool on, float* addr, float a, float b, float c, float d)
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
 {
-    asm volatile("{\n.reg .pred p;\nsetp.ne.u32 p, %5, 0;\n@p red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n}" ::"l"(addr),
-                 "f"(a), "f"(b), "f"(c), "f"(d), "r"((uint32_t)on)
-                 : "memory");
-}
-__device__ __forceinline__ void red_add_if(bool on, float* addr, float a)
-{
-    asm volatile("{\n.reg .pred p;\nsetp.ne.u32 p, %2, 0;\n@p red.global.add.f32 [%0], %1;\n}" ::"l"(addr), "f"(a),
-                 "r"((uint32_t)on)
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                  : "memory");
 }
 
@@ -346,7 +336,9 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
                 const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
                 const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
-                const bool geo_lane = (lane & 3) == 0 && lane < 28;
+                // All reductions of the pair sit in ONE lane-divergent region (lanes 0, 4, .., 28); four separate
+                // `if (lane ...) red` were four BSSY/BSYNC reconvergence brackets, 7 % of the kernel's stall samples
+                // (profiles/r01_v15).  Lane 28 adds 0 to the unused eighth word of the packed record.
                 if (VEC_RED) {
                     const float a1 = __shfl_down_sync(0xffffffffu, col0, 1);
                     const float a2 = __shfl_down_sync(0xffffffffu, col0, 2);
@@ -354,14 +346,24 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     const float b1 = __shfl_down_sync(0xffffffffu, col1, 1);
                     const float b2 = __shfl_down_sync(0xffffffffu, col1, 2);
                     const float b3 = __shfl_down_sync(0xffffffffu, col1, 3);
-                    red_add_v4_if(any0 && (lane & 3) == 0, dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
-                    red_add_v4_if(any1 && (lane & 3) == 0, dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
+                    const float m0 = lane < 28 ? mom0 : 0.0f, m1 = lane < 28 ? mom1 : 0.0f;
+                    if ((lane & 3) == 0) {
+                        if (any0) {
+                            red_add_v4(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
+                            atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), m0);
+                        }
+                        if (any1) {
+                            red_add_v4(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
+                            atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), m1);
+                        }
+                    }
                 } else {
-                    red_add_if(any0, dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
-                    red_add_if(any1, dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
+                    const bool geo_lane = (lane & 3) == 0 && lane < 28;
+                    if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
+                    if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
+                    if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
+                    if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
                 }
-                red_add_if(any0 && geo_lane, grad_geo + gi0 * 8 + (lane >> 2), mom0);
-                red_add_if(any1 && geo_lane, grad_geo + gi1 * 8 + (lane >> 2), mom1);
             }
         }
         mask_cur = mask_next;
