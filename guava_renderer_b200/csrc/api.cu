@@ -131,7 +131,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->final_T = o;      o = align_up(o + npix * 4);
     L->n_contrib = o;    o = align_up(o + npix * 4);
     L->ranges = o;       o = align_up(o + tiles * 8);
-    L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE);
+    L->tile_cursor = o;  o = align_up(o + tiles * 4 * CURSOR_STRIDE + tile_scan_scratch_bytes(tiles));   // + scan scratch
     L->tile_order = o;   o = align_up(o + tiles * 16);
     L->num_rendered = o; o = align_up(o + 32);
     L->image_bytes = o;
@@ -324,7 +324,8 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     const int total_tiles = in.V * in.tiles;
     StageTimer timer(stream);
     timer.begin(0);
-    GUAVA_CUDA(cudaMemsetAsync(im.tile_cursor, 0, (size_t)total_tiles * 4 * CURSOR_STRIDE, stream));
+    GUAVA_CUDA(cudaMemsetAsync(im.tile_cursor, 0,
+                               (size_t)total_tiles * 4 * CURSOR_STRIDE + tile_scan_scratch_bytes((size_t)total_tiles), stream));
     launch_preprocess_forward(in, g, im, radii, stream);
     timer.end();
     GUAVA_STAGE("preprocess", debug);

@@ -51,79 +51,106 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t x, uint32
     return incl - x + ((tid >> 5) ? warp_sums[(tid >> 5) - 1] : 0u);
 }
 
+// Scan scratch (zeroed with the tile counters, which it follows in the image buffer): ticket, longest list,
+// 256 length bins, 256 bin cursors, one look-back word per 1024-tile block.
+constexpr int SCAN_TICKET = 0, SCAN_LONGEST = 1, SCAN_BINS = 32, SCAN_BINCUR = 288, SCAN_STATE = 544;
+size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (total_tiles + 1023) / 1024 + 1); }
+
+// Kernel 1: one block per 1024 tiles, chained by a decoupled look-back (blocks ordered by ticket): exclusive
+// scan of the per-tile counts = tile ranges (identifyTileRanges) and bucket cursors, the histogram of list
+// lengths for kernel 2, the longest list, and -- by the last block of the chain -- R and the overflow flag.
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint4* __restrict__ tile_order,
+tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ scratch,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
-    __shared__ uint32_t longest;
-    const int tid = threadIdx.x;
+    __shared__ uint32_t s_bid, s_carry;
+    const int tid = threadIdx.x, lane = tid & 31;
     if (tid < 256) bins[tid] = 0u;
-    if (tid == 0) longest = 0u;
+    if (tid == 0) s_bid = atomicAdd(scratch + SCAN_TICKET, 1u);
     __syncthreads();
-    // Pass 1: a longest-list-first order of the tiles (counting sort on 255 - len/8), in which the
-    // persistent compositing kernels pull their work so that the long lists -- each a serial chain
-    // through one warp -- start first and the short ones fill the tail; and the longest list.
-    uint32_t my_max = 0;
-    for (int k = tid; k < n; k += 1024) {
-        const uint32_t c = cursor[(size_t)k * CURSOR_STRIDE];
-        my_max = max(my_max, c);
-        // warp-aggregated: most tiles of a frame are empty and would all hit one counter
-        const uint32_t bin = 255u - min(c >> 3, 255u);
-        const uint32_t peers = __match_any_sync(__activemask(), bin);
-        if ((uint32_t)(tid & 31) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&bins[bin], (uint32_t)__popc(peers));
-    }
-    my_max = __reduce_max_sync(0xffffffffu, my_max);
-    if ((tid & 31) == 0 && my_max != 0u) atomicMax(&longest, my_max);
-    __syncthreads();
+    const int bid = (int)s_bid;
+    const int nblocks = (n + 1023) / 1024;
+    const int k = bid * 1024 + tid;
+    const uint32_t c = k < n ? cursor[(size_t)k * CURSOR_STRIDE] : 0u;
+    // length bins (255 - len/8) and the longest list; warp-aggregated: most tiles of a frame are empty
     {
-        uint32_t dummy;
-        const uint32_t mine = tid < 256 ? bins[tid] : 0u;
-        const uint32_t ex = block_exclusive_scan_1024(mine, warp_sums, tid, dummy);
-        if (tid < 256) bins[tid] = ex;
+        const uint32_t bin = k < n ? 255u - min(c >> 3, 255u) : 256u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        if (lane == __ffs(peers) - 1 && bin < 256u) atomicAdd(&bins[bin], (uint32_t)__popc(peers));
+        const uint32_t wmax = __reduce_max_sync(0xffffffffu, c);
+        if (lane == 0 && wmax != 0u) atomicMax(scratch + SCAN_LONGEST, wmax);
+    }
+    uint32_t chunk_total;
+    const uint32_t local = block_exclusive_scan_1024(c, warp_sums, tid, chunk_total);   // syncs: bins complete
+    if (tid < 256 && bins[tid] != 0u) atomicAdd(scratch + SCAN_BINS + tid, bins[tid]);
+    __threadfence();   // the bins and the maximum are visible before this block's word is published
+    __syncthreads();
+    if (tid < 32) {
+        uint32_t* state = scratch + SCAN_STATE;
+        if (lane == 0) st_volatile(state + bid, (chunk_total & LB_VAL) | (bid == 0 ? LB_INC : LB_AGG));
+        const uint32_t carry = lookback_exclusive_warp(state, bid, lane);
+        if (lane == 0) {
+            if (bid > 0) st_volatile(state + bid, ((carry + chunk_total) & LB_VAL) | LB_INC);
+            s_carry = carry;
+        }
     }
     __syncthreads();
-    // Pass 2: exclusive scan of the counts = tile ranges (identifyTileRanges) and bucket cursors.
-    uint32_t carry = 0;
-    for (int base = 0; base < n; base += 1024) {
-        const int k = base + tid;
-        const uint32_t c = k < n ? cursor[(size_t)k * CURSOR_STRIDE] : 0u;
-        uint32_t chunk_total;
-        const uint32_t run = carry + block_exclusive_scan_1024(c, warp_sums, tid, chunk_total);
-        if (k < n) {
-            // untouched tiles keep (0,0), as the reference's memset leaves them
-            ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-            cursor[(size_t)k * CURSOR_STRIDE] = run;
-        }
-        {
-            const uint32_t bin = k < n ? 255u - min(c >> 3, 255u) : 256u;   // 256: no tile
-            const uint32_t peers = __match_any_sync(0xffffffffu, bin);
-            const int leader = __ffs(peers) - 1;
-            uint32_t pos = 0;
-            if ((tid & 31) == leader && bin < 256u) pos = atomicAdd(&bins[bin], (uint32_t)__popc(peers));
-            pos = __shfl_sync(0xffffffffu, pos, leader);
-            if (bin < 256u)
-                tile_order[pos + __popc(peers & ((1u << (tid & 31)) - 1u))] =
-                    c ? make_uint4((uint32_t)k, run, run + c, 0u) : make_uint4((uint32_t)k, 0u, 0u, 0u);
-        }
-        carry += chunk_total;
+    const uint32_t run = s_carry + local;
+    if (k < n) {
+        // untouched tiles keep (0,0), as the reference's memset leaves them
+        ranges[k] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+        cursor[(size_t)k * CURSOR_STRIDE] = run;
     }
-    if (tid == 0) {
-        num_rendered[0] = carry;
-        num_rendered[1] = ((unsigned long long)carry > capacity) ? 1u : 0u;
+    if (bid == nblocks - 1 && tid == 0) {   // every other block has published, hence fenced its bins / maximum
+        const uint32_t R = s_carry + chunk_total;
+        const uint32_t longest = ld_volatile(scratch + SCAN_LONGEST);
+        num_rendered[0] = R;
+        num_rendered[1] = ((unsigned long long)R > capacity) ? 1u : 0u;
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
-        if (host_R != nullptr) { host_R[1] = longest; __threadfence_system(); host_R[0] = carry; __threadfence_system(); }
+        if (host_R != nullptr) { host_R[1] = longest; __threadfence_system(); host_R[0] = R; __threadfence_system(); }
     }
+}
+
+// Kernel 2: work items in longest-list-first order (counting sort on the length bin), in which the persistent
+// compositing kernels pull their blocks so that the long lists -- each a serial chain through one warp --
+// start first and the short ones fill the tail.
+__global__ void __launch_bounds__(1024)
+tile_order_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict__ scratch, uint4* __restrict__ tile_order)
+{
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t bin_base[256];
+    const int tid = threadIdx.x, lane = tid & 31;
+    {
+        uint32_t dummy;
+        const uint32_t mine = tid < 256 ? scratch[SCAN_BINS + tid] : 0u;
+        const uint32_t ex = block_exclusive_scan_1024(mine, warp_sums, tid, dummy);
+        if (tid < 256) bin_base[tid] = ex;
+    }
+    __syncthreads();
+    const int k = blockIdx.x * 1024 + tid;
+    const uint2 r = k < n ? ranges[k] : make_uint2(0u, 0u);
+    const uint32_t c = r.y - r.x;
+    const uint32_t bin = k < n ? 255u - min(c >> 3, 255u) : 256u;   // 256: no tile
+    const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+    const int leader = __ffs(peers) - 1;
+    uint32_t pos = 0;
+    if (lane == leader && bin < 256u) pos = bin_base[bin] + atomicAdd(scratch + SCAN_BINCUR + bin, (uint32_t)__popc(peers));
+    pos = __shfl_sync(0xffffffffu, pos, leader);
+    if (bin < 256u) tile_order[pos + __popc(peers & ((1u << lane) - 1u))] = make_uint4((uint32_t)k, r.x, r.y, 0u);
 }
 
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity, cudaStream_t s)
 {
-    tile_scan_kernel<<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.tile_order, img.num_rendered,
-                                        host_mapped_R, (unsigned long long)capacity);
-    count_launch();
+    const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
+    uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
+    tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
+                                              host_mapped_R, (unsigned long long)capacity);
+    tile_order_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.ranges, scratch, img.tile_order);
+    count_launch(2);
 }
 
 // -------------------------------------------------------------------- scatter

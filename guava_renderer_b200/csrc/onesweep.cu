@@ -36,38 +36,6 @@ constexpr int OS_WARPS = OS_THREADS / 32;
 constexpr int OS_ITEMS = 8;
 constexpr int OS_PART = OS_THREADS * OS_ITEMS;   // pairs per partition
 constexpr int OS_MAX_PASSES = 8;
-constexpr uint32_t LB_AGG = 1u << 30;            // word = flag (2 bits) | count (30 bits)
-constexpr uint32_t LB_INC = 2u << 30;
-constexpr uint32_t LB_VAL = (1u << 30) - 1u;
-
-__device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p)
-{
-    return *reinterpret_cast<const volatile uint32_t*>(p);
-}
-__device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v)
-{
-    *reinterpret_cast<volatile uint32_t*>(p) = v;
-}
-
-// Sum of the values published by blocks [0, bid): warp-parallel decoupled look-back, 32
-// predecessors per round.  Called by one full warp; every lane returns the sum.
-__device__ __forceinline__ uint32_t lookback_exclusive_warp(const uint32_t* state, int bid, int lane)
-{
-    uint32_t acc = 0;
-    for (int q = bid - 1; q >= 0; q -= 32) {
-        const int idx = q - lane;
-        uint32_t s = LB_INC;   // before block 0: an inclusive prefix of 0
-        if (idx >= 0) {
-            do { s = ld_volatile(state + idx); } while ((s >> 30) == 0u);
-        }
-        const uint32_t inc = __ballot_sync(0xffffffffu, (s >> 30) == 2u);
-        const int first = inc ? __ffs(inc) - 1 : 32;            // nearest predecessor with an inclusive prefix
-        acc += __reduce_add_sync(0xffffffffu, lane <= first ? (s & LB_VAL) : 0u);
-        if (inc) break;
-    }
-    return acc;
-}
-
 // ---------------------------------------------------------------------------------------------
 // Scan + duplicateWithKeys + histograms.  One thread per (view, Gaussian); blocks are ordered by
 // ticket.  point_offsets gets the reference's inclusive sums (GeometryState::point_offsets).
