@@ -53,6 +53,11 @@ class GraphedRenderStep:
         self.color = self.radii = self.invdepth = self.loss = None
         self.grads: Dict[str, torch.Tensor] = {}
         self._flag_dev = None
+        V = int(settings.viewmatrix.shape[0])
+        P = int(means3D.shape[-2])
+        # means2D is a gradient sink whose values no kernel reads (gaussian_render.py:30-33): never filled
+        self._m2_shape = (V, P, 3)
+        self._side = torch.cuda.Stream(device=self.device)
         self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
         self.graph = torch.cuda.CUDAGraph()
 
@@ -86,7 +91,7 @@ class GraphedRenderStep:
             leaf = {k: v.detach().requires_grad_(True) for k, v in i.items()}
         else:
             leaf = i
-        m2 = torch.zeros(V, P, 3, device=self.device, requires_grad=self.training)
+        m2 = torch.empty(self._m2_shape, device=self.device, requires_grad=self.training)
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
                                                            leaf["scaling"], leaf["rotation"], self.settings)
@@ -101,14 +106,21 @@ class GraphedRenderStep:
             loss.backward()
             self.loss = loss.detach()
         else:
-            # loss = <color, dL_dcolor>: one dot-product kernel for the value, and the upstream
-            # gradient handed straight to the rasterizer's backward (no product tensor is materialised)
-            self.loss = torch.dot(color.detach().reshape(-1), self.dL_dcolor.reshape(-1))
+            # loss = <color, dL_dcolor>: one dot-product for the value, and the upstream gradient handed
+            # straight to the rasterizer's backward (no product tensor is materialised).  The value is
+            # not an input of the backward, so its HBM-bound reduction runs on a side stream under the
+            # issue-bound backward compositor; the step's stream rejoins it before the step ends.
+            cur = torch.cuda.current_stream(self.device)
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):
+                self.loss = torch.dot(color.detach().reshape(-1), self.dL_dcolor.reshape(-1))
             color.backward(self.dL_dcolor)
         self.grads = {k: v.grad for k, v in leaf.items()}
         self.viewspace_grad = m2.grad
         order = ("xyz", "scaling", "rotation", "opacity", "features")
         self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
+        if self.loss_fn is None:
+            cur.wait_stream(self._side)
 
     def replay(self):
         self.graph.replay()

@@ -256,11 +256,18 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
                               geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
+        # an output the loss does not use arrives as None instead of a zero-filled tensor (the reference
+        # lets autograd materialise both, two fills per view); a None invdepth gradient takes the
+        # "no invdepth gradients" branch of rasterize_points.cu:176-182, which yields the same result
+        ctx.set_materialize_grads(False)
         return color, radii, invdepths
 
     @staticmethod
     def backward(ctx, grad_out_color, _, grad_out_depth):
         rs = ctx.raster_settings
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(NUM_CHANNELS, int(rs.image_height), int(rs.image_width),
+                                         dtype=torch.float32, device=ctx.saved_tensors[1].device)
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
          geomBuffer, binningBuffer, imgBuffer) = ctx.saved_tensors
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
@@ -348,6 +355,11 @@ def _vstride(t: torch.Tensor, V: int, per_view_numel: int) -> int:
     return per_view_numel
 
 
+# per Gaussian and view: dL_dcolors first (its rows must stay 16-byte aligned for the vector reductions),
+# mean2D, opacity, mean3D, cov3D, scale, rotation, conic, invdepth
+_GRAD_WIDTHS = [32, 3, 1, 3, 6, 3, 4, 4, 1]
+
+
 class _RasterizeGaussiansBatch(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, colors_precomp, opacities, scales, rotations, settings):
@@ -391,6 +403,8 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
             _tls.call = None
             _tls.last_buffers = bufs.bufs      # (geometry, binning, image) of the most recent batched forward
             _check(rc)
+        # unused outputs' upstream gradients arrive as None, not as zero-filled tensors
+        ctx.set_materialize_grads(False)
         ctx.settings = st
         ctx.num_rendered = int(rendered.value)
         ctx.strides = strides
@@ -408,8 +422,12 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         dev = m.device
         with _device_of(m):
             has_inv = grad_invdepth is not None
-            widths = [32, 3, 1, 3, 6, 3, 4, 4] + ([1] if has_inv else [])
+            widths = _GRAD_WIDTHS if has_inv else _GRAD_WIDTHS[:8]
             n = V * P
+            if grad_color is None:
+                grad_color = torch.zeros(V, NUM_CHANNELS, H, W, dtype=torch.float32, device=dev)
+            # one fill for all gradient tensors.  (Issuing it during the forward on a side stream was
+            # measured slower inside the captured step: the fork/join costs more than the 9 us fill.)
             flat = torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
             parts, off = [], 0
             for w in widths:

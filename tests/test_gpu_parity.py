@@ -478,3 +478,49 @@ def test_equal_depth_ties_keep_index_order(sort_mode):
     k = o["keys"]
     same = k[1:] == k[:-1]
     assert same.mean() > 0.5 and np.all(o["point_list"][1:][same] > o["point_list"][:-1][same])
+
+
+def test_invdepth_only_loss_and_repeated_backward(ref):
+    """Upstream gradients autograd leaves undefined (an output the loss does not use) are not
+    materialised; a loss on invdepth alone matches the reference build, and a second backward through
+    the same batched graph (retain_graph) starts from a fresh gradient block."""
+    case = CASES[1]
+    inp = util.inputs_for(**case)
+    g = torch.Generator().manual_seed(3)
+    dL_dinv = torch.randn(1, case["H"], case["W"], generator=g).to(DEV)
+
+    def single(mod):
+        leaf = {k: inp[k].to(DEV).clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+        m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+        rast = mod.GaussianRasterizer_32(raster_settings=util.settings_for(mod, inp, DEV, False))
+        color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                                  opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"],
+                                  cov3D_precomp=None)
+        (invd * dL_dinv).sum().backward()
+        torch.cuda.synchronize()
+        return {k: v.grad.cpu().numpy() for k, v in leaf.items()}
+
+    go, gr = single(ours), single(ref)
+    for k in ("xyz", "opacity", "scaling", "rotation"):
+        assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+    assert not go["features"].any() and not gr["features"].any()
+
+    # batched entry: the same loss, then the same backward twice
+    leaf = {k: inp[k].to(DEV).clone()[None].requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+    m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+    st = grb.BatchRasterizationSettings(case["H"], case["W"], torch.tensor([[inp["tanfovx"], inp["tanfovy"]]], device=DEV),
+                                        inp["bg"].to(DEV)[None], 1.0, inp["viewmatrix"].to(DEV)[None],
+                                        inp["projmatrix"].to(DEV)[None])
+    color, radii, invd = grb.rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
+                                                       leaf["scaling"], leaf["rotation"], st)
+    loss = (invd[0] * dL_dinv).sum()
+    loss.backward(retain_graph=True)
+    first = {k: v.grad.clone() for k, v in leaf.items()}
+    for k in ("xyz", "opacity", "scaling", "rotation"):
+        assert util.rel_err(first[k][0].cpu().numpy(), gr[k]) <= 1e-4, k
+    for v in leaf.values():
+        v.grad = None
+    loss.backward()
+    torch.cuda.synchronize()
+    for k in ("xyz", "opacity", "scaling", "rotation"):
+        assert util.rel_err(leaf[k].grad.cpu().numpy(), first[k].cpu().numpy()) <= 1e-4, k
