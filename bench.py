@@ -244,6 +244,11 @@ def run_own(args, rank, world, device):
         for g in g_e2e:
             g.done_ev, g.fin_ev = torch.cuda.Event(), torch.cuda.Event()
 
+    trace = {}
+
+    def trace_point(i):      # --trace-e2e: device timestamps of one step's phases (debug aid, not a bench number)
+        return trace.setdefault(i, {k: torch.cuda.Event(enable_timing=True) for k in ("step0", "step1", "reduced", "result")})
+
     def step_e2e(i, last):
         b = stage[i % NSTAGE]
         compute = torch.cuda.current_stream(device)
@@ -251,18 +256,27 @@ def run_own(args, rank, world, device):
         if graphed:
             g = g_e2e[i % NSTAGE]
             compute.wait_event(g.fin_ev)          # the result of step i-NSTAGE has been read out of g.packed
+            tr = trace_point(i) if args.trace_e2e else None
+            if tr:
+                tr["step0"].record(compute)
             g.replay()
             g.done_ev.record(compute)
+            if tr:
+                tr["step1"].record(compute)
 
-            def finish(h, g=g):
+            def finish(h, g=g, tr=tr):
                 with torch.cuda.stream(result_stream):
                     if h is not None:
                         h.wait()
                     else:
                         result_stream.wait_event(g.done_ev)
+                    if tr:
+                        tr["reduced"].record(result_stream)
                     res = torch.stack([g.loss, torch.linalg.vector_norm(g.packed.view(-1), 1)])
                     result_host.copy_(res, non_blocking=True)
                     g.fin_ev.record(result_stream)
+                    if tr:
+                        tr["result"].record(result_stream)
             pending.append((sharding.allreduce_gradients(g.packed, async_op=True), finish))
             join(1)
             return None
@@ -336,6 +350,17 @@ def run_own(args, rank, world, device):
     clk = clocks.stop()
     copy_stream.synchronize()
     ms_h2d_loaded = sum(a.elapsed_time(b) for a, b in copy_times) / max(len(copy_times), 1)
+    if args.trace_e2e:
+        torch.cuda.synchronize(device)
+        rows = []
+        first = args.warmup
+        for j, (c0_, c1_) in enumerate(copy_times):
+            rows.append({"copy_issue": j, "t0": round(e2.elapsed_time(c0_), 4), "t1": round(e2.elapsed_time(c1_), 4)})
+        for i in sorted(trace):
+            if i >= first:
+                rows.append({"step": i - first, **{k: round(e2.elapsed_time(ev), 4) for k, ev in trace[i].items()}})
+        with open(f"{args.trace_e2e}.rank{rank}.json", "w") as f:
+            json.dump(rows, f, indent=0)
 
     # the step's host->device copy timed alone (what `e2e` would cost if the kernels were free)
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -565,6 +590,7 @@ def main():
     ap.add_argument("--views-per-gpu", type=int, default=VIEWS_PER_GPU)
     ap.add_argument("--view-sets", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--trace-e2e", default="", help="write device timestamps of the e2e steps' phases to PATH.rank<r>.json")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to its GPU's NUMA node")
     ap.add_argument("--eager", action="store_true", help="enqueue every step op by op instead of replaying CUDA graphs")
     args = ap.parse_args()
@@ -589,6 +615,7 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        sharding.limit_collective_footprint()
         dist.init_process_group("nccl", device_id=device)
     r = run_own(args, rank, world, device)
     if rank == 0:
