@@ -4,7 +4,7 @@ sys.path.insert(0, '.')
 from tests import util
 import guava_renderer_b200 as grb
 DEV = 'cuda:0'
-for name, (P, H, W, V, sm) in dict(C3=(100000, 512, 512, 2, 1.0), C4=(300000, 1024, 1024, 2, 1.0), C5=(1000000, 1080, 1920, 1, 4.0)).items():
+for name, (P, H, W, V, sm) in dict(C3=(100000, 512, 512, 2, 1.0), C3b=(202000, 512, 512, 2, 1.0), C4=(300000, 1024, 1024, 2, 1.0), C5=(1000000, 1080, 1920, 1, 4.0)).items():
     views = [util.inputs_for(P, H, W, 4000 + v, view=v, num_views=4, scale_mult=sm) for v in range(V)]
     st = grb.BatchRasterizationSettings(H, W, torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV),
                                         torch.zeros(V, 32, device=DEV), 1.0, torch.stack([x["viewmatrix"] for x in views]).to(DEV),
