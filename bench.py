@@ -454,13 +454,16 @@ def roofline_object(stages, s, tanfov, bg, dL, P, H, W, V, device):
     dur_s = per_launch[dom] * 1e-3
     achieved = alg[dom] / dur_s / 1e9 if dur_s > 0 else 0.0
     # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture of this command
-    traffic, tpath = None, os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    traffic, issue, tpath = None, None, os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.isfile(tpath):
         t = json.load(open(tpath)).get(dom)
         if t and t.get("P") == P and t.get("views") == V and t.get("H") == H and t.get("W") == W:
             traffic = int(t["dram_bytes_read"] + t["dram_bytes_write"])
+            if "issue_active_pct" in t:   # what actually bounds the kernel (same ncu capture): issue slots, not HBM
+                issue = {"issue_slots_busy_pct": t["issue_active_pct"], "ipc": t["ipc"], "peak_ipc": 4.0,
+                         "source": "profiles/" + t["source"]}
     return {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+            "frac": round(achieved / peak, 4), "traffic": traffic, "issue": issue, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": int(alg[dom]), "launch_ms": round(per_launch[dom], 4),
             "units": {"R": Rtot, "Rc": Rc, "pairs": pairs, "views": V, "P": P},
             "per_kernel_ms": {k: round(v, 4) for k, v in per_launch.items()},

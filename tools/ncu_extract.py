@@ -73,12 +73,15 @@ def main():
             if pat in k:
                 rd = num(r[hdr.index("dram__bytes_read.sum")]) * scale("dram__bytes_read.sum")
                 wr = num(r[hdr.index("dram__bytes_write.sum")]) * scale("dram__bytes_write.sum")
-                a = acc.setdefault(st, [0.0, 0.0, 0])
+                a = acc.setdefault(st, [0.0, 0.0, 0, 0.0, 0.0])
                 a[0] += rd
                 a[1] += wr
                 a[2] += 1
+                a[3] += num(r[hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")])
+                a[4] += num(r[hdr.index("sm__inst_executed.avg.per_cycle_active")])
                 break
     traffic = {st: {"dram_bytes_read": int(a[0] / a[2]), "dram_bytes_write": int(a[1] / a[2]), "launches_averaged": a[2],
+                    "issue_active_pct": round(a[3] / a[2], 2), "ipc": round(a[4] / a[2], 3),
                     "P": shape[0], "views": shape[1], "H": shape[2], "W": shape[3], "source": os.path.basename(out)}
                for st, a in acc.items()}
     tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
