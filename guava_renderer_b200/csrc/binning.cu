@@ -19,6 +19,8 @@
 // established per tile inside shared memory.  HBM traffic per instance drops
 // from 152 B (1 histogram + 6 onesweep passes over 12-byte pairs) to 8 B
 // written by the scatter + 8 B read and 4 B written by the tile sort.
+#include <atomic>
+
 #include "internal.cuh"
 
 namespace guava {
@@ -399,11 +401,14 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
     (void)global_scratch;
     const int total_tiles = in.V * in.tiles;
     if (total_tiles == 0) return;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // function attributes are per device: one flag per device ordinal (setting it twice is harmless)
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(SORT_LARGE * sizeof(uint64_t)));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
     tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.ranges, img.num_rendered, b.keys_unsorted, b.point_list,
                                                        b.keys_sorted, in.tiles);
