@@ -159,3 +159,13 @@ def test_synthetic_inputs_are_deterministic_and_well_formed():
     # the cloud centre projects to the image centre with depth 22
     p = torch.tensor([0.0, 0.0, 0.0, 1.0]) @ cam["viewmatrix"]
     assert abs(float(p[2]) - 22.0) < 1e-3
+
+
+def test_collective_footprint_cap_keeps_an_explicit_setting(monkeypatch):
+    from guava_renderer_b200 import sharding
+    monkeypatch.delenv("NCCL_MAX_CTAS", raising=False)
+    sharding.limit_collective_footprint()
+    assert os.environ["NCCL_MAX_CTAS"] == "4"
+    monkeypatch.setenv("NCCL_MAX_CTAS", "16")
+    sharding.limit_collective_footprint()
+    assert os.environ["NCCL_MAX_CTAS"] == "16"
