@@ -298,29 +298,28 @@ __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__
                     }
                 }
             } else if (j < 32 * E) {
+                // one 64-bit compare per element: keys are distinct (the Gaussian index is part of the
+                // key), and between two equal +inf pads either choice stores the same value
                 const int tj = j / E;   // partner thread distance, within the warp
-                const bool lower = (tid & tj) == 0;
+                // k >= 2j >= 2E here, so the direction bit (index & k) is the same for all E keys of a thread
+                const bool keep_max = ((tid & tj) == 0) != (((tid * E) & k) == 0);
 #pragma unroll
                 for (int e = 0; e < E; e++) {
-                    const bool asc = (((tid * E + e) & k) == 0);
                     const uint64_t other = __shfl_xor_sync(0xffffffffu, key[e], tj);
-                    const bool keep_min = lower == asc;
-                    const bool take_other = keep_min ? (other < key[e]) : (other > key[e]);
+                    const bool take_other = (other < key[e]) != keep_max;
                     key[e] = take_other ? other : key[e];
                 }
             } else {
                 const int tj = j / E;
-                const bool lower = (tid & tj) == 0;
+                const bool keep_max = ((tid & tj) == 0) != (((tid * E) & k) == 0);
                 __syncthreads();
 #pragma unroll
                 for (int e = 0; e < E; e++) skeys[e * 256 + tid] = key[e];
                 __syncthreads();
 #pragma unroll
                 for (int e = 0; e < E; e++) {
-                    const bool asc = (((tid * E + e) & k) == 0);
                     const uint64_t other = skeys[e * 256 + (tid ^ tj)];
-                    const bool keep_min = lower == asc;
-                    const bool take_other = keep_min ? (other < key[e]) : (other > key[e]);
+                    const bool take_other = (other < key[e]) != keep_max;
                     key[e] = take_other ? other : key[e];
                 }
             }
@@ -337,17 +336,21 @@ __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__
 }
 
 __global__ void __launch_bounds__(256)
-tile_sort_small_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
+tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __restrict__ num_rendered,
                        const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
                        uint64_t* __restrict__ keys_sorted, int tiles_per_view)
 {
     __shared__ uint64_t skeys[2048];
     if (num_rendered[1]) return;
-    const uint2 r = ranges[blockIdx.x];
+    // blocks take the tiles longest list first (the compositors' work order): all non-empty buckets are
+    // resident in one wave at the GUAVA shapes, and this deals the 2048-key sorts evenly over the SMs
+    // instead of leaving them clustered where the image centre falls in row-major tile order
+    const uint4 item = tile_order[blockIdx.x];
+    const uint2 r = make_uint2(item.y, item.z);
     const uint32_t n = r.y - r.x;
     if (n == 0 || n > 2048) return;   // block-uniform; longer buckets: tile_sort_large_kernel
     const int tid = threadIdx.x;
-    const uint64_t tile_hi = (uint64_t)(blockIdx.x % tiles_per_view) << 32;
+    const uint64_t tile_hi = (uint64_t)(item.x % (uint32_t)tiles_per_view) << 32;
     uint64_t* ks = keys_sorted != nullptr ? keys_sorted + r.x : nullptr;
     if (n <= 256) tile_sort_registers<1>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
     else if (n <= 512) tile_sort_registers<2>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
@@ -410,7 +413,7 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
-    tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.ranges, img.num_rendered, b.keys_unsorted, b.point_list,
+    tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted, b.point_list,
                                                        b.keys_sorted, in.tiles);
     const int big_grid = total_tiles < 148 ? total_tiles : 148;
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
