@@ -524,3 +524,20 @@ def test_invdepth_only_loss_and_repeated_backward(ref):
     torch.cuda.synchronize()
     for k in ("xyz", "opacity", "scaling", "rotation"):
         assert util.rel_err(leaf[k].grad.cpu().numpy(), first[k].cpu().numpy()) <= 1e-4, k
+
+
+@pytest.mark.parametrize("V,P", [(1, 1), (2, 4099), (3, 1001), (4, 257), (5, 33), (8, 130)])
+def test_pack_view_gradients_all_batch_sizes(V, P):
+    """Every view-count branch of the packing kernel (templated 1/2/4/8 and the runtime loop), row counts
+    that do not fill the last warp's four rows: equal to the view-ordered sum, bit for bit."""
+    from guava_renderer_b200 import sharding
+    g = torch.Generator().manual_seed(V * 1000 + P)
+    grads = [torch.randn(V, P, w, generator=g).to(DEV) for w in sharding.GRAD_WIDTHS]
+    packed = sharding.pack_gradients(grads)
+    cols = []
+    for x in grads:
+        acc = torch.zeros_like(x[0])
+        for v in range(V):
+            acc = acc + x[v]
+        cols.append(acc)
+    assert torch.equal(packed, torch.cat(cols, dim=1))
