@@ -120,6 +120,19 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
     const float* __restrict__ Pm = in.projmatrix + 16 * v;
     const float* __restrict__ mp = in.means3D + (size_t)v * in.means3D_vs + 3 * (size_t)i;
     const float mx = mp[0], my = mp[1], mz = mp[2];
+    // Every input of this Gaussian is requested before the first early exit: the grid is a single wave, so
+    // each dependent round trip to HBM behind a branch (scale/rotation after the frustum test, opacity after
+    // the rect test) lengthened the whole kernel by one memory latency.  Culled Gaussians read 32 bytes in vain.
+    float sr[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (in.cov3D_precomp == nullptr) {
+        const float* __restrict__ sp = in.scales + (size_t)v * in.scales_vs + 3 * (size_t)i;
+        const float* __restrict__ qp = in.rotations + (size_t)v * in.rotations_vs + 4 * (size_t)i;
+        sr[0] = sp[0]; sr[1] = sp[1]; sr[2] = sp[2];
+        sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
+    }
+    const float opacity = in.opacities[(size_t)v * in.opacities_vs + i];
+    float tan_fovx = in.tan_fovx, tan_fovy = in.tan_fovy;
+    if (in.tan_fov_dev != nullptr) { tan_fovx = in.tan_fov_dev[2 * v]; tan_fovy = in.tan_fov_dev[2 * v + 1]; }
 
     // in_frustum (auxiliary.h:151-176): only the near-plane test is live
     const float depth = xform_row(Vm, 2, mx, my, mz);
@@ -142,12 +155,9 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
 #pragma unroll
         for (int k = 0; k < 6; k++) c3[k] = cp[k];
     } else {
-        cov3d_from_scale_rot(in.scales + (size_t)v * in.scales_vs + 3 * (size_t)i, in.scale_modifier,
-                             in.rotations + (size_t)v * in.rotations_vs + 4 * (size_t)i, c3);
+        cov3d_from_scale_rot(sr, in.scale_modifier, sr + 3, c3);
     }
 
-    float tan_fovx = in.tan_fovx, tan_fovy = in.tan_fovy;
-    if (in.tan_fov_dev != nullptr) { tan_fovx = in.tan_fov_dev[2 * v]; tan_fovy = in.tan_fov_dev[2 * v + 1]; }
     // rasterizer_impl.cu:223-224 (host float arithmetic in the reference)
     const float focal_y = __fdiv_rn(__int2float_rn(in.H), fmul(2.0f, tan_fovy));
     const float focal_x = __fdiv_rn(__int2float_rn(in.W), fmul(2.0f, tan_fovx));
@@ -176,7 +186,6 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
     const uint32_t touched = (maxx - minx) * (maxy - miny);
     if (touched == 0) return;
 
-    const float opacity = in.opacities[(size_t)v * in.opacities_vs + i];
     SplatRec rec;
     rec.x = px; rec.y = py; rec.cx = conx; rec.cy = cony; rec.cz = conz;
     rec.op = fmul(h_scale, opacity);
@@ -241,14 +250,28 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
 {
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (gid >= (size_t)in.V * in.P) return;
-    if (!(radii[gid] > 0)) return;
     // Per-Gaussian sums written by the backward compositing kernel: moments of s = dL/dG * G about
     // the pixel offset d = mean2D - pixel, (sum s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2), then
-    // sum G*dL/dalpha and sum w*dL/dinvdepth.  backward.cu:612-635 in terms of them:
+    // sum G*dL/dalpha and sum w*dL/dinvdepth.  backward.cu:612-635 in terms of them.
+    // All of this Gaussian's inputs are requested together with its radius, before the visibility exit
+    // (single-wave grid: a second round trip to HBM behind the branch is paid by the whole kernel).
+    const int rad = radii[gid];
     const float4 mo0 = reinterpret_cast<const float4*>(grad_geo)[2 * gid];
     const float4 mo1 = reinterpret_cast<const float4*>(grad_geo)[2 * gid + 1];
     const float4 rc0 = reinterpret_cast<const float4*>(recs)[2 * gid];       // x, y, conic.x, conic.y
     const float4 rc1 = reinterpret_cast<const float4*>(recs)[2 * gid + 1];   // conic.z, ...
+    const int v = (int)(gid / in.P);
+    const int i = (int)(gid - (size_t)v * in.P);
+    const float* __restrict__ mp = in.means3D + (size_t)v * in.means3D_vs + 3 * (size_t)i;
+    const float mx = mp[0], my = mp[1], mz = mp[2];
+    float sr[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    if (in.cov3D_precomp == nullptr) {
+        const float* __restrict__ sp = in.scales + (size_t)v * in.scales_vs + 3 * (size_t)i;
+        const float* __restrict__ qp = in.rotations + (size_t)v * in.rotations_vs + 4 * (size_t)i;
+        sr[0] = sp[0]; sr[1] = sp[1]; sr[2] = sp[2];
+        sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
+    }
+    if (!(rad > 0)) return;
     float4 gg0, gg1;
     gg0.x = -(rc0.z * mo0.x + rc0.w * mo0.y) * (0.5f * in.W);   // dL/dmean2D.x (NDC units, :626)
     gg0.y = -(rc1.x * mo0.y + rc0.w * mo0.x) * (0.5f * in.H);   // dL/dmean2D.y
@@ -267,27 +290,19 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
         dL_dconic[4 * gid + 3] = gg1.x;
     }
     if (has_invdepth && dL_dinvdepth != nullptr) dL_dinvdepth[gid] = gg1.z;
-    const int v = (int)(gid / in.P);
-    const int i = (int)(gid - (size_t)v * in.P);
     const float* __restrict__ V = in.viewmatrix + 16 * v;
     const float* __restrict__ proj = in.projmatrix + 16 * v;
-    const float* __restrict__ mp = in.means3D + (size_t)v * in.means3D_vs + 3 * (size_t)i;
-    const float mx = mp[0], my = mp[1], mz = mp[2];
 
     float tan_fovx = in.tan_fovx, tan_fovy = in.tan_fovy;
     if (in.tan_fov_dev != nullptr) { tan_fovx = in.tan_fov_dev[2 * v]; tan_fovy = in.tan_fov_dev[2 * v + 1]; }
     const float h_y = in.H / (2.0f * tan_fovy), h_x = in.W / (2.0f * tan_fovx);
 
     float c3[6];
-    const float* sc = nullptr;
-    const float* q = nullptr;
     if (in.cov3D_precomp != nullptr) {
 #pragma unroll
         for (int k = 0; k < 6; k++) c3[k] = in.cov3D_precomp[6 * gid + k];
     } else {
-        sc = in.scales + (size_t)v * in.scales_vs + 3 * (size_t)i;
-        q = in.rotations + (size_t)v * in.rotations_vs + 4 * (size_t)i;
-        cov3d_from_scale_rot(sc, in.scale_modifier, q, c3);
+        cov3d_from_scale_rot(sr, in.scale_modifier, sr + 3, c3);
     }
 
     const float dLc_x = gg0.z, dLc_y = gg0.w, dLc_z = gg1.x;
@@ -395,13 +410,13 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
     gmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
     dL_dmean3D[3 * gid] = gmx; dL_dmean3D[3 * gid + 1] = gmy; dL_dmean3D[3 * gid + 2] = gmz;
 
-    if (sc != nullptr) {
-        const float r = q[0], x = q[1], y = q[2], z = q[3];
+    if (in.cov3D_precomp == nullptr) {
+        const float r = sr[3], x = sr[4], y = sr[5], z = sr[6];
         const float R[3][3] = {
             {1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
             {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
             {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
-        const float s[3] = {in.scale_modifier * sc[0], in.scale_modifier * sc[1], in.scale_modifier * sc[2]};
+        const float s[3] = {in.scale_modifier * sr[0], in.scale_modifier * sr[1], in.scale_modifier * sr[2]};
         float M[3][3];
 #pragma unroll
         for (int c = 0; c < 3; c++)
