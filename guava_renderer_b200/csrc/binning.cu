@@ -113,7 +113,9 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
-        if (host_R != nullptr) { host_R[1] = longest; __threadfence_system(); host_R[0] = R; __threadfence_system(); }
+        // one aligned 8-byte store: (R, longest) reach the pinned host words together, no system fences
+        if (host_R != nullptr)
+            *reinterpret_cast<volatile unsigned long long*>(host_R) = (unsigned long long)R | ((unsigned long long)longest << 32);
     }
 }
 
