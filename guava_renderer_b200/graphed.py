@@ -75,15 +75,14 @@ class GraphedRenderStep:
         try:
             n0 = _lib.launch_count()
             with torch.cuda.graph(self.graph):
-                self._step()
-                self._flag_host.copy_(self._flag_dev, non_blocking=True)
+                self._step(capturing=True)
             # kernels of libguava_rasterizer_b200.so that one replay launches
             self.launches_per_replay = _lib.launch_count() - n0
         finally:
             _lib.set_option("async_forward", prev)
 
     # one step, eager or under capture
-    def _step(self):
+    def _step(self, capturing: bool = False):
         i = self.inputs
         V = int(self.settings.viewmatrix.shape[0])
         P = int(i["xyz"].shape[-2])
@@ -99,7 +98,12 @@ class GraphedRenderStep:
         L = _lib.buffer_layout(V, P, int(self.settings.image_width), int(self.settings.image_height), 0)
         self._flag_dev = bufs[2][L.num_rendered + 4:L.num_rendered + 8].view(torch.int32)
         self.color, self.radii, self.invdepth = color, radii, invd
+        # the overflow flag is final once the forward's tile scan has run; its 4-byte copy to pinned host
+        # memory is a PCIe round trip, so in training steps it rides on the side branch next to the loss
+        flag_copied = False
         if not self.training:
+            if capturing:
+                self._flag_host.copy_(self._flag_dev, non_blocking=True)
             return
         if self.loss_fn is not None:
             loss = self.loss_fn(color, invd)
@@ -113,6 +117,9 @@ class GraphedRenderStep:
             cur = torch.cuda.current_stream(self.device)
             self._side.wait_stream(cur)
             with torch.cuda.stream(self._side):
+                if capturing:
+                    self._flag_host.copy_(self._flag_dev, non_blocking=True)
+                    flag_copied = True
                 self.loss = torch.dot(color.detach().reshape(-1), self.dL_dcolor.reshape(-1))
             color.backward(self.dL_dcolor)
         self.grads = {k: v.grad for k, v in leaf.items()}
@@ -121,6 +128,8 @@ class GraphedRenderStep:
         self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
         if self.loss_fn is None:
             cur.wait_stream(self._side)
+        if capturing and not flag_copied:
+            self._flag_host.copy_(self._flag_dev, non_blocking=True)
 
     def replay(self):
         self.graph.replay()
