@@ -23,6 +23,8 @@ EXPORTS = (
     "guava_rasterizer_backward_batch",
     "guava_pack_view_gradients",
     "guava_rasterizer_set_refiner_output",
+    "guava_rasterizer_set_status_words",
+    "guava_image_dot",
     "guava_deform_gaussians_forward",
     "guava_deform_gaussians_backward",
     "guava_buffer_layout",
@@ -102,6 +104,10 @@ def load() -> ctypes.CDLL:
     lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]
     lib.guava_rasterizer_set_refiner_output.restype = c_int
     lib.guava_rasterizer_set_refiner_output.argtypes = [P]
+    lib.guava_image_dot.restype = c_int
+    lib.guava_image_dot.argtypes = [P, P, c_size_t, P, P]
+    lib.guava_rasterizer_set_status_words.restype = c_int
+    lib.guava_rasterizer_set_status_words.argtypes = [P]
     lib.guava_deform_gaussians_forward.restype = c_int
     lib.guava_deform_gaussians_forward.argtypes = [c_int] * 4 + [P] * 21
     lib.guava_deform_gaussians_backward.restype = c_int

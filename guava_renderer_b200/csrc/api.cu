@@ -36,6 +36,7 @@ static std::atomic<long long> g_opt_scalar_red{0};
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
 static thread_local void* t_refiner_output = nullptr;   // consumed by the next forward call of this thread
+static thread_local uint32_t* t_status_host = nullptr;  // caller's pinned status words, consumed likewise
 
 static int fail(int code, const std::string& msg)
 {
@@ -281,6 +282,59 @@ pack_view_gradients_kernel(int V, int P, const float* __restrict__ g_xyz, const 
     }
 }
 
+// <a, b> with a deliberately small footprint: `IMAGE_DOT_CTAS` CTAs stream both arrays while a
+// persistent compositor owns the rest of the machine (a full-grid library reduction launched next to the
+// backward compositor delayed its first wave; launched after it, it was exposed at the end of the step).
+// Deterministic: per-thread partial sums over a fixed stride, tree reduction per CTA, and the CTA that
+// takes the last ticket adds the per-CTA partials in index order.
+constexpr int IMAGE_DOT_CTAS = 16;
+__global__ void __launch_bounds__(512)
+image_dot_kernel(const float* __restrict__ a, const float* __restrict__ b, size_t n, float* __restrict__ out)
+{
+    __shared__ float warp_part[16];
+    __shared__ bool last;
+    const size_t n4 = n >> 2;
+    const float4* __restrict__ a4 = reinterpret_cast<const float4*>(a);
+    const float4* __restrict__ b4 = reinterpret_cast<const float4*>(b);
+    const size_t stride = (size_t)gridDim.x * 512;
+    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    size_t i = (size_t)blockIdx.x * 512 + threadIdx.x;
+    for (; i + 3 * stride < n4; i += 4 * stride) {
+        float4 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { x[u] = __ldcs(a4 + i + u * stride); y[u] = __ldcs(b4 + i + u * stride); }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            acc[u] += x[u].x * y[u].x + x[u].y * y[u].y + x[u].z * y[u].z + x[u].w * y[u].w;
+    }
+    for (; i < n4; i += stride) {
+        const float4 x = __ldcs(a4 + i), y = __ldcs(b4 + i);
+        acc[0] += x.x * y.x + x.y * y.y + x.z * y.z + x.w * y.w;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) acc[1] += a[(n4 << 2) + threadIdx.x] * b[(n4 << 2) + threadIdx.x];
+    float v = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_part[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < 16; w++) t += warp_part[w];
+        out[1 + blockIdx.x] = t;
+        __threadfence();
+        const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(out) + 63, 1u);
+        last = ticket == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        float t = 0.0f;
+        for (unsigned c = 0; c < gridDim.x; c++) t += reinterpret_cast<volatile float*>(out)[1 + c];
+        out[0] = t;
+        reinterpret_cast<unsigned*>(out)[63] = 0u;   // ready for the next call
+    }
+}
+
 // ------------------------------------------------------------------- forward
 static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
                         guava_alloc_fn binningBuffer, void* binning_user,
@@ -291,6 +345,10 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     if (num_rendered) *num_rendered = 0;
     in.aux_nhwc_bf16 = t_refiner_output;
     t_refiner_output = nullptr;
+    uint32_t* const status_host = t_status_host;
+    t_status_host = nullptr;
+    if (((uintptr_t)status_host & 7) != 0)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");
     if (((uintptr_t)in.aux_nhwc_bf16 & 15) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "refiner output must be 16-byte aligned");
     if (in.V < 0 || in.P < 0 || in.W <= 0 || in.H <= 0)
@@ -344,9 +402,24 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     im.tile_order = (uint4*)(img + L.tile_order);
     im.num_rendered = (uint32_t*)(img + L.num_rendered);
 
-    const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
-    volatile uint32_t* hslot = g_slots.host + 2 * slot;   // [0] = R, [1] = longest tile list
-    *hslot = 0xFFFFFFFFu;
+    // [0] = R, [1] = longest tile list | overflow << 31: the library's rotating pinned slots, or the
+    // caller's own two words (guava_rasterizer_set_status_words)
+    volatile uint32_t* hslot;
+    uint32_t* hslot_dev;
+    if (status_host != nullptr) {
+        void* d = nullptr;
+        if (cudaHostGetDevicePointer(&d, status_host, 0) != cudaSuccess || d == nullptr) {
+            cudaGetLastError();
+            return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be pinned, device-mapped host memory");
+        }
+        hslot = status_host;
+        hslot_dev = (uint32_t*)d;
+    } else {
+        const unsigned slot = g_slots.next.fetch_add(1) % HostSlots::N;
+        hslot = g_slots.host + 2 * slot;
+        hslot_dev = g_slots.dev + 2 * slot;
+    }
+    if (!async_fwd || status_host == nullptr) *hslot = 0xFFFFFFFFu;   // a captured step's words are only written by its replays
 
     const int total_tiles = in.V * in.tiles;
     StageTimer timer(stream);
@@ -357,7 +430,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     timer.end();
     GUAVA_STAGE("preprocess", debug);
     timer.begin(1);
-    launch_tile_scan(total_tiles, im, g_slots.dev + 2 * slot, exact ? (size_t)-1 : cap, stream);
+    launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap, stream);
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 
@@ -434,7 +507,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
                                                                            im.num_rendered, (unsigned long long)cap);
         count_launch();
     }
-    if (!async_fwd) capacity_record(n, in.W, in.H, R, hslot[1]);
+    if (!async_fwd) capacity_record(n, in.W, in.H, R, hslot[1] & 0x7FFFFFFFu);
     if (num_rendered) *num_rendered = async_fwd ? -1 : (int)R;
     return GUAVA_OK;
 }
@@ -648,6 +721,24 @@ int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const floa
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
+    return GUAVA_OK;
+}
+
+int guava_image_dot(const float* a, const float* b, size_t n, float* out64, void* stream)
+{
+    if (!a || !b || !out64) return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (((uintptr_t)a & 15) || ((uintptr_t)b & 15)) return fail(GUAVA_ERR_INVALID_ARGUMENT, "inputs must be 16-byte aligned");
+    static const int ctas = [] { const char* e = getenv("GUAVA_DOT_CTAS"); int c = e ? atoi(e) : IMAGE_DOT_CTAS; return c < 1 ? 1 : (c > 62 ? 62 : c); }();   // tuning knob
+    image_dot_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(a, b, n, out64);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
+    return GUAVA_OK;
+}
+
+int guava_rasterizer_set_status_words(void* pinned_host_u32x2)
+{
+    t_status_host = (uint32_t*)pinned_host_u32x2;
     return GUAVA_OK;
 }
 

@@ -115,7 +115,8 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
         // one aligned 8-byte store: (R, longest) reach the pinned host words together, no system fences
         if (host_R != nullptr)
-            *reinterpret_cast<volatile unsigned long long*>(host_R) = (unsigned long long)R | ((unsigned long long)longest << 32);
+            *reinterpret_cast<volatile unsigned long long*>(host_R) =
+                (unsigned long long)R | ((unsigned long long)(longest | (((unsigned long long)R > capacity) ? 0x80000000u : 0u)) << 32);
     }
 }
 

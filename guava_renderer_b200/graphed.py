@@ -9,8 +9,10 @@ cost.  Inputs are STATIC device tensors (the graph reads their storage on every 
 with `copy_`), exactly as for torch.cuda.graphs whole-network capture.
 
 The binning buffer of a captured forward has a fixed capacity (learnt from eager warm-up runs on the
-same inputs, +25 %).  Every replay copies the library's overflow flag to pinned host memory;
-`check()` raises if a replay ever needed more, after which the step must be re-captured.
+same inputs, +25 %).  Every replay's tile scan stores (num_rendered, longest list | overflow << 31)
+straight into two pinned host words the step owns (no copy node: as the graph's last node a 4-byte
+device->host copy cost 22 us per replay); `check()` raises if the latest replay needed more capacity,
+after which the step must be re-captured.
 """
 from __future__ import annotations
 
@@ -22,6 +24,22 @@ from . import _lib
 from . import rasterizer as _rz
 from .rasterizer import BatchRasterizationSettings, rasterize_gaussians_batch
 from .sharding import pack_gradients
+
+
+def image_dot(a: torch.Tensor, b: torch.Tensor, out64: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """<a, b> as a 0-dim tensor, computed by the library's 16-CTA reduction (`guava_image_dot`) on the
+    current stream.  `out64`: 64 zero-initialised floats to reuse across calls (CUDA-graph friendly)."""
+    import ctypes
+    if not (a.is_cuda and b.is_cuda) or a.dtype != torch.float32 or b.dtype != torch.float32 or a.numel() != b.numel():
+        raise ValueError("image_dot needs two float32 CUDA tensors of equal size")
+    a, b = a.contiguous(), b.contiguous()
+    if out64 is None:
+        out64 = torch.zeros(64, device=a.device)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(a.device).cuda_stream)
+    rc = _lib.load().guava_image_dot(a.data_ptr(), b.data_ptr(), a.numel(), out64.data_ptr(), stream)
+    if rc != _lib.GUAVA_OK:
+        raise RuntimeError(_lib.last_error())
+    return out64[0]
 
 
 class GraphedRenderStep:
@@ -52,13 +70,15 @@ class GraphedRenderStep:
         self.packed = packed_out
         self.color = self.radii = self.invdepth = self.loss = None
         self.grads: Dict[str, torch.Tensor] = {}
-        self._flag_dev = None
+        # (num_rendered, longest list | overflow << 31) of the latest replay: the tile scan stores them
+        # straight into these pinned words (guava_rasterizer_set_status_words) -- no copy node in the graph
+        self._status = torch.zeros(2, dtype=torch.int32).pin_memory()
         V = int(settings.viewmatrix.shape[0])
         P = int(means3D.shape[-2])
         # means2D is a gradient sink whose values no kernel reads (gaussian_render.py:30-33): never filled
         self._m2_shape = (V, P, 3)
         self._side = torch.cuda.Stream(device=self.device)
-        self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._loss_buf = torch.zeros(64, device=self.device)      # guava_image_dot: [0] value, rest scratch
         self.graph = torch.cuda.CUDAGraph()
 
         # eager warm-up on a side stream: loads kernels, sets function attributes, learns the capacity
@@ -75,14 +95,14 @@ class GraphedRenderStep:
         try:
             n0 = _lib.launch_count()
             with torch.cuda.graph(self.graph):
-                self._step(capturing=True)
+                self._step()
             # kernels of libguava_rasterizer_b200.so that one replay launches
             self.launches_per_replay = _lib.launch_count() - n0
         finally:
             _lib.set_option("async_forward", prev)
 
     # one step, eager or under capture
-    def _step(self, capturing: bool = False):
+    def _step(self):
         i = self.inputs
         V = int(self.settings.viewmatrix.shape[0])
         P = int(i["xyz"].shape[-2])
@@ -91,19 +111,12 @@ class GraphedRenderStep:
         else:
             leaf = i
         m2 = torch.empty(self._m2_shape, device=self.device, requires_grad=self.training)
+        _rz._tls.status_words = self._status
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
                                                            leaf["scaling"], leaf["rotation"], self.settings)
-        bufs = _rz._tls.last_buffers
-        L = _lib.buffer_layout(V, P, int(self.settings.image_width), int(self.settings.image_height), 0)
-        self._flag_dev = bufs[2][L.num_rendered + 4:L.num_rendered + 8].view(torch.int32)
         self.color, self.radii, self.invdepth = color, radii, invd
-        # the overflow flag is final once the forward's tile scan has run; its 4-byte copy to pinned host
-        # memory is a PCIe round trip, so in training steps it rides on the side branch next to the loss
-        flag_copied = False
         if not self.training:
-            if capturing:
-                self._flag_host.copy_(self._flag_dev, non_blocking=True)
             return
         if self.loss_fn is not None:
             loss = self.loss_fn(color, invd)
@@ -113,14 +126,13 @@ class GraphedRenderStep:
             # loss = <color, dL_dcolor>: one dot-product for the value, and the upstream gradient handed
             # straight to the rasterizer's backward (no product tensor is materialised).  The value is
             # not an input of the backward, so its HBM-bound reduction runs on a side stream under the
-            # issue-bound backward compositor; the step's stream rejoins it before the step ends.
+            # issue-bound backward compositor -- on 16 CTAs (guava_image_dot): a full-grid library
+            # reduction launched there held the SMs while the compositor's first wave arrived (-15 us);
+            # the step's stream rejoins the side stream before the step ends.
             cur = torch.cuda.current_stream(self.device)
             self._side.wait_stream(cur)
             with torch.cuda.stream(self._side):
-                if capturing:
-                    self._flag_host.copy_(self._flag_dev, non_blocking=True)
-                    flag_copied = True
-                self.loss = torch.dot(color.detach().reshape(-1), self.dL_dcolor.reshape(-1))
+                self.loss = image_dot(color.detach(), self.dL_dcolor, self._loss_buf)
             color.backward(self.dL_dcolor)
         self.grads = {k: v.grad for k, v in leaf.items()}
         self.viewspace_grad = m2.grad
@@ -128,16 +140,14 @@ class GraphedRenderStep:
         self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
         if self.loss_fn is None:
             cur.wait_stream(self._side)
-        if capturing and not flag_copied:
-            self._flag_host.copy_(self._flag_dev, non_blocking=True)
 
     def replay(self):
         self.graph.replay()
         return self
 
     def check(self):
-        """Synchronise and raise if any replay so far overflowed the captured binning capacity."""
+        """Synchronise and raise if the latest replay overflowed the captured binning capacity."""
         torch.cuda.current_stream(self.device).synchronize()
-        if int(self._flag_host[0]) != 0:
+        if int(self._status[1]) < 0:      # bit 31: the replay's num_rendered exceeded the captured capacity
             raise RuntimeError("GraphedRenderStep: a replay needed more binning capacity than was captured; "
                                "re-create the step (or raise option 'capacity_hint')")

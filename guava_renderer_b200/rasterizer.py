@@ -392,6 +392,10 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                 if V * P == 0:
                     aux.zero_()
                 _check(lib.guava_rasterizer_set_refiner_output(_ptr(aux)))
+            status = getattr(_tls, "status_words", None)    # set by GraphedRenderStep: its pinned (R, longest|overflow)
+            _tls.status_words = None
+            if status is not None:
+                _check(lib.guava_rasterizer_set_status_words(status.data_ptr()))
             rc = lib.guava_rasterizer_forward_batch(
                 _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
                 V, P, _ptr(bg), W, H,

@@ -280,6 +280,24 @@ unsigned long long guava_launch_count(void);
 int guava_stage_time(const char *stage, double *total_ms, unsigned long long *calls);
 void guava_stage_time_reset(void);
 
+/* Training-side helper: out64[0] = sum_i a[i]*b[i] -- the value of a loss that is linear in the image
+ * (loss = <out_color, dL_dout_color>, the form the benchmark step and the parity tests use; GUAVA's own
+ * losses are computed by its trainer, main/trainer.py:60-95).  Runs on 16 CTAs so that it can share the
+ * GPU with the backward compositing kernel on another stream.  Deterministic.  `out64` is 64 floats of
+ * device memory owned by the caller: [0] result, [1..62] scratch, word [63] must be zero before the
+ * first call (the kernel leaves it zero).  a, b: device pointers, 16-byte aligned, n elements. */
+int guava_image_dot(const float *a, const float *b, size_t n, float *out64, void *stream);
+
+/* Status words.  The reference returns num_rendered through a blocking device->host copy per view
+ * (rasterizer_impl.cu:284).  Here the tile scan stores two words straight into pinned host memory:
+ * [0] = num_rendered, [1] = longest tile list | (capacity overflow << 31).  By default they go to a slot
+ * the library owns; a caller that enqueues the forward without waiting (option "async_forward", CUDA
+ * graph capture) hands its OWN two words -- 8-byte aligned, pinned, device-mapped host memory, e.g.
+ * cudaHostAlloc -- to the NEXT forward call of the calling thread and reads them after synchronising:
+ * no copy node, no copy engine, nothing on the stream after the last kernel.  Consumed by that call;
+ * NULL cancels. */
+int guava_rasterizer_set_status_words(void *pinned_host_u32x2);
+
 /* ---- the step immediately after the rasterizer ---------------------------
  * Refiner hand-off.  GUAVA feeds the stacked 32-channel image to its neural refiner
  * (models/UbodyAvatar/gaussian_render.py:70-73).  The NEXT forward call (single-view or batch) made by

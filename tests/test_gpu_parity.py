@@ -541,3 +541,45 @@ def test_pack_view_gradients_all_batch_sizes(V, P):
             acc = acc + x[v]
         cols.append(acc)
     assert torch.equal(packed, torch.cat(cols, dim=1))
+
+
+def test_graphed_step_reports_capacity_overflow_through_its_status_words():
+    """A captured forward whose binning capacity is too small skips its instance kernels and says so in
+    the step's pinned status words (written by the tile scan, no copy node); a normal capture does not."""
+    V, P, H, W = 2, 4000, 96, 96
+    views = [util.inputs_for(P, H, W, seed=950 + v, view=v, num_views=V, scale_mult=1.5) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    tanfov = torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=DEV), 1.0,
+                                        stack("viewmatrix"), stack("projmatrix"))
+    args = (stack("xyz"), stack("features"), stack("opacity"), stack("scaling"), stack("rotation"), st)
+    ok = grb.GraphedRenderStep(*args)
+    ok.replay()
+    ok.check()
+    R = int(ok._status[0])
+    assert R > 64 and int(ok._status[1]) > 0
+    grb.set_option("capacity_hint", 64)
+    try:
+        small = grb.GraphedRenderStep(*args)
+        small.replay()
+        with pytest.raises(RuntimeError, match="capacity"):
+            small.check()
+        assert int(small._status[0]) == R
+    finally:
+        grb.set_option("capacity_hint", 0)
+    ok.replay()
+    ok.check()
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 1027, 2 * 32 * 96 * 128, 5_000_003])
+def test_image_dot_matches_float64_and_is_deterministic(n):
+    from guava_renderer_b200.graphed import image_dot
+    g = torch.Generator().manual_seed(n)
+    a = torch.randn(n, generator=g).to(DEV)
+    b = torch.randn(n, generator=g).to(DEV)
+    buf = torch.zeros(64, device=DEV)
+    first = float(image_dot(a, b, buf))
+    again = float(image_dot(a, b, buf))          # the scratch words are left ready for reuse
+    want = float((a.double() * b.double()).sum())
+    assert first == again
+    assert abs(first - want) <= 1e-5 * float((a.double() * b.double()).abs().sum()) + 1e-6
