@@ -430,7 +430,17 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     timer.end();
     GUAVA_STAGE("preprocess", debug);
     timer.begin(1);
-    launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap, stream);
+    // The long-bucket sort (lists beyond the register-resident network) is an empty 4 us launch at the
+    // GUAVA shapes: it is left out while the previous call of this shape stayed well below the limit.  A
+    // list that outgrows the limit anyway is reported by the tile scan exactly like a capacity overflow
+    // (every later kernel skips itself) and the call is redone with the long-bucket sort.
+    bool with_large = true;
+    if (sort_mode == 0 && !exact) {
+        const uint32_t est = longest_estimate(n, in.W, in.H);
+        if (est != 0 && est <= tile_sort_small_limit() * 3 / 4) with_large = false;
+    }
+    launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap,
+                     with_large ? 0xFFFFFFFFu : tile_sort_small_limit(), stream);
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 
@@ -483,7 +493,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         timer.end();
         GUAVA_STAGE("scatter", debug);
         timer.begin(3);
-        launch_tile_sort(in, im, b, nullptr, stream);
+        launch_tile_sort(in, im, b, with_large, stream);
         timer.end();
         GUAVA_STAGE("tile_sort", debug);
         }
@@ -497,9 +507,11 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
             if (rc) return rc;
             have_R = true;
         }
-        if ((size_t)R <= cap) break;
-        // estimate too small: every kernel after the scan skipped itself
-        cap = (size_t)R;
+        if (attempt == 1 || (hslot[1] & 0x80000000u) == 0u) break;
+        // estimate too small (capacity, or a list beyond the sort that was launched): every kernel after
+        // the scan skipped itself
+        with_large = true;
+        if ((size_t)R > cap) cap = (size_t)R;
         compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
         bin = binningBuffer(binning_user, L.binning_bytes);
         if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");

@@ -63,7 +63,8 @@ size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (t
 // lengths for kernel 2, the longest list, and -- by the last block of the chain -- R and the overflow flag.
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ scratch,
-                 uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity)
+                 uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
+                 uint32_t list_limit)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
@@ -108,15 +109,18 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     if (bid == nblocks - 1 && tid == 0) {   // every other block has published, hence fenced its bins / maximum
         const uint32_t R = s_carry + chunk_total;
         const uint32_t longest = ld_volatile(scratch + SCAN_LONGEST);
+        // overflow: more instances than the binning buffer holds, or a list longer than the sort kernels
+        // that were launched can handle (the long-bucket sort is skipped while lists stay short)
+        const bool overflow = (unsigned long long)R > capacity || longest > list_limit;
         num_rendered[0] = R;
-        num_rendered[1] = ((unsigned long long)R > capacity) ? 1u : 0u;
+        num_rendered[1] = overflow ? 1u : 0u;
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
         // one aligned 8-byte store: (R, longest) reach the pinned host words together, no system fences
         if (host_R != nullptr)
             *reinterpret_cast<volatile unsigned long long*>(host_R) =
-                (unsigned long long)R | ((unsigned long long)(longest | (((unsigned long long)R > capacity) ? 0x80000000u : 0u)) << 32);
+                (unsigned long long)R | ((unsigned long long)(longest | (overflow ? 0x80000000u : 0u)) << 32);
     }
 }
 
@@ -148,12 +152,13 @@ tile_order_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict_
     if (bin < 256u) tile_order[pos + __popc(peers & ((1u << lane) - 1u))] = make_uint4((uint32_t)k, r.x, r.y, 0u);
 }
 
-void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity, cudaStream_t s)
+void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity,
+                      uint32_t list_limit, cudaStream_t s)
 {
     const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
     tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
-                                              host_mapped_R, (unsigned long long)capacity);
+                                              host_mapped_R, (unsigned long long)capacity, list_limit);
     tile_order_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.ranges, scratch, img.tile_order);
     count_launch(2);
 }
@@ -402,9 +407,10 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
     }
 }
 
-void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs& b, uint64_t* global_scratch, cudaStream_t s)
+uint32_t tile_sort_small_limit() { return SORT_SMALL; }
+
+void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs& b, bool with_large, cudaStream_t s)
 {
-    (void)global_scratch;
     const int total_tiles = in.V * in.tiles;
     if (total_tiles == 0) return;
     // function attributes are per device: one flag per device ordinal (setting it twice is harmless)
@@ -418,10 +424,12 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
     }
     tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted, b.point_list,
                                                        b.keys_sorted, in.tiles);
+    count_launch();
+    if (!with_large) return;
     const int big_grid = total_tiles < 148 ? total_tiles : 148;
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
         img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
-    count_launch(2);
+    count_launch();
 }
 
 }  // namespace guava

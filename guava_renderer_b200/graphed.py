@@ -149,5 +149,5 @@ class GraphedRenderStep:
         """Synchronise and raise if the latest replay overflowed the captured binning capacity."""
         torch.cuda.current_stream(self.device).synchronize()
         if int(self._status[1]) < 0:      # bit 31: the replay's num_rendered exceeded the captured capacity
-            raise RuntimeError("GraphedRenderStep: a replay needed more binning capacity than was captured; "
-                               "re-create the step (or raise option 'capacity_hint')")
+            raise RuntimeError("GraphedRenderStep: a replay needed more binning capacity (or a longer tile list) than "
+                               "was captured; re-create the step (or raise option 'capacity_hint')")

@@ -583,3 +583,26 @@ def test_image_dot_matches_float64_and_is_deterministic(n):
     want = float((a.double() * b.double()).sum())
     assert first == again
     assert abs(first - want) <= 1e-5 * float((a.double() * b.double()).abs().sum()) + 1e-6
+
+
+def test_list_longer_than_the_launched_sort_is_recovered():
+    """While a shape's tile lists stay short the long-bucket sort is not launched; a call of the same shape
+    whose lists outgrow the register-resident sort is detected by the tile scan and redone -- same image,
+    bit for bit, as with exact binning (which always launches both sorts)."""
+    P, H, W = 6000, 64, 64
+    short = util.inputs_for(P, H, W, seed=77, scale_mult=0.3)
+    long_ = util.inputs_for(P, H, W, seed=78, scale_mult=8.0)
+    grb.set_option("sort_mode", 0)
+    try:
+        for _ in range(2):
+            _ours_forward(short)                       # the shape is now known with short lists
+        got = _ours_forward(long_)
+        r = got["ranges"].reshape(-1, 2)
+        assert int((r[:, 1] - r[:, 0]).max()) > 2048   # the case is what it claims to be
+        grb.set_option("exact_binning", 1)
+        want = _ours_forward(long_)
+    finally:
+        grb.set_option("exact_binning", 0)
+        grb.set_option("sort_mode", -1)
+    for k in ("color", "invdepth", "radii", "n_contrib", "point_list", "ranges"):
+        assert np.array_equal(got[k], want[k]), k
