@@ -17,6 +17,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
 echo "ncu launches exit $?"
 $CMD > $O/plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on \
-    -k regex:"render_|preprocess_|tile_|scatter_|pack_" -s 30 -c 20 -f -o $O/prof $CMD > $O/ncu_full.log 2>&1
+    -k regex:"render_|preprocess_|tile_|scatter_|pack_|image_dot" -s 30 -c 20 -f -o $O/prof $CMD > $O/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $O
