@@ -26,24 +26,51 @@
 //    through 128 bytes of shared memory and every lane does 32 FFMAs.  The
 //    reference's 32 atomics per PIXEL become one 128-byte reduction per WARP,
 //    without the shuffle tree a per-pixel formulation needs;
-//  * the seven geometric partials (mean2D.xy, conic.xyw, opacity, invdepth) are
-//    reduced with a transposing butterfly and leave the SM as one 32-byte
-//    reduction into a packed per-Gaussian record (GeomPtrs::grad_geo) that the
-//    backward preprocess kernel consumes.
+//  * the seven geometric partials (moments of s = dL/dG*G about the pixel offset,
+//    G*dL/dalpha, w*dL/dinvdepth) are reduced in registers with a transposing
+//    butterfly (9 shuffles per splat) and leave the SM as one 28-byte reduction
+//    into a packed per-Gaussian record (GeomPtrs::grad_geo) that the backward
+//    preprocess kernel consumes.  The shared-memory data pipe is the busiest unit
+//    of this kernel: only what every lane needs in full -- feature
+//    rows, the 32 blending weights -- goes through shared memory.
 #include "internal.cuh"
 #include "tma.cuh"
 #include <cstdlib>
 
 namespace guava {
 
+// Survivor records staged PAIR-INTERLEAVED as in the forward kernel (FwdStage): pair k = survivors 2k, 2k+1, so one
+// LDS.128 delivers a quantity of both as the halves of packed f32x2 operands.
 struct __align__(128) BwdStage {
     float feat[32][NUM_CHANNELS];   // 4 KB
-    SplatRec rec[32];               // 1 KB
+    float4 xy[16];                  // x0 x1 y0 y1
+    float4 cab[16];                 // conic.x0 conic.x1 -conic.y0 -conic.y1
+    float4 cop[16];                 // conic.z0 conic.z1 opacity0 opacity1
+    float2 rd[16];                  // rdepth0 rdepth1
 };
 static_assert(sizeof(BwdStage) >= 32 * 32 * sizeof(float), "a stage doubles as the transpose scratch");
-// row stride of the exchange buffer: 32 pixels + 4 floats of padding, so that the 8-lane phases of
-// the row-sum LDS.128 (lanes 4k..4k+3 read row k) fall on distinct banks
-constexpr int EX_STRIDE = 36;
+
+// Transposing butterfly over two 8-vectors at once: afterwards lane 4*k holds in a[0] / b[0] the warp-wide sum
+// of element k of a / b.  9 shuffles per vector (4 + 2 + 1 exchange half of what is left, 2 finish the last 4 lanes).
+__device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&b)[8], int lane)
+{
+    int mask = 16;
+#pragma unroll
+    for (int half = 4; half >= 1; half >>= 1, mask >>= 1) {
+        const bool upper = (lane & mask) != 0;
+#pragma unroll
+        for (int i = 0; i < half; i++) {
+            const float sa = upper ? a[i] : a[i + half], ka = upper ? a[i + half] : a[i];
+            const float sb = upper ? b[i] : b[i + half], kb = upper ? b[i + half] : b[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, mask);
+            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, mask);
+        }
+    }
+    a[0] += __shfl_xor_sync(0xffffffffu, a[0], 2);
+    b[0] += __shfl_xor_sync(0xffffffffu, b[0], 2);
+    a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
+    b[0] += __shfl_xor_sync(0xffffffffu, b[0], 1);
+}
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
 {
@@ -53,8 +80,10 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 
 // One warp (= one CTA) per 8x4 pixel block, as in the forward kernel: no block
 // barrier, private double-buffered stage of culled survivors.
-// VEC_RED: 1 = 16-byte vector reductions (red.global.add.v4.f32, 8 + 2 lanes per
-// (warp, Gaussian)); 0 = 4-byte reductions (32 + 8 lanes), for unaligned outputs.
+// VEC_RED: 0 (default) = 4-byte reductions, one 128-byte request from all 32 lanes per (warp, Gaussian)
+// plus 7 lanes for the packed record; 1 = 16-byte vector reductions (red.global.add.v4.f32) from 8 lanes,
+// which costs three gathering shuffles per splat on the data pipe and measured 2 % slower
+// (option "scalar_red" = 0 selects it; profiles/r01_v43).
 template <int VEC_RED>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
@@ -64,13 +93,13 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ work_counter)
 {
     __shared__ BwdStage stage[2];
-    __shared__ __align__(16) float ex[4][8][EX_STRIDE];   // per-survivor exchange: two pairs in flight
+    __shared__ __align__(16) float ex[4][32];   // blending weights of a survivor, one per pixel: two pairs in flight
 
     const int lane = threadIdx.x;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
     uint32_t parity = 0;   // ex buffers (parity, parity+1) & 3 are used by the next pair
-    float* const exbase = &ex[0][0][0];
+    float* const exbase = &ex[0][0];
 
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
     const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
@@ -167,9 +196,12 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             BwdStage& st = stage[c & 1];
             if (keep) {
                 const int slot = __popc(mask & lt_mask);
-                float4* dst = reinterpret_cast<float4*>(&st.rec[slot]);
-                dst[0] = c0;
-                dst[1] = c1;
+                const int o = (slot >> 1) * 4 + (slot & 1);
+                float* q;
+                q = &st.xy[0].x + o;   q[0] = c0.x; q[2] = c0.y;
+                q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
+                q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
+                (&st.rd[0].x)[slot] = c1.z;
                 // the lane's own 128-byte feature row as eight 16-byte asynchronous copies, piece order rotated by
                 // the slot so that the lanes of one instruction fall on distinct bank groups (render_forward.cu)
                 const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
@@ -209,32 +241,36 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         if (mask_cur != 0u) {
             tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
             __syncwarp();
-            const float4* __restrict__ recp = reinterpret_cast<const float4*>(&stage[s].rec[0]);
+            const BwdStage& stg = stage[s];
+            int kp = 0;
             const float4* __restrict__ featp = reinterpret_cast<const float4*>(&stage[s].feat[0][0]);
             const uint32_t pos0 = (uint32_t)(total - 1 - (c << 5));   // list position of chunk lane 0
             uint32_t m = mask_cur;
             // Survivors are walked two at a time.  Everything that does not depend on the running
-            // transmittance -- SplatRec loads, alpha, the 32-channel dot product -- is evaluated for
-            // both side by side (independent latency chains); the T / accum recurrences then run in
-            // list order; the exchange, the two matrix-vector products and the reductions are again
-            // independent.
-            for (; m != 0u; recp += 4, featp += 2 * (NUM_CHANNELS / 4)) {
+            // transmittance -- record loads, alpha, the moments' products -- is evaluated for both at once
+            // with packed f32x2 instructions, the two 32-channel dot products side by side (independent
+            // latency chains); the T / accum recurrences then run in list order; the exchange, the two
+            // matrix-vector products and the reductions are again independent.
+            for (; m != 0u; kp++, featp += 2 * (NUM_CHANNELS / 4)) {
                 const int jl0 = __ffs(m) - 1;
                 m &= m - 1;
                 const bool has1 = m != 0u;
                 const int jl1 = has1 ? __ffs(m) - 1 : jl0;
                 m &= m - 1;
-                const float4 p0 = recp[0], p1 = recp[1];   // x, y, cx, cy | cz, op, rdepth, aux
-                const float4 q0 = recp[2], q1 = recp[3];   // second of the pair (stale data if !has1)
-                const float dx0 = fsub(p0.x, pxf), dy0 = fsub(p0.y, pyf);
-                const float dx1 = fsub(q0.x, pxf), dy1 = fsub(q0.y, pyf);
-                const float pw0 = ffma(ffma(dx0, fmul(dx0, p0.z), fmul(dy0, fmul(dy0, p1.x))), -0.5f,
-                                       -fmul(dy0, fmul(dx0, p0.w)));
-                const float pw1 = ffma(ffma(dx1, fmul(dx1, q0.z), fmul(dy1, fmul(dy1, q1.x))), -0.5f,
-                                       -fmul(dy1, fmul(dx1, q0.w)));
-                const float G0 = expf(pw0), G1 = expf(pw1);
-                const float alpha0 = fminf(0.99f, fmul(p1.y, G0));
-                const float alpha1 = fminf(0.99f, fmul(q1.y, G1));
+                // both alpha chains as packed f32x2 instructions: per half the very operations, in the very order, of
+                // the forward kernel's eval_pair (bit-identical alpha); the second half is stale data if !has1
+                const float4 pa = stg.xy[kp], pb = stg.cab[kp], pc = stg.cop[kp];
+                const float2 rdp = stg.rd[kp];
+                const float2 dxp = __fadd2_rn(f2(pa.x, pa.y), f2(-pxf));
+                const float2 dyp = __fadd2_rn(f2(pa.z, pa.w), f2(-pyf));
+                const float2 qd = __ffma2_rn(dxp, __fmul2_rn(dxp, f2(pb.x, pb.y)), __fmul2_rn(dyp, __fmul2_rn(dyp, f2(pc.x, pc.y))));
+                const float2 pwp = __ffma2_rn(qd, f2(-0.5f), __fmul2_rn(dyp, __fmul2_rn(dxp, f2(pb.z, pb.w))));   // pb.zw = -conic.y
+                const float2 Gp = expf_pair(pwp);
+                const float2 agp = __fmul2_rn(f2(pc.z, pc.w), Gp);
+                const float pw0 = pwp.x, pw1 = pwp.y, G0 = Gp.x, G1 = Gp.y;
+                const float alpha0 = fminf(0.99f, agp.x);
+                const float alpha1 = fminf(0.99f, agp.y);
+                const float rdepth0 = rdp.x, rdepth1 = rdp.y;
                 const bool take0 = ((pos0 - (uint32_t)jl0) < last_contributor) && !(pw0 > 0.0f) && !(alpha0 < 1.0f / 255.0f);
                 const bool take1 = has1 && ((pos0 - (uint32_t)jl1) < last_contributor) && !(pw1 > 0.0f) &&
                                    !(alpha1 < 1.0f / 255.0f);
@@ -253,16 +289,18 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     dc = __ffma2_rn(make_float2(h.x, h.y), g[2 * q + 0], dc);
                     dd = __ffma2_rn(make_float2(h.z, h.w), g[2 * q + 1], dd);
                 }
-                const float d0 = fmaf(p1.z, g_inv, (da.x + da.y) + (db.x + db.y));
-                const float d1 = fmaf(q1.z, g_inv, (dc.x + dc.y) + (dd.x + dd.y));
+                const float2 ds0 = __fadd2_rn(da, db), ds1 = __fadd2_rn(dc, dd);
+                const float d0 = fmaf(rdepth0, g_inv, ds0.x + ds0.y);
+                const float d1 = fmaf(rdepth1, g_inv, ds1.x + ds1.y);
 
                 // Per-pixel partials: the blending weight w and moments of s = dL/dG * G about the
                 // pixel offset d (the conic / mean2D / opacity gradients are linear in them;
                 // backward.cu:612-635 is finished per Gaussian by the backward preprocess kernel).
                 // In list order: first splat ...
                 float w0 = 0.0f, mo0 = 0.0f, w1 = 0.0f, mo1 = 0.0f;
+                const float2 om2 = __ffma2_rn(f2(alpha0, alpha1), f2(-1.0f), f2(1.0f));   // 1 - alpha of both
                 {
-                    const float inv_om = __fdividef(1.0f, 1.0f - alpha0);
+                    const float inv_om = __fdividef(1.0f, om2.x);
                     const float Tn = T * inv_om;
                     const float An = fmaf(last_alpha, last_d - A, A);   // last_alpha*last_d + (1-last_alpha)*A
                     const float dLda = fmaf(d0 - An, Tn, -(T_final * inv_om) * bgdot);
@@ -274,7 +312,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 }
                 // ... then the second
                 {
-                    const float inv_om = __fdividef(1.0f, 1.0f - alpha1);
+                    const float inv_om = __fdividef(1.0f, om2.y);
                     const float Tn = T * inv_om;
                     const float An = fmaf(last_alpha, last_d - A, A);
                     const float dLda = fmaf(d1 - An, Tn, -(T_final * inv_om) * bgdot);
@@ -284,32 +322,28 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                         mo1 = G1 * dLda;
                     }
                 }
-                const float sx0 = (p1.y * mo0) * dx0, sy0 = (p1.y * mo0) * dy0;   // s*dx, s*dy
-                const float sx1 = (q1.y * mo1) * dx1, sy1 = (q1.y * mo1) * dy1;
-                // Exchange through shared memory: row k of an ex buffer holds partial k of all 32 pixels.
-                float* exb0 = exbase + (parity & 3u) * (8 * EX_STRIDE);
-                float* exb1 = exbase + ((parity + 1u) & 3u) * (8 * EX_STRIDE);
+                // the moments of both splats as packed products (dxp / dyp hold the offsets of both)
+                const float2 s2 = __fmul2_rn(f2(pc.z, pc.w), f2(mo0, mo1));
+                const float2 sx2 = __fmul2_rn(s2, dxp), sy2 = __fmul2_rn(s2, dyp);   // s*dx, s*dy
+                const float2 sxx2 = __fmul2_rn(sx2, dxp), sxy2 = __fmul2_rn(sx2, dyp), syy2 = __fmul2_rn(sy2, dyp);
+                const float2 wg2 = __fmul2_rn(f2(w0, w1), f2(g_inv));
+                float* exb0 = exbase + (parity & 3u) * 32;
+                float* exb1 = exbase + ((parity + 1u) & 3u) * 32;
                 parity += 2u;
-                exb0[0 * EX_STRIDE + lane] = sx0;
-                exb0[1 * EX_STRIDE + lane] = sy0;
-                exb0[2 * EX_STRIDE + lane] = sx0 * dx0;
-                exb0[3 * EX_STRIDE + lane] = sx0 * dy0;
-                exb0[4 * EX_STRIDE + lane] = sy0 * dy0;
-                exb0[5 * EX_STRIDE + lane] = mo0;
-                exb0[6 * EX_STRIDE + lane] = w0 * g_inv;
-                exb0[7 * EX_STRIDE + lane] = w0;
-                exb1[0 * EX_STRIDE + lane] = sx1;
-                exb1[1 * EX_STRIDE + lane] = sy1;
-                exb1[2 * EX_STRIDE + lane] = sx1 * dx1;
-                exb1[3 * EX_STRIDE + lane] = sx1 * dy1;
-                exb1[4 * EX_STRIDE + lane] = sy1 * dy1;
-                exb1[5 * EX_STRIDE + lane] = mo1;
-                exb1[6 * EX_STRIDE + lane] = w1 * g_inv;
-                exb1[7 * EX_STRIDE + lane] = w1;
+                // Only the blending weights go through shared memory (every lane needs all 32 of them for the
+                // colour-gradient mat-vec); the seven moments are reduced in registers by a transposing butterfly:
+                // 18 shuffles per pair instead of 14 STS + 4 non-broadcast LDS.128 (16 wavefronts) + 4 shuffles on the
+                // shared-memory data pipe, the busiest unit of this kernel (+1.7 % step throughput, profiles/r01_v42).
+                exb0[lane] = w0;
+                exb1[lane] = w1;
                 __syncwarp();
+                float mv0[8] = {sx2.x, sy2.x, sxx2.x, sxy2.x, syy2.x, mo0, wg2.x, 0.0f};
+                float mv1[8] = {sx2.y, sy2.y, sxx2.y, sxy2.y, syy2.y, mo1, wg2.y, 0.0f};
+                warp_transpose_reduce8x2(mv0, mv1, lane);
+                const float mom0 = mv0[0], mom1 = mv1[0];   // lane 4k: moment k
                 // (a) lane c accumulates channel c of dL/dcolor: 32 weights x its column of g
-                const float4* __restrict__ wa = reinterpret_cast<const float4*>(exb0 + 7 * EX_STRIDE);
-                const float4* __restrict__ wb = reinterpret_cast<const float4*>(exb1 + 7 * EX_STRIDE);
+                const float4* __restrict__ wa = reinterpret_cast<const float4*>(exb0);
+                const float4* __restrict__ wb = reinterpret_cast<const float4*>(exb1);
                 float2 ca = make_float2(0.0f, 0.0f), cb = ca, cc = ca, cd = ca;
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
@@ -320,19 +354,9 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     cc = __ffma2_rn(make_float2(x.x, x.y), gT[2 * q + 0], cc);
                     cd = __ffma2_rn(make_float2(x.z, x.w), gT[2 * q + 1], cd);
                 }
-                const float col0 = (ca.x + ca.y) + (cb.x + cb.y);
-                const float col1 = (cc.x + cc.y) + (cd.x + cd.y);
-                // (b) lanes 4k..4k+3 sum row k (8 pixels each), two shuffles finish it
-                const int eoff = (lane >> 2) * EX_STRIDE + (lane & 3) * 8;
-                const float4* __restrict__ e0 = reinterpret_cast<const float4*>(exb0 + eoff);
-                const float4* __restrict__ e1 = reinterpret_cast<const float4*>(exb1 + eoff);
-                const float4 ea = e0[0], eb = e0[1], ec = e1[0], ed = e1[1];
-                float mom0 = ((ea.x + ea.y) + (ea.z + ea.w)) + ((eb.x + eb.y) + (eb.z + eb.w));
-                float mom1 = ((ec.x + ec.y) + (ec.z + ec.w)) + ((ed.x + ed.y) + (ed.z + ed.w));
-                mom0 += __shfl_xor_sync(0xffffffffu, mom0, 1);
-                mom1 += __shfl_xor_sync(0xffffffffu, mom1, 1);
-                mom0 += __shfl_xor_sync(0xffffffffu, mom0, 2);
-                mom1 += __shfl_xor_sync(0xffffffffu, mom1, 2);
+                const float2 cs0 = __fadd2_rn(ca, cb), cs1 = __fadd2_rn(cc, cd);
+                const float col0 = cs0.x + cs0.y;
+                const float col1 = cs1.x + cs1.y;
 
                 const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
                 const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
