@@ -266,7 +266,10 @@ int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, gu
  * chained scan + duplicateWithKeys + onesweep LSD radix sort of the 64-bit tile|depth keys +
  * identifyTileRanges, rasterizer_impl.cu:280-320; identical keys, values and ranges; -1 (default): 1 when
  * the previous call of the same shape produced a tile list longer than 2048 instances, else 0;
- * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes).
+ * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes),
+ * "scalar_red" (0/1, default 1: the backward compositor adds dL_dcolors with one 4-byte reduction per
+ * lane -- a 128-byte request per (pixel block, Gaussian); 0 = gather 16-byte vectors into 8 lanes first,
+ * needs 16-byte aligned dL_dcolors, measured 1 % slower).
  * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);
