@@ -50,8 +50,11 @@ struct __align__(128) BwdStage {
 };
 static_assert(sizeof(BwdStage) >= 32 * 32 * sizeof(float), "a stage doubles as the transpose scratch");
 
-// Transposing butterfly over two 8-vectors at once: afterwards lane 4*k holds in a[0] / b[0] the warp-wide sum
-// of element k of a / b.  9 shuffles per vector (4 + 2 + 1 exchange half of what is left, 2 finish the last 4 lanes).
+// Transposing butterfly over two 8-vectors at once: afterwards lanes 4k .. 4k+3 hold in a[0] / b[0] four partial
+// sums (over 8 lanes each) of element k of a / b.  7 shuffles per vector (4 + 2 + 1, each step exchanges half of what
+// is left).  The four partials are not combined here: each of those lanes adds its own to the same word of the
+// packed record -- two more shuffle steps on the data pipe measured 2.8 % slower than the 21 extra L2 reductions
+// per splat (profiles/r01_v46).
 __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&b)[8], int lane)
 {
     int mask = 16;
@@ -66,10 +69,6 @@ __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&
             b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, mask);
         }
     }
-    a[0] += __shfl_xor_sync(0xffffffffu, a[0], 2);
-    b[0] += __shfl_xor_sync(0xffffffffu, b[0], 2);
-    a[0] += __shfl_xor_sync(0xffffffffu, a[0], 1);
-    b[0] += __shfl_xor_sync(0xffffffffu, b[0], 1);
 }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
@@ -340,7 +339,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 float mv0[8] = {sx2.x, sy2.x, sxx2.x, sxy2.x, syy2.x, mo0, wg2.x, 0.0f};
                 float mv1[8] = {sx2.y, sy2.y, sxx2.y, sxy2.y, syy2.y, mo1, wg2.y, 0.0f};
                 warp_transpose_reduce8x2(mv0, mv1, lane);
-                const float mom0 = mv0[0], mom1 = mv1[0];   // lane 4k: moment k
+                const float mom0 = mv0[0], mom1 = mv1[0];   // lanes 4k..4k+3: partial sums of moment k
                 // (a) lane c accumulates channel c of dL/dcolor: 32 weights x its column of g
                 const float4* __restrict__ wa = reinterpret_cast<const float4*>(exb0);
                 const float4* __restrict__ wb = reinterpret_cast<const float4*>(exb1);
@@ -360,9 +359,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
                 const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
                 const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
-                // All reductions of the pair sit in ONE lane-divergent region (lanes 0, 4, .., 28); four separate
-                // `if (lane ...) red` were four BSSY/BSYNC reconvergence brackets, 7 % of the kernel's stall samples
-                // (profiles/r01_v15).  Lane 28 adds 0 to the unused eighth word of the packed record.
+                // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
                 if (VEC_RED) {
                     const float a1 = __shfl_down_sync(0xffffffffu, col0, 1);
                     const float a2 = __shfl_down_sync(0xffffffffu, col0, 2);
@@ -370,19 +367,14 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                     const float b1 = __shfl_down_sync(0xffffffffu, col1, 1);
                     const float b2 = __shfl_down_sync(0xffffffffu, col1, 2);
                     const float b3 = __shfl_down_sync(0xffffffffu, col1, 3);
-                    const float m0 = lane < 28 ? mom0 : 0.0f, m1 = lane < 28 ? mom1 : 0.0f;
                     if ((lane & 3) == 0) {
-                        if (any0) {
-                            red_add_v4(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
-                            atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), m0);
-                        }
-                        if (any1) {
-                            red_add_v4(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
-                            atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), m1);
-                        }
+                        if (any0) red_add_v4(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
+                        if (any1) red_add_v4(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
                     }
+                    if (any0 && lane < 28) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
+                    if (any1 && lane < 28) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
                 } else {
-                    const bool geo_lane = (lane & 3) == 0 && lane < 28;
+                    const bool geo_lane = lane < 28;   // lanes 4k..4k+3: partials of moment k (moment 7 is unused)
                     if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
                     if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
                     if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);

@@ -165,6 +165,26 @@ def test_backward_vs_reference_build(ref, case, with_invdepth):
         assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
 
 
+def test_backward_vector_reduction_option_vs_reference_build(ref):
+    """Option scalar_red = 0: dL_dcolors leaves the SM as 16-byte vector reductions from 8 lanes instead of the
+    default 4-byte reductions from all 32; same gradients."""
+    case = GRAD_CASES[0]
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(9)
+    dL_dcolor = torch.randn(32, case["H"], case["W"], generator=g)
+    dL_dinv = torch.randn(1, case["H"], case["W"], generator=g)
+    assert grb.get_option("scalar_red") == 1
+    grb.set_option("scalar_red", 0)
+    try:
+        _, go = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
+    finally:
+        grb.set_option("scalar_red", 1)
+    _, gr = _run_autograd(ref, inp, dL_dcolor, dL_dinv)
+    for k in gr:
+        assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+
+
 @pytest.mark.parametrize("antialiasing", [False, True])
 def test_backward_vs_cpu_oracle(antialiasing):
     import oracle
