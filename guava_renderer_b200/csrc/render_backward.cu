@@ -1,5 +1,5 @@
-// Backward compositing: one CTA per 16x16 tile walks its depth-sorted list back
-// to front and produces the per-Gaussian screen-space gradients.
+// Backward compositing: every 8x4 pixel block of a 16x16 tile (one warp = one CTA) walks the
+// tile's depth-sorted list back to front and produces the per-Gaussian screen-space gradients.
 //
 // Reference behaviour: DGR32/cuda_rasterizer/backward.cu:452-638 (renderCUDA),
 // which issues 39 global atomicAdd per contributing (pixel, Gaussian) pair
@@ -28,9 +28,9 @@
 //    without the shuffle tree a per-pixel formulation needs;
 //  * the seven geometric partials (moments of s = dL/dG*G about the pixel offset,
 //    G*dL/dalpha, w*dL/dinvdepth) are reduced in registers with a transposing
-//    butterfly (9 shuffles per splat) and leave the SM as one 28-byte reduction
-//    into a packed per-Gaussian record (GeomPtrs::grad_geo) that the backward
-//    preprocess kernel consumes.  The shared-memory data pipe is the busiest unit
+//    butterfly (7 shuffles per splat; lanes 4k..4k+3 end with four partial sums
+//    of moment k and each adds its own) into a packed per-Gaussian record
+//    (GeomPtrs::grad_geo) that the backward preprocess kernel consumes.  The shared-memory data pipe is the busiest unit
 //    of this kernel: only what every lane needs in full -- feature
 //    rows, the 32 blending weights -- goes through shared memory.
 #include "internal.cuh"
@@ -80,7 +80,7 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // One warp (= one CTA) per 8x4 pixel block, as in the forward kernel: no block
 // barrier, private double-buffered stage of culled survivors.
 // VEC_RED: 0 (default) = 4-byte reductions, one 128-byte request from all 32 lanes per (warp, Gaussian)
-// plus 7 lanes for the packed record; 1 = 16-byte vector reductions (red.global.add.v4.f32) from 8 lanes,
+// plus 28 lanes for the packed record; 1 = 16-byte vector reductions (red.global.add.v4.f32) from 8 lanes,
 // which costs three gathering shuffles per splat on the data pipe and measured 2 % slower
 // (option "scalar_red" = 0 selects it; profiles/r01_v43).
 template <int VEC_RED>
