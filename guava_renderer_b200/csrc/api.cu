@@ -33,6 +33,7 @@ static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_async_forward{0};
 static std::atomic<long long> g_opt_scalar_red{1};   // 1: 4-byte reductions from all 32 lanes (measured faster than gathering 16-byte vectors, profiles/r01_v43)
+static std::atomic<long long> g_opt_block_masks{0};   // experimental, see Inputs::block_masks (internal.cuh)
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
 static thread_local void* t_refiner_output = nullptr;   // consumed by the next forward call of this thread
@@ -344,6 +345,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
 {
     if (num_rendered) *num_rendered = 0;
     in.aux_nhwc_bf16 = t_refiner_output;
+    const int block_masks = g_opt_block_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;
     t_refiner_output = nullptr;
     uint32_t* const status_host = t_status_host;
     t_status_host = nullptr;
@@ -493,12 +495,12 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         timer.end();
         GUAVA_STAGE("scatter", debug);
         timer.begin(3);
-        launch_tile_sort(in, im, b, with_large, stream);
+        launch_tile_sort(in, g, im, b, with_large, block_masks, stream);
         timer.end();
         GUAVA_STAGE("tile_sort", debug);
         }
         timer.begin(4);
-        launch_render_forward(in, g, im, b, out_color, out_invdepth, stream);
+        launch_render_forward(in, g, im, b, out_color, out_invdepth, block_masks, stream);
         timer.end();
         GUAVA_STAGE("render_forward", debug);
         if (async_fwd) { R = 0xFFFFFFFFu; break; }
@@ -532,6 +534,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
                          float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream)
 {
     if ((size_t)in.V * in.P == 0) return GUAVA_OK;
+    const int block_masks = g_opt_block_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // as in the forward call
     if (!geom || !bin || !img || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
         !dL_dmean3D || !dL_dcov3D || !radii)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
@@ -568,7 +571,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     StageTimer timer(stream);
     timer.begin(5);
     GUAVA_CUDA(cudaMemsetAsync(g.grad_geo, 0, (size_t)in.V * in.P * 32, stream));
-    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, vec_red, stream);
+    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, vec_red, block_masks, stream);
     timer.end();
     GUAVA_STAGE("render_backward", debug);
     timer.begin(6);
@@ -777,6 +780,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
     if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
     if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;
+    if (!strcmp(name, "block_masks")) return &g_opt_block_masks;
     return nullptr;
 }
 

@@ -278,10 +278,27 @@ __device__ __forceinline__ uint32_t next_pow2(uint32_t n)
 // is register-to-register for j < E, a warp shuffle for j < 32*E, and goes through shared memory
 // (transposed layout, conflict-free) only for the few steps with j >= 32*E -- 6 of 55 steps at
 // N = 1024 -- where the first version synchronised the block after every step.
-template <int E>
+// Option "block_masks": bits 24..31 of a point_list entry = the 8x4 pixel blocks of the tile (block b = column
+// b & 1, row b >> 1, as the compositors number them) that the splat provably cannot touch -- the compositors'
+// own test (splat_may_touch), evaluated once per list entry instead of once per (block, entry) and kernel.
+__device__ __forceinline__ uint32_t untouched_blocks(const SplatRec* __restrict__ recs, uint32_t id, float tx0, float ty0)
+{
+    const float4* __restrict__ rp = reinterpret_cast<const float4*>(recs + id);
+    const float4 c0 = rp[0], c1 = rp[1];
+    uint32_t bits = 0;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const float wx0 = tx0 + (float)((b & 1) * 8), wy0 = ty0 + (float)((b >> 1) * 4);
+        if (!splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f)) bits |= 1u << b;
+    }
+    return bits << BLOCK_MASK_SHIFT;
+}
+
+template <int E, int MASKS>
 __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__ src, uint32_t n, uint64_t* skeys,
                                                     uint32_t* __restrict__ point_list, uint64_t* __restrict__ keys_sorted,
-                                                    uint64_t tile_hi, int tid)
+                                                    uint64_t tile_hi, int tid,
+                                                    const SplatRec* __restrict__ mask_recs, float tx0, float ty0)
 {
     constexpr int N = 256 * E;
     uint64_t key[E];
@@ -337,16 +354,20 @@ __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__
     for (int e = 0; e < E; e++) {
         const uint32_t i = (uint32_t)(tid * E + e);
         if (i < n) {
-            point_list[i] = (uint32_t)key[e];
+            uint32_t id = (uint32_t)key[e];
+            if (MASKS) id |= untouched_blocks(mask_recs, id, tx0, ty0);
+            point_list[i] = id;
             if (keys_sorted != nullptr) keys_sorted[i] = tile_hi | (key[e] >> 32);
         }
     }
 }
 
+template <int MASKS>
 __global__ void __launch_bounds__(256)
 tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __restrict__ num_rendered,
                        const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                       uint64_t* __restrict__ keys_sorted, int tiles_per_view)
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view,
+                       const SplatRec* __restrict__ mask_recs, int P, int gx)
 {
     __shared__ uint64_t skeys[2048];
     if (num_rendered[1]) return;
@@ -360,10 +381,19 @@ tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __r
     const int tid = threadIdx.x;
     const uint64_t tile_hi = (uint64_t)(item.x % (uint32_t)tiles_per_view) << 32;
     uint64_t* ks = keys_sorted != nullptr ? keys_sorted + r.x : nullptr;
-    if (n <= 256) tile_sort_registers<1>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
-    else if (n <= 512) tile_sort_registers<2>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
-    else if (n <= 1024) tile_sort_registers<4>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
-    else tile_sort_registers<8>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    // block masks (option): records of this tile's view, pixel origin of the tile
+    const SplatRec* mr = nullptr;
+    float tx0 = 0.0f, ty0 = 0.0f;
+    if (MASKS) {
+        const uint32_t view = item.x / (uint32_t)tiles_per_view, tile = item.x % (uint32_t)tiles_per_view;
+        mr = mask_recs + (size_t)view * P;
+        tx0 = (float)((tile % (uint32_t)gx) * TILE_X);
+        ty0 = (float)((tile / (uint32_t)gx) * TILE_Y);
+    }
+    if (n <= 256) tile_sort_registers<1, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
+    else if (n <= 512) tile_sort_registers<2, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
+    else if (n <= 1024) tile_sort_registers<4, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
+    else tile_sort_registers<8, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
 }
 
 // Buckets longer than SORT_SMALL are rare (none at the GUAVA shapes): one persistent
@@ -409,7 +439,8 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
 
 uint32_t tile_sort_small_limit() { return SORT_SMALL; }
 
-void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs& b, bool with_large, cudaStream_t s)
+void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b, bool with_large,
+                      int block_masks, cudaStream_t s)
 {
     const int total_tiles = in.V * in.tiles;
     if (total_tiles == 0) return;
@@ -422,9 +453,14 @@ void launch_tile_sort(const Inputs& in, const ImagePtrs& img, const BinningPtrs&
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
-    tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted, b.point_list,
-                                                       b.keys_sorted, in.tiles);
+    if (block_masks)
+        tile_sort_small_kernel<1><<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted,
+                                                              b.point_list, b.keys_sorted, in.tiles, g.rec, in.P, in.gx);
+    else
+        tile_sort_small_kernel<0><<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted,
+                                                              b.point_list, b.keys_sorted, in.tiles, nullptr, 0, 0);
     count_launch();
+    // (lists sorted by the long-bucket kernel keep plain ids: no block of theirs is marked untouched)
     if (!with_large) return;
     const int big_grid = total_tiles < 148 ? total_tiles : 148;
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(

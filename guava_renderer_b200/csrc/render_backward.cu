@@ -83,7 +83,9 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // plus 28 lanes for the packed record; 1 = 16-byte vector reductions (red.global.add.v4.f32) from 8 lanes,
 // which costs three gathering shuffles per splat on the data pipe and measured 2 % slower
 // (option "scalar_red" = 0 selects it; profiles/r01_v43).
-template <int VEC_RED>
+// MASKS = 1 (option "block_masks"): see render_forward.cu -- the list entries carry the forward's block masks, no
+// footprint test is run here.
+template <int VEC_RED, int MASKS>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
@@ -182,14 +184,18 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
     // those moves stalled the warp for the whole L2 round trip right after the load was issued
     // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
+    auto is_kept = [&](uint32_t id) -> bool { return id != NO_ID && ((id >> (BLOCK_MASK_SHIFT + sub)) & 1u) == 0u; };
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + (id != NO_ID ? id : 0u));
+        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? id : 0u);
+        const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + r);
         c0 = rp[0];
         c1 = rp[1];
     };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
-        const bool keep = id != NO_ID &&
-                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
+        const bool keep = MASKS ? is_kept(id)
+                                : (id != NO_ID &&
+                                   splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
+        if (MASKS) id &= BLOCK_MASK_ID;
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             BwdStage& st = stage[c & 1];
@@ -357,8 +363,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 const float col0 = cs0.x + cs0.y;
                 const float col1 = cs1.x + cs1.y;
 
-                const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
-                const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
+                const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
+                const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
                 if (VEC_RED) {
                     const float a1 = __shfl_down_sync(0xffffffffu, col0, 1);
@@ -393,21 +399,20 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
                             const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor, int vec_red,
-                            cudaStream_t s)
+                            int block_masks, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 12; }();   // tuning knob
     const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
-    if (vec_red)
-        render_backward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T, img.n_contrib,
-                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,
-                                                      img.num_rendered + 3);
-    else
-        render_backward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T, img.n_contrib,
-                                                      dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,
-                                                      img.num_rendered + 3);
+#define GUAVA_LAUNCH_BWD(VR, MK)                                                                                          \
+    render_backward_kernel<VR, MK><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T,   \
+                                                       img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,    \
+                                                       img.num_rendered + 3)
+    if (block_masks) { if (vec_red) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(0, 1); }
+    else             { if (vec_red) GUAVA_LAUNCH_BWD(1, 0); else GUAVA_LAUNCH_BWD(0, 0); }
+#undef GUAVA_LAUNCH_BWD
     cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();
 }

@@ -44,6 +44,9 @@ struct __align__(128) FwdStage {
     float4 dpos[16];                // rdepth0 rdepth1 list-position0 list-position1 (positions as bits, 1-based)
 };
 
+// MASKS = 1 (option "block_masks"): the tile sort has marked, in bits 24..31 of every list entry, the blocks the
+// splat cannot touch; the footprint test is that bit, and records are gathered for survivors only.
+template <int MASKS>
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
@@ -107,16 +110,21 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
     // those moves stalled the warp for the whole L2 round trip right after the load was issued
     // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
+    // (MASKS: `id` is the raw list entry; entries of other blocks re-read record 0 like the lanes past the end)
+    auto is_kept = [&](uint32_t id) -> bool { return id != NO_ID && ((id >> (BLOCK_MASK_SHIFT + sub)) & 1u) == 0u; };
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + (id != NO_ID ? id : 0u));
+        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? id : 0u);
+        const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + r);
         c0 = rp[0];
         c1 = rp[1];
     };
     // Test chunk c (one list entry per lane) and stage the survivors into stage[c & 1].
     // Returns the survivor mask (bit = lane = list offset within the chunk).
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
-        const bool keep = id != NO_ID &&
-                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
+        const bool keep = MASKS ? is_kept(id)
+                                : (id != NO_ID &&
+                                   splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
+        if (MASKS) id &= BLOCK_MASK_ID;
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             FwdStage& st = stage[c & 1];
@@ -283,14 +291,18 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 }
 
 void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
-                           float* out_color, float* out_invdepth, cudaStream_t s)
+                           float* out_color, float* out_invdepth, int block_masks, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_FWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
     const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
-    render_forward_kernel<<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
-                                              img.final_T, img.n_contrib, out_color, out_invdepth);
+    if (block_masks)
+        render_forward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
+                                                     img.final_T, img.n_contrib, out_color, out_invdepth);
+    else
+        render_forward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
+                                                     img.final_T, img.n_contrib, out_color, out_invdepth);
     count_launch();
 }
 

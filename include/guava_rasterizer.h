@@ -269,7 +269,11 @@ int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, gu
  * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes),
  * "scalar_red" (0/1, default 1: the backward compositor adds dL_dcolors with one 4-byte reduction per
  * lane -- a 128-byte request per (pixel block, Gaussian); 0 = gather 16-byte vectors into 8 lanes first,
- * needs 16-byte aligned dL_dcolors, measured 1 % slower).
+ * needs 16-byte aligned dL_dcolors, measured 1 % slower),
+ * "block_masks" (0/1, default 0; EXPERIMENTAL, compiled but not yet run on hardware: the tile sort evaluates the
+ * compositors' footprint test once per list entry and stores the blocks a splat cannot touch in bits 24..31 of the
+ * point_list entries, which then are not plain indices; P < 2^24; must not change between a forward call and its
+ * backward call).
  * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);
