@@ -33,7 +33,7 @@ static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_async_forward{0};
 static std::atomic<long long> g_opt_scalar_red{1};   // 1: 4-byte reductions from all 32 lanes (measured faster than gathering 16-byte vectors, profiles/r01_v43)
-static std::atomic<long long> g_opt_block_masks{0};   // experimental, see Inputs::block_masks (internal.cuh)
+static std::atomic<long long> g_opt_block_masks{0};   // experimental, see BLOCK_MASK_SHIFT (internal.cuh)
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
 static thread_local void* t_refiner_output = nullptr;   // consumed by the next forward call of this thread
