@@ -337,7 +337,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 parity += 2u;
                 // Only the blending weights go through shared memory (every lane needs all 32 of them for the
                 // colour-gradient mat-vec); the seven moments are reduced in registers by a transposing butterfly:
-                // 18 shuffles per pair instead of 14 STS + 4 non-broadcast LDS.128 (16 wavefronts) + 4 shuffles on the
+                // 14 shuffles per pair (18 before the last two steps were left to the L2) instead of 14 STS + 4 non-broadcast LDS.128 (16 wavefronts) + 4 shuffles on the
                 // shared-memory data pipe, the busiest unit of this kernel (+1.7 % step throughput, profiles/r01_v42).
                 exb0[lane] = w0;
                 exb1[lane] = w1;
