@@ -1,31 +1,36 @@
 #!/usr/bin/env python
 """Benchmark of the rasterizer hot path.  Contract: see the task statement; one JSON line on rank 0.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference] [--workload C3|C2|C4]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (config.workload): BASELINE.json config 3, the one its metric is quoted on --
-GUAVA training step, 100k-Gaussian 32-channel avatar at 512x512, forward + backward,
-16 views sharded over 8 GPUs => 2 views per GPU per step (weak scaling: N GPUs render
-2N views per step), followed for N > 1 by one NCCL all-reduce(sum) of the packed
-per-Gaussian parameter gradients [P,43] fp32.
+Workloads (config.workload), all synthetic (guava_renderer_b200/synthetic.py):
 
-A step = one pass of the hot path over one batch of views:
-  value : inputs (Gaussians, cameras, upstream dL/dcolor) resident in HBM; batched entry
-          (one launch chain for the rank's views) forward + backward (+ all-reduce);
-  e2e   : the same step through the public per-step call with HOST inputs: the step's
-          Gaussians [V,P,43] + cameras are copied from pinned host memory, and the
-          step's loss and gradient checksum are read back, inside the timed region.
-Synthetic data (guava_renderer_b200/synthetic.py); `views_sets` distinct
-input sets are rotated so that consecutive steps do not re-use L2-resident inputs
-(per-step working set ~230 MB > 126 MB L2).
+  C3 (default, the configuration BASELINE.json's metric is quoted on) -- GUAVA training step,
+      100k-Gaussian 32-channel avatar at 512x512, forward + backward, 16 views sharded over 8 GPUs
+      => 2 views per GPU per step (weak scaling: N GPUs render 2N views per step), followed for
+      N > 1 by one NCCL all-reduce(sum) of the packed per-Gaussian gradients [P,43] fp32.
+  C2  -- inference shape: 8 views x 100k Gaussians, 512x512, forward only, one launch chain (N = 1;
+      for N > 1 every rank renders its own 8 views: weak).
+  C4  -- cross-reenactment video: 300k Gaussians, 1024x1024, 240 frames, forward only, frames split
+      contiguously over the N ranks (strong scaling: the job is the 240 frames); the cloud is resident,
+      each frame has its own positions (base + 0.02 sin(2 pi f/240 + phi_i)); no cross-GPU traffic.
+
+A step = one pass of the hot path over one batch of views (C4: over the rank's share of the frames):
+  value : inputs (Gaussians, cameras, upstream dL/dcolor) resident in HBM;
+  e2e   : the same step through the public per-step call with HOST inputs: the step's inputs are copied
+          from pinned host memory, and the step's result (loss + gradient checksum, or an image checksum
+          for the forward-only workloads) is read back, inside the timed region.
+`--impl reference` runs the UNMODIFIED reference CUDA build (oracle/_ref) through its own Python API under
+the same sharding, inputs, loss recipe and collective; that arm imports nothing of the product.
+`views_sets` distinct input sets are rotated so that consecutive steps do not re-use L2-resident inputs.
 """
 from __future__ import annotations
 
 import argparse
+import importlib.util
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -37,80 +42,110 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-P_DEFAULT, H_DEFAULT, W_DEFAULT = 100_000, 512, 512
-VIEWS_PER_GPU = 2
 METRIC = "Mpix/s fwd+bwd, 32-ch 512x512 100k-Gaussian avatar"
 UNIT = "Mpix/s"
+
+WORKLOADS = {
+    # name: P, H, W, views per GPU and step, backward, scaling
+    "C3": dict(P=100_000, H=512, W=512, views=2, backward=True, scaling="weak", config_id=3),
+    "C2": dict(P=100_000, H=512, W=512, views=8, backward=False, scaling="weak", config_id=2),
+    "C4": dict(P=300_000, H=1024, W=1024, views=240, backward=False, scaling="strong", config_id=4),
+}
+C4_CHUNK = 8      # frames per launch chain
+
+
+def load_synthetic():
+    """guava_renderer_b200/synthetic.py loaded BY PATH: pure torch, and the reference arm must not import
+    the product package (its __init__ maps libguava_rasterizer_b200.so)."""
+    name = "_bench_synthetic"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "guava_renderer_b200", "synthetic.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def shard_views(num_views, rank, world):
+    """Contiguous blocks, as guava_renderer_b200.sharding.shard_views (restated: see load_synthetic)."""
+    base, rem = divmod(num_views, world)
+    start = rank * base + min(rank, rem)
+    return list(range(start, start + base + (1 if rank < rem else 0)))
 
 
 # ----------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled DURING the timed regions (NVML, ~1 ms period; the timed region of
+    the default run is tens of milliseconds, far below nvidia-smi's start-up time)."""
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.proc = None
-        self.lines = []
-
-    def start(self):
+        self.samples, self.reasons = [], set()
+        self.active = threading.Event()
+        self.stop_flag = False
+        self.h = None
+        self.max_mhz = None
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.t = threading.Thread(target=self._loop, daemon=True)
             self.t.start()
-        except Exception:
-            self.proc = None
+        except Exception as e:   # noqa: BLE001
+            self.err = repr(e)
+            self.h = None
 
-    def _read(self):
-        for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
-
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9:
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self.stop_flag:
+            if not self.active.wait(0.05):
                 continue
             try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = int(get_reasons(self.h))
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:   # noqa: BLE001
+                pass
+            time.sleep(0.001)
+
+    def begin(self):
+        self.active.set()
+
+    def end(self):
+        self.active.clear()
+
+    def result(self):
+        self.stop_flag = True
+        if self.h is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "?")],
+                    "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def smi_index(device_index):
+    cvd = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+    try:
+        return int(cvd.split(",")[device_index]) if cvd else device_index
+    except (ValueError, IndexError):
+        return device_index
 
 
 # ------------------------------------------------------------------- workload
-def build_inputs(config_id, P, H, W, views, num_views, n_sets, pin):
-    """n_sets distinct input sets for the rank's views; host tensors (optionally pinned)."""
-    from guava_renderer_b200 import synthetic
-    sets = []
-    for s in range(n_sets):
-        d = synthetic.make_views(config_id * 10 + s, P, H, W, views, num_views)
-        cams = torch.cat([d["viewmatrix"].reshape(len(views), 16), d["projmatrix"].reshape(len(views), 16)], 1).contiguous()
-        e = dict(xyz=d["xyz"], sc=d["scaling"], rot=d["rotation"], op=d["opacity"], feat=d["features_color"], cams=cams)
-        if pin:   # one pinned block per set (feat first: its rows must stay 16-byte aligned) -> one H2D copy per step
-            packed = torch.empty(sum(v.numel() for v in e.values())).pin_memory()
-            e = carve(packed, len(views), P, fill=e)
-            e["packed"] = packed
-        e.update(tanfovx=d["tanfovx"], tanfovy=d["tanfovy"], campos=d["campos"])
-        sets.append(e)
-    return sets
+PACK_ORDER = ("feat", "xyz", "sc", "rot", "op", "cams")
+TENSOR_KEYS = ("xyz", "sc", "rot", "op", "feat")      # [V,P,3|3|4|1|32] = 43 floats per Gaussian
+WIDTHS = dict(xyz=3, sc=3, rot=4, op=1, feat=32)
 
 
 def carve(packed, V, P, fill=None):
@@ -126,15 +161,76 @@ def carve(packed, V, P, fill=None):
     return out
 
 
-PACK_ORDER = ("feat", "xyz", "sc", "rot", "op", "cams")
-TENSOR_KEYS = ("xyz", "sc", "rot", "op", "feat")      # [V,P,3|3|4|1|32] = 43 floats per Gaussian
-WIDTHS = dict(xyz=3, sc=3, rot=4, op=1, feat=32)
+def build_inputs(config_id, P, H, W, views, num_views, n_sets, pin):
+    """n_sets distinct input sets for the rank's views; host tensors (optionally one pinned block per set)."""
+    synthetic = load_synthetic()
+    sets = []
+    for s in range(n_sets):
+        d = synthetic.make_views(config_id * 10 + s, P, H, W, views, num_views)
+        cams = torch.cat([d["viewmatrix"].reshape(len(views), 16), d["projmatrix"].reshape(len(views), 16)], 1).contiguous()
+        e = dict(xyz=d["xyz"], sc=d["scaling"], rot=d["rotation"], op=d["opacity"], feat=d["features_color"], cams=cams)
+        if pin:   # one pinned block per set (feat first: its rows must stay 16-byte aligned) -> one H2D copy per step
+            packed = torch.empty(sum(v.numel() for v in e.values())).pin_memory()
+            e = carve(packed, len(views), P, fill=e)
+            e["packed"] = packed
+        e.update(tanfovx=d["tanfovx"], tanfovy=d["tanfovy"], campos=d["campos"])
+        sets.append(e)
+    return sets
+
+
+def build_c4(P, H, W, frames, pin):
+    """C4: one resident cloud, per-frame positions base + 0.02 sin(2 pi f/240 + phi_i), a fixed
+    camera (render_motion.py:177-214).  Returns the shared tensors and the rank's [F,P,3] positions (host)."""
+    synthetic = load_synthetic()
+    c = synthetic.guava_cloud(P, 4000, 1.0)
+    g = torch.Generator().manual_seed(4001)
+    phi = torch.rand(P, 3, generator=g) * (2.0 * np.pi)
+    f = torch.tensor(frames, dtype=torch.float32).view(-1, 1, 1)
+    pos = (c["xyz"][None] + 0.02 * torch.sin(2.0 * np.pi * f / 240.0 + phi[None])).contiguous()
+    if pin:
+        pos = pos.pin_memory()
+    cam = synthetic.camera(0, 1, 1.0 / 24 * W / H, 1.0 / 24)
+    return c, pos, cam
 
 
 def upstream(V, H, W, device):
-    from guava_renderer_b200 import synthetic
+    synthetic = load_synthetic()
     gs = [synthetic.upstream_grads(H, W, 3000 + v)[0] for v in range(V)]
     return torch.stack(gs, 0).to(device)
+
+
+def workload_name(args):
+    wl = WORKLOADS[args.workload]
+    if args.workload == "C3":
+        return (f"C3 GUAVA training step: {args.P // 1000}k-Gaussian 32-ch avatar, {args.H}x{args.W}, fwd+bwd, "
+                f"{args.views_per_gpu} views/GPU/step (16 views over 8 GPUs), NCCL all-reduce of [P,43] grads for N>1")
+    if args.workload == "C2":
+        return (f"C2 GUAVA inference: {args.P // 1000}k-Gaussian 32-ch avatar, {args.H}x{args.W}, forward only, "
+                f"{args.views_per_gpu} views batched per GPU and step")
+    return (f"C4 cross-reenactment video: {args.P // 1000}k Gaussians, {args.H}x{args.W}, forward only, "
+            f"{wl['views']} frames split by frame over the GPUs, {C4_CHUNK} frames per launch chain")
+
+
+def config_of(args, world):
+    """The `config` object -- the SAME function for both arms, so the two lines carry identical dicts."""
+    wl = WORKLOADS[args.workload]
+    gv = wl["views"] if args.workload == "C4" else args.views_per_gpu * world
+    return {"workload": workload_name(args), "P": args.P, "H": args.H, "W": args.W,
+            "views_per_gpu": (wl["views"] // world if args.workload == "C4" else args.views_per_gpu),
+            "global_views_per_step": gv, "parallelism": f"view-sharded x{world}",
+            "l2": (f"inputs rotate over {args.view_sets} distinct view sets; per-step working set > 126 MB L2"
+                   if args.workload != "C4" else "every frame has its own positions; per-step working set > 126 MB L2")}
+
+
+def base_line(args, world, impl=None):
+    wl = WORKLOADS[args.workload]
+    line = {"metric": METRIC if args.workload == "C3" else METRIC + f" [workload {args.workload}: see config]",
+            "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+            "scaling": wl["scaling"], "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": config_of(args, world)}
+    if impl:
+        line["impl"] = impl
+    return line
 
 
 # -------------------------------------------------------------------- own arm
@@ -143,7 +239,11 @@ def run_own(args, rank, world, device):
     from guava_renderer_b200 import sharding
     import torch.distributed as dist
 
+    if args.workload != "C3":
+        return run_own_forward_only(args, rank, world, device)
+
     P, H, W, V = args.P, args.H, args.W, args.views_per_gpu
+    clocks = ClockSampler(smi_index(device.index))
     views = sharding.shard_views(V * world, rank, world)
     sets_host = build_inputs(3, P, H, W, views, V * world, args.view_sets, pin=True)
     dL = upstream(V, H, W, device)
@@ -285,11 +385,11 @@ def run_own(args, rank, world, device):
                                             b["cams"][:, 16:].reshape(V, 4, 4))
         m2 = torch.zeros(V, P, 3, device=device, requires_grad=True)
         color, radii, invd = grb.rasterize_gaussians_batch(leaves[0], m2, leaves[4], leaves[3], leaves[1], leaves[2], st)
-        loss = (color * dL).sum()
-        loss.backward()
+        loss = grb.graphed.image_dot(color.detach(), dL)
+        color.backward(dL)
         sharding.pack_gradients([l.grad for l in leaves], out=gbuf)
         sharding.allreduce_gradients(gbuf)
-        res = torch.stack([loss.detach(), gbuf.abs().sum()])
+        res = torch.stack([loss, gbuf.abs().sum()])
         result_host.copy_(res, non_blocking=True)
         return res
 
@@ -303,21 +403,16 @@ def run_own(args, rank, world, device):
         step_resident(i)
     join(0)
     barrier()
-    cvd = os.environ.get("CUDA_VISIBLE_DEVICES", "")
-    try:
-        smi_index = int(cvd.split(",")[device.index]) if cvd else device.index
-    except (ValueError, IndexError):
-        smi_index = device.index
-    clocks = ClockSampler(smi_index)
-    clocks.start()
     n0 = grb.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.begin()
     e0.record()
     for i in range(args.steps):
         step_resident(args.warmup + i)
     join(0)
     e1.record()
     barrier()
+    clocks.end()
     launches = grb.launch_count() - n0
     if graphed:   # replays do not pass through the library's launch counter: count what each replay launches
         launches = sum(g_res[(args.warmup + i) % len(g_res)].launches_per_replay for i in range(args.steps))
@@ -334,6 +429,7 @@ def run_own(args, rank, world, device):
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     del copy_times[:]
     t_wall0 = time.perf_counter()
+    clocks.begin()
     e2.record()
     for i in range(args.steps):
         k = args.warmup + i
@@ -344,10 +440,11 @@ def run_own(args, rank, world, device):
     e3.record()
     t_enq = (time.perf_counter() - t_wall0) * 1e3   # host time to enqueue the timed steps
     barrier()
+    clocks.end()
     _ = float(result_host[0])                 # the D2H result is consumed on the host
     t_wall = (time.perf_counter() - t_wall0) * 1e3
     ms_e2e = e2.elapsed_time(e3)
-    clk = clocks.stop()
+    clk = clocks.result()
     copy_stream.synchronize()
     ms_h2d_loaded = sum(a.elapsed_time(b) for a, b in copy_times) / max(len(copy_times), 1)
     if args.trace_e2e:
@@ -384,7 +481,7 @@ def run_own(args, rank, world, device):
             g.check()      # no replay overflowed its captured binning capacity
     grb.set_option("profile_stages", 0)
     stages = grb._lib_mod.stage_times()
-    roof = roofline_object(stages, sets_dev[0], tanfov, bg, dL, P, H, W, V, device)
+    roof = roofline_object(stages, sets_dev[0], tanfov, bg, P, H, W, V, device, backward=True)
 
     t = torch.tensor([ms_res, ms_e2e], device=device, dtype=torch.float64)
     if world > 1:
@@ -392,14 +489,174 @@ def run_own(args, rank, world, device):
     ms_res, ms_e2e = float(t[0]), float(t[1])
     pix = V * world * H * W * args.steps
     return dict(ms_res=ms_res, ms_e2e=ms_e2e, pix=pix, launches=int(launches), clocks=clk, roofline=roof,
-                h2d=h2d_bytes, d2h=d2h_bytes, stages={k: (v[0] / max(v[1], 1)) for k, v in stages.items()},
-                wall_ms_e2e=t_wall, enqueue_ms_e2e=t_enq, ms_h2d_alone=ms_h2d_alone, ms_h2d_loaded=ms_h2d_loaded)
+                h2d=h2d_bytes, d2h=d2h_bytes, wall_ms_e2e=t_wall, enqueue_ms_e2e=t_enq, ms_h2d_alone=ms_h2d_alone,
+                ms_h2d_loaded=ms_h2d_loaded,
+                step_call="eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)")
 
 
-def roofline_object(stages, s, tanfov, bg, dL, P, H, W, V, device):
+def run_own_forward_only(args, rank, world, device):
+    """C2 (8 views batched per step) and C4 (the rank's share of 240 frames per step, C4_CHUNK frames per launch
+    chain, one resident cloud with per-frame positions)."""
+    import guava_renderer_b200 as grb
+    import torch.distributed as dist
+    P, H, W = args.P, args.H, args.W
+    clocks = ClockSampler(smi_index(device.index))
+    result_host = torch.empty(1, dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream(device=device)
+
+    if args.workload == "C2":
+        V = args.views_per_gpu
+        views = shard_views(V * world, rank, world)
+        sets_host = build_inputs(2, P, H, W, views, V * world, args.view_sets, pin=True)
+        tanfov = torch.tensor([[sets_host[0]["tanfovx"], sets_host[0]["tanfovy"]]] * V, device=device)
+        bg = torch.zeros(V, 32, device=device)
+        NSTAGE = 3
+        stage = []
+        for i in range(NSTAGE):
+            packed = torch.empty(V * P * 43 + V * 32, device=device)
+            packed.copy_(sets_host[i % len(sets_host)]["packed"])
+            stage.append(dict(carve(packed, V, P), packed=packed, ev=torch.cuda.Event()))
+        steps_g = [grb.GraphedRenderStep(b["xyz"], b["feat"], b["op"], b["sc"], b["rot"],
+                                         grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0,
+                                                                        b["cams"][:, :16].reshape(V, 4, 4),
+                                                                        b["cams"][:, 16:].reshape(V, 4, 4)))
+                   for b in stage]
+        h2d_bytes, pix_per_step = V * P * 43 * 4 + V * 32 * 4, V * H * W
+        launches_per_step = steps_g[0].launches_per_replay
+
+        def prefetch(i):
+            b = stage[i % NSTAGE]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_stream(torch.cuda.current_stream(device))
+                b["packed"].copy_(sets_host[i % len(sets_host)]["packed"], non_blocking=True)
+                b["ev"].record(copy_stream)
+
+        def step(i, host_inputs):
+            if host_inputs:
+                torch.cuda.current_stream(device).wait_event(stage[i % NSTAGE]["ev"])
+            g = steps_g[i % NSTAGE]
+            g.replay()
+            if host_inputs:   # the step's result: an image checksum -> pinned host memory
+                result_host.copy_(g.color.view(-1)[::4099].sum().reshape(1), non_blocking=True)
+
+        def check():
+            for g in steps_g:
+                g.check()
+        prof_set = dict(xyz=stage[0]["xyz"], feat=stage[0]["feat"], op=stage[0]["op"], sc=stage[0]["sc"], rot=stage[0]["rot"],
+                        vm=stage[0]["cams"][:, :16].reshape(V, 4, 4), pm=stage[0]["cams"][:, 16:].reshape(V, 4, 4))
+        Vp = V
+    else:   # C4
+        frames = shard_views(WORKLOADS["C4"]["views"], rank, world)
+        c, pos_host, cam = build_c4(P, H, W, frames, pin=True)
+        F = len(frames)
+        V = C4_CHUNK
+        shared = {k: c[k].to(device) for k in ("scaling", "rotation", "opacity", "features_color")}
+        pos_dev = pos_host.to(device)                                   # [F,P,3] resident for `value`
+        pos_stage = [torch.empty(V, P, 3, device=device) for _ in range(3)]
+        stage_ev = [torch.cuda.Event() for _ in range(3)]
+        tanfov = torch.tensor([[cam["tanfovx"], cam["tanfovy"]]] * V, device=device)
+        bg = torch.zeros(V, 32, device=device)
+        vm = cam["viewmatrix"].to(device)[None].repeat(V, 1, 1).contiguous()
+        pm = cam["projmatrix"].to(device)[None].repeat(V, 1, 1).contiguous()
+        st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, vm, pm)
+        m2 = torch.zeros(V, P, 3, device=device)
+        nchunks = (F + V - 1) // V
+        h2d_bytes, pix_per_step = F * P * 12, F * H * W
+        acc = torch.zeros(1, device=device)
+
+        def render_chunk(xyz, n):
+            stn = st if n == V else grb.BatchRasterizationSettings(H, W, tanfov[:n], bg[:n], 1.0, vm[:n], pm[:n])
+            with torch.no_grad():
+                color, radii, invd = grb.rasterize_gaussians_batch(xyz[:n], m2[:n], shared["features_color"], shared["opacity"],
+                                                                   shared["scaling"], shared["rotation"], stn)
+            return color
+
+        n_before = grb.launch_count()
+        render_chunk(pos_dev[:V], min(V, F))
+        launches_per_step = (grb.launch_count() - n_before) * nchunks
+
+        def prefetch(i):
+            pass
+
+        def step(i, host_inputs):
+            acc.zero_()
+            for ch in range(nchunks):
+                n = min(V, F - ch * V)
+                if host_inputs:   # the chunk's positions from pinned host memory, double-buffered on the copy stream
+                    k = ch % 3
+                    with torch.cuda.stream(copy_stream):
+                        copy_stream.wait_stream(torch.cuda.current_stream(device))
+                        pos_stage[k][:n].copy_(pos_host[ch * V:ch * V + n], non_blocking=True)
+                        stage_ev[k].record(copy_stream)
+                    torch.cuda.current_stream(device).wait_event(stage_ev[k])
+                    color = render_chunk(pos_stage[k], n)
+                    acc.add_(color.view(-1)[::4099].sum())
+                else:
+                    render_chunk(pos_dev[ch * V:ch * V + n], n)
+            if host_inputs:
+                result_host.copy_(acc, non_blocking=True)
+
+        def check():
+            pass
+        prof_set = dict(xyz=pos_dev[:V], feat=shared["features_color"], op=shared["opacity"], sc=shared["scaling"],
+                        rot=shared["rotation"], vm=vm, pm=pm)
+        Vp = V
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    out = {}
+    for name, host_inputs in (("res", False), ("e2e", True)):
+        if host_inputs:
+            prefetch(0); prefetch(1)
+        for i in range(args.warmup):
+            if host_inputs:
+                prefetch(i + 2)
+            step(i, host_inputs)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks.begin()
+        e0.record()
+        for i in range(args.steps):
+            if host_inputs:
+                prefetch(args.warmup + i + 2)
+            step(args.warmup + i, host_inputs)
+        e1.record()
+        barrier()
+        clocks.end()
+        out[name] = e0.elapsed_time(e1)
+    _ = float(result_host[0])
+    check()
+    grb.set_option("profile_stages", 1)
+    grb._lib_mod.stage_times_reset()
+    with torch.no_grad():
+        for _ in range(3):
+            grb.rasterize_gaussians_batch(prof_set["xyz"], torch.zeros(Vp, P, 3, device=device), prof_set["feat"], prof_set["op"],
+                                          prof_set["sc"], prof_set["rot"],
+                                          grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, prof_set["vm"], prof_set["pm"]))
+    torch.cuda.synchronize(device)
+    grb.set_option("profile_stages", 0)
+    roof = roofline_object(grb._lib_mod.stage_times(), prof_set, tanfov, bg, P, H, W, Vp, device, backward=False)
+    t = torch.tensor([out["res"], out["e2e"]], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if args.workload == "C4":
+        pix = WORKLOADS["C4"]["views"] * H * W * args.steps        # the job: all 240 frames, whatever N is
+    else:
+        pix = pix_per_step * world * args.steps
+    return dict(ms_res=float(t[0]), ms_e2e=float(t[1]), pix=pix, launches=int(launches_per_step * args.steps),
+                clocks=clocks.result(), roofline=roof, h2d=h2d_bytes, d2h=4,
+                step_call=("guava_renderer_b200.GraphedRenderStep (CUDA graph replay)" if args.workload == "C2"
+                           else f"rasterize_gaussians_batch, {C4_CHUNK} frames per call, eager"))
+
+
+def roofline_object(stages, s, tanfov, bg, P, H, W, V, device, backward):
     """HBM roofline of the dominant kernel: algorithmic bytes per launch (SURVEY.md 8(d),
     DESIGN.md section 5) / average launch duration measured above with CUDA events."""
     import guava_renderer_b200 as grb
+    from guava_renderer_b200 import rasterizer as rz
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
@@ -407,39 +664,19 @@ def roofline_object(stages, s, tanfov, bg, dL, P, H, W, V, device):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     per_launch = {k: (ms / n if n else 0.0) for k, (ms, n) in stages.items()}
     dom = max(per_launch, key=lambda k: stages[k][0])
-    # measure R, Rc from the run's own buffers
+    # R, Rc from the run's own buffers: a forward whose three buffers are handed back
     st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, s["vm"], s["pm"])
-    from guava_renderer_b200.rasterizer import _RasterizeGaussiansBatch  # noqa: F401
-    m2 = torch.zeros(V, P, 3, device=device)
     with torch.no_grad():
-        color, radii, invd = grb.rasterize_gaussians_batch(s["xyz"], m2, s["feat"], s["op"], s["sc"], s["rot"], st)
-    # n_contrib lives in the image buffer; recompute Rc = sum over tiles of max n_contrib
-    # from a fresh forward through the _C-level call that hands the buffers back
-    import ctypes
-    from guava_renderer_b200 import rasterizer as rz
-    L = grb.buffer_layout(V, P, W, H, 0)
-    bufs = rz._CallBuffers(torch.device(device))
-    rz._tls.call = bufs
-    out_c = torch.empty(V, 32, H, W, device=device)
-    out_d = torch.empty(V, 1, H, W, device=device)
-    rad = torch.empty(V, P, dtype=torch.int32, device=device)
-    R = ctypes.c_int(0)
-    lib = grb._lib_mod.load()
-    feat = s["feat"].contiguous()
-    rc = lib.guava_rasterizer_forward_batch(
-        rz._ALLOC, rz._USER[0], rz._ALLOC, rz._USER[1], rz._ALLOC, rz._USER[2], V, P, bg.data_ptr(), W, H,
-        s["xyz"].data_ptr(), P * 3, feat.data_ptr(), P * 32, s["op"].data_ptr(), P, s["sc"].data_ptr(), P * 3, 1.0,
-        s["rot"].data_ptr(), P * 4, s["vm"].data_ptr(), s["pm"].data_ptr(), tanfov.data_ptr(), out_c.data_ptr(),
-        out_d.data_ptr(), 0, rad.data_ptr(), 0, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), ctypes.byref(R))
-    rz._tls.call = None
-    assert rc == 0, grb._lib_mod.last_error()
+        grb.rasterize_gaussians_batch(s["xyz"], torch.zeros(V, P, 3, device=device), s["feat"], s["op"], s["sc"], s["rot"], st)
     torch.cuda.synchronize()
-    img = bufs.bufs[2]
+    img = rz._tls.last_buffers[2]
+    L = grb.buffer_layout(V, P, W, H, 0)
     npix = V * H * W
+    hdr = img[L.num_rendered:L.num_rendered + 32].view(torch.int32)
+    Rtot = int(hdr[0].item())
     ncontrib = img[L.n_contrib:L.n_contrib + npix * 4].view(torch.int32).view(V, H // 16, 16, W // 16, 16)
     Rc = int(ncontrib.amax(dim=(2, 4)).sum().item())
     pairs = int(ncontrib.sum().item())
-    Rtot = int(R.value)
     Nt = V * (H // 16) * (W // 16)
     n = V * P
     alg = {
@@ -472,113 +709,206 @@ def roofline_object(stages, s, tanfov, bg, dL, P, H, W, V, device):
 
 
 # ------------------------------------------------------------- cpu baseline
-def cpu_baseline(P, H, W, max_views=2):
-    """The oracle port (C + OpenMP, all host threads) on a bounded sample of the same workload."""
+def cpu_baseline(args, max_views=2):
+    """The oracle port (C + OpenMP, all host threads) on a bounded sample of the same workload.  The reference
+    ships no CPU rasterizer (BASELINE.json); this is the CPU restatement of its equations, kind "port"."""
     import oracle
-    from guava_renderer_b200 import synthetic
+    synthetic = load_synthetic()
+    P, H, W = args.P, args.H, args.W
+    backward = WORKLOADS[args.workload]["backward"]
     oracle.build()
     cores = oracle.num_threads()
-    d = synthetic.make_views(3, P, H, W, list(range(max_views)), 16)
+    d = synthetic.make_views(WORKLOADS[args.workload]["config_id"], P, H, W, list(range(max_views)), 16)
     t0 = time.perf_counter()
     for v in range(max_views):
         f = oracle.forward(d["xyz"][v].numpy(), d["features_color"][v].numpy(), d["opacity"][v].numpy(),
                            d["scaling"][v].numpy(), d["rotation"][v].numpy(), d["viewmatrix"][v].numpy(),
                            d["projmatrix"][v].numpy(), d["tanfovx"], d["tanfovy"], H, W, np.zeros(32, np.float32))
-        dc, di = synthetic.upstream_grads(H, W, 3000 + v)
-        oracle.backward(f, dc.numpy(), di.numpy())
+        if backward:
+            dc, di = synthetic.upstream_grads(H, W, 3000 + v)
+            oracle.backward(f, dc.numpy(), di.numpy())
     dt = time.perf_counter() - t0
     return {"value": round(max_views * H * W / dt / 1e6, 4), "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{max_views} views of the bench workload (P={P}, {H}x{W}, fwd+bwd), oracle/splat_oracle.c with OpenMP"}
+            "sample": f"{max_views} views of the bench workload (P={P}, {H}x{W}, {'fwd+bwd' if backward else 'fwd'}), "
+                      "oracle/splat_oracle.c with OpenMP"}
 
 
 # --------------------------------------------------------- reference arm
-def run_reference(args, rank, world):
-    """Reference arm.  The reference ships no CPU rasterizer (BASELINE.json), so "the reference's own
-    implementation of the path" is its CUDA extension: when oracle/_ref (the unmodified build) loads and a
-    GPU is visible, rank 0 times it through its own Python API with the per-view loop of
-    models/UbodyAvatar/gaussian_render.py:37-67, host inputs copied in and the loss read back each step
-    (the same e2e recipe as the own arm).  Otherwise the CPU oracle port is timed."""
-    if rank != 0:
+def import_reference():
+    """The unmodified reference build (oracle/_ref) by path, or None when it has not been built."""
+    d = os.path.join(ROOT, "oracle", "_ref", "diff_gaussian_rasterization_32")
+    if not os.path.isfile(os.path.join(d, "_C.so")):
         return None
-    from tests import util
-    P, H, W, V = args.P, args.H, args.W, args.views_per_gpu
-    ref = util.import_reference() if torch.cuda.is_available() else None
-    cpu = cpu_baseline(P, H, W, max_views=2)
-    base = {"metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "impl": "reference",
-            "config": {"workload": workload_name(args), "P": P, "H": H, "W": W, "views_per_gpu": V}}
+    spec = importlib.util.spec_from_file_location("ref_diff_gaussian_rasterization_32", os.path.join(d, "__init__.py"),
+                                                  submodule_search_locations=[d])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ref_diff_gaussian_rasterization_32"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def run_reference(args, rank, world, local_rank):
+    """Reference arm.  The reference ships no CPU rasterizer (BASELINE.json), so "the reference's own
+    implementation of the path" is its CUDA extension: when oracle/_ref (the unmodified build) loads and a GPU
+    is visible, EVERY rank times it through its own Python API with the per-view loop of
+    models/UbodyAvatar/gaussian_render.py:37-67 under the same view sharding, the same loss recipe
+    (backward(dL) + a dot product for the value) and -- N > 1 -- one all-reduce of the [P,43] gradients per
+    step, as its trainer's DDP step does (main/trainer.py:40-43,95).  `value` = inputs resident, `e2e` = host
+    inputs copied in and the result read back every step (the own arm's meanings).  Without a GPU or the
+    build, rank 0 times the CPU oracle port.  Nothing of the product is imported here."""
+    ref = import_reference() if torch.cuda.is_available() else None
+    base = base_line(args, world, impl="reference")
+    P, H, W = args.P, args.H, args.W
+    wl = WORKLOADS[args.workload]
     if ref is None:
+        if rank != 0:
+            return None
+        cpu = cpu_baseline(args, max_views=2)
         v = cpu["value"]
-        base.update(value=v, ms_per_step=round(V * H * W / (v * 1e6) * 1e3, 3), cpu_baseline=cpu,
-                    e2e={"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        base.update(value=v, ms_per_step=round(config_of(args, world)["global_views_per_step"] * H * W / (v * 1e6) * 1e3, 3),
+                    cpu_baseline=cpu, e2e={"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     reference_kind="oracle port on host cores (reference CUDA build not loadable here)")
         return base
 
-    device = torch.device("cuda:0")
-    sets_host = build_inputs(3, P, H, W, list(range(V)), V * world, args.view_sets, pin=True)
-    dL = upstream(V, H, W, device)
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    clocks = ClockSampler(smi_index(device.index))
+    backward = wl["backward"]
     bgv = torch.zeros(32, device=device)
-    stage = [dict({k: torch.empty(V, P, WIDTHS[k], device=device) for k in TENSOR_KEYS},
-                  cams=torch.empty(V, 32, device=device)) for _ in range(2)]
-    result_host = torch.empty(1, dtype=torch.float32).pin_memory()
+    result_host = torch.empty(2, dtype=torch.float32).pin_memory()
 
-    def step(i, host_inputs):
-        b = stage[i % 2]
-        s = sets_host[i % len(sets_host)]
-        if host_inputs:
-            for k in TENSOR_KEYS + ("cams",):
-                b[k].copy_(s[k], non_blocking=True)
-        leaves = [b[k].detach().requires_grad_(True) for k in TENSOR_KEYS]
-        mean_2d = torch.zeros(V, P, 3, device=device, requires_grad=True)
-        imgs = []
-        for bi in range(V):          # gaussian_render.py:37-67
-            rs = ref.GaussianRasterizationSettings(
-                image_height=H, image_width=W, tanfovx=s["tanfovx"], tanfovy=s["tanfovy"], bg=bgv, scale_modifier=1.0,
-                viewmatrix=b["cams"][bi, :16].reshape(4, 4), projmatrix=b["cams"][bi, 16:].reshape(4, 4), sh_degree=0,
-                campos=s["campos"][bi].to(device), prefiltered=False, debug=False, antialiasing=False)
-            img, radii, depth = ref.GaussianRasterizer_32(raster_settings=rs)(
-                means3D=leaves[0][bi], means2D=mean_2d[bi], shs=None, colors_precomp=leaves[4][bi],
-                opacities=leaves[3][bi], scales=leaves[1][bi], rotations=leaves[2][bi], cov3D_precomp=None)
-            imgs.append(img)
-        color = torch.stack(imgs, 0)
-        loss = (color * dL).sum()
-        loss.backward()
-        if host_inputs:
-            result_host.copy_(loss.detach().reshape(1), non_blocking=True)
+    if args.workload == "C4":
+        frames = shard_views(wl["views"], rank, world)
+        c, pos_host, cam = build_c4(P, H, W, frames, pin=True)
+        F = len(frames)
+        shared = {k: c[k].to(device) for k in ("scaling", "rotation", "opacity", "features_color")}
+        pos_dev = pos_host.to(device)
+        pos_stage = [torch.empty(C4_CHUNK, P, 3, device=device) for _ in range(2)]
+        rs = ref.GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], bg=bgv, scale_modifier=1.0,
+            viewmatrix=cam["viewmatrix"].to(device), projmatrix=cam["projmatrix"].to(device), sh_degree=0,
+            campos=cam["campos"].to(device), prefiltered=False, debug=False, antialiasing=False)
+        rast = ref.GaussianRasterizer_32(raster_settings=rs)
+        m2 = torch.zeros(P, 3, device=device)
+        h2d, d2h = F * P * 12, 4
+        pix_per_step = None
+        acc = torch.zeros(1, device=device)
+
+        def step(i, host_inputs):
+            acc.zero_()
+            with torch.no_grad():
+                for f0 in range(0, F, C4_CHUNK):          # main/test.py:70-74: one frame after the other
+                    n = min(C4_CHUNK, F - f0)
+                    if host_inputs:
+                        buf = pos_stage[(f0 // C4_CHUNK) % 2]
+                        buf[:n].copy_(pos_host[f0:f0 + n], non_blocking=True)
+                    else:
+                        buf = pos_dev[f0:f0 + n]
+                    for j in range(n):
+                        img, radii, depth = rast(means3D=buf[j], means2D=m2, shs=None, colors_precomp=shared["features_color"],
+                                                 opacities=shared["opacity"], scales=shared["scaling"],
+                                                 rotations=shared["rotation"], cov3D_precomp=None)
+                        if host_inputs:
+                            acc.add_(img.view(-1)[::4099].sum())
+            if host_inputs:
+                result_host[:1].copy_(acc, non_blocking=True)
+    else:
+        V = args.views_per_gpu
+        views = shard_views(V * world, rank, world)
+        sets_host = build_inputs(wl["config_id"], P, H, W, views, V * world, args.view_sets, pin=True)
+        dL = upstream(V, H, W, device) if backward else None
+        stage = [dict({k: torch.empty(V, P, WIDTHS[k], device=device) for k in TENSOR_KEYS},
+                      cams=torch.empty(V, 32, device=device)) for _ in range(2)]
+        campos_dev = [s["campos"].to(device) for s in sets_host]          # moved once, outside the step
+        gbuf = torch.zeros(P, 43, device=device)
+        h2d, d2h = V * P * 43 * 4 + V * 32 * 4, (8 if backward else 4)
+
+        def step(i, host_inputs):
+            b = stage[i % 2]
+            si = i % len(sets_host)
+            s = sets_host[si]
+            if host_inputs:
+                for k in TENSOR_KEYS + ("cams",):
+                    b[k].copy_(s[k], non_blocking=True)
+            leaves = [b[k].detach().requires_grad_(backward) for k in TENSOR_KEYS]
+            mean_2d = torch.zeros(V, P, 3, device=device, requires_grad=backward)
+            imgs = []
+            with torch.set_grad_enabled(backward):
+                for bi in range(V):          # gaussian_render.py:37-67
+                    rs = ref.GaussianRasterizationSettings(
+                        image_height=H, image_width=W, tanfovx=s["tanfovx"], tanfovy=s["tanfovy"], bg=bgv, scale_modifier=1.0,
+                        viewmatrix=b["cams"][bi, :16].reshape(4, 4), projmatrix=b["cams"][bi, 16:].reshape(4, 4), sh_degree=0,
+                        campos=campos_dev[si][bi], prefiltered=False, debug=False, antialiasing=False)
+                    img, radii, depth = ref.GaussianRasterizer_32(raster_settings=rs)(
+                        means3D=leaves[0][bi], means2D=mean_2d[bi], shs=None, colors_precomp=leaves[4][bi],
+                        opacities=leaves[3][bi], scales=leaves[1][bi], rotations=leaves[2][bi], cov3D_precomp=None)
+                    imgs.append(img)
+                color = torch.stack(imgs, 0)   # gaussian_render.py:70 -- part of the reference's own loop
+            if not backward:
+                if host_inputs:
+                    result_host[:1].copy_(color.view(-1)[::4099].sum().reshape(1), non_blocking=True)
+                return
+            # the own arm's loss recipe: loss value = <color, dL> as one dot product, dL handed straight to backward
+            loss = torch.dot(color.detach().view(-1), dL.view(-1))
+            color.backward(dL)
+            torch.cat([leaves[0].grad.sum(0), leaves[1].grad.sum(0), leaves[2].grad.sum(0), leaves[3].grad.sum(0),
+                       leaves[4].grad.sum(0)], dim=1, out=gbuf)
+            if world > 1:
+                dist.all_reduce(gbuf)          # what DDP does inside fabric.backward (main/trainer.py:95)
+            if host_inputs:
+                result_host.copy_(torch.stack([loss, torch.linalg.vector_norm(gbuf.view(-1), 1)]), non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
 
     out = {}
     for name, host_inputs in (("resident", False), ("e2e", True)):
-        for i in range(2):   # make sure both staging buffers hold data for the resident pass
-            for k in TENSOR_KEYS + ("cams",):
-                stage[i][k].copy_(sets_host[i % len(sets_host)][k])
+        if args.workload != "C4":
+            for i in range(2):   # both staging buffers hold data for the resident pass
+                for k in TENSOR_KEYS + ("cams",):
+                    stage[i][k].copy_(sets_host[i % len(sets_host)][k])
         for i in range(args.warmup):
             step(i, host_inputs)
-        torch.cuda.synchronize()
+        barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks.begin()
         e0.record()
         for i in range(args.steps):
             step(args.warmup + i, host_inputs)
         e1.record()
-        torch.cuda.synchronize()
+        barrier()
+        clocks.end()
         out[name] = e0.elapsed_time(e1)
-    pix = V * H * W * args.steps
-    v_e2e = pix / (out["e2e"] * 1e-3) / 1e6
-    v_res = pix / (out["resident"] * 1e-3) / 1e6
-    h2d = V * P * 43 * 4 + V * 32 * 4
-    base.update(value=round(v_e2e, 2), ms_per_step=round(out["e2e"] / args.steps, 4),
-                value_resident=round(v_res, 2), ms_per_step_resident=round(out["resident"] / args.steps, 4),
-                timed="e2e: pinned-host inputs copied in and the loss read back every step, same recipe as the own arm's e2e",
-                reference_kind="unmodified reference CUDA build (oracle/_ref) through its own Python API, per-view loop; "
-                               "single GPU (the reference's inference/render path is single-GPU, main/test.py:229-230)",
-                cpu_baseline={**cpu, "kind": "port"},
-                e2e={"value": round(v_e2e, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4})
+    _ = float(result_host[0])
+    t = torch.tensor([out["resident"], out["e2e"]], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    ms_res, ms_e2e = float(t[0]), float(t[1])
+    gv = config_of(args, world)["global_views_per_step"]
+    pix = gv * H * W * args.steps
+    v_res, v_e2e = pix / (ms_res * 1e-3) / 1e6, pix / (ms_e2e * 1e-3) / 1e6
+    base.update(value=round(v_res, 2), ms_per_step=round(ms_res / args.steps, 4),
+                e2e={"value": round(v_e2e, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                     "ms_per_step": round(ms_e2e / args.steps, 4)},
+                clocks=clocks.result(),
+                notes={"reference_kind": "unmodified reference CUDA build (oracle/_ref) through its own Python API, per-view "
+                                         "loop + torch.stack of gaussian_render.py:37-70, one process per GPU under the own "
+                                         "arm's view sharding" + (", dist.all_reduce of the [P,43] gradients" if backward else ""),
+                       "loss_recipe": "torch.dot(color, dL) for the value + color.backward(dL)" if backward else "forward only",
+                       "timed": "value: inputs resident; e2e: pinned-host inputs copied in and the result read back every step"})
+    if world == 1:
+        base["cpu_baseline"] = cpu_baseline(args, max_views=2)
     return base
-
-
-def workload_name(args):
-    return (f"C3 GUAVA training step: {args.P // 1000}k-Gaussian 32-ch avatar, {args.H}x{args.W}, fwd+bwd, "
-            f"{args.views_per_gpu} views/GPU/step (16 views over 8 GPUs), NCCL all-reduce of [P,43] grads for N>1")
 
 
 def main():
@@ -587,10 +917,11 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
-    ap.add_argument("--P", type=int, default=P_DEFAULT)
-    ap.add_argument("--H", type=int, default=H_DEFAULT)
-    ap.add_argument("--W", type=int, default=W_DEFAULT)
-    ap.add_argument("--views-per-gpu", type=int, default=VIEWS_PER_GPU)
+    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--P", type=int, default=None)
+    ap.add_argument("--H", type=int, default=None)
+    ap.add_argument("--W", type=int, default=None)
+    ap.add_argument("--views-per-gpu", type=int, default=None)
     ap.add_argument("--view-sets", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--trace-e2e", default="", help="write device timestamps of the e2e steps' phases to PATH.rank<r>.json")
@@ -598,13 +929,18 @@ def main():
     ap.add_argument("--eager", action="store_true", help="enqueue every step op by op instead of replaying CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    wl = WORKLOADS[args.workload]
+    args.P = args.P or wl["P"]
+    args.H = args.H or wl["H"]
+    args.W = args.W or wl["W"]
+    args.views_per_gpu = args.views_per_gpu or (wl["views"] if args.workload != "C4" else C4_CHUNK)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
     if args.impl == "reference":
-        line = run_reference(args, rank, world)
+        line = run_reference(args, rank, world, local_rank)
         if line is not None:
             print(json.dumps(line), flush=True)
         return
@@ -624,27 +960,22 @@ def main():
     if rank == 0:
         value = r["pix"] / (r["ms_res"] * 1e-3) / 1e6
         e2e = r["pix"] / (r["ms_e2e"] * 1e-3) / 1e6
-        line = {
-            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(r["ms_res"] / args.steps, 4), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": workload_name(args), "P": args.P, "H": args.H, "W": args.W,
-                       "views_per_gpu": args.views_per_gpu, "global_views_per_step": args.views_per_gpu * world,
-                       "parallelism": f"view-sharded x{world}",
-                       "host_numa_bind": (f"rank 0 pinned to {len(numa_cpus)} CPUs local to its GPU" if numa_cpus else "none"),
-                       "step_call": "eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)",
-                       "l2": f"inputs rotate over {args.view_sets} distinct view sets; per-step working set ~230 MB > 126 MB L2"},
+        line = base_line(args, world)
+        line.update({
+            "value": round(value, 2), "ms_per_step": round(r["ms_res"] / args.steps, 4),
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "ms_per_step": round(r["ms_e2e"] / args.steps, 4),
-                    "host_enqueue_ms_per_step": round(r["enqueue_ms_e2e"] / args.steps, 4),
-                    "h2d_ms_alone": round(r["ms_h2d_alone"], 4),
-                    "h2d_ms_under_kernels": round(r["ms_h2d_loaded"], 4)},
+                    "ms_per_step": round(r["ms_e2e"] / args.steps, 4)},
             "gpu_launches": r["launches"],
             "clocks": r["clocks"],
             "roofline": r["roofline"],
-        }
+            "notes": {"step_call": r["step_call"],
+                      "host_numa_bind": (f"rank 0 pinned to {len(numa_cpus)} CPUs local to its GPU" if numa_cpus else "none")},
+        })
+        if "enqueue_ms_e2e" in r:
+            line["e2e"].update(host_enqueue_ms_per_step=round(r["enqueue_ms_e2e"] / args.steps, 4),
+                               h2d_ms_alone=round(r["ms_h2d_alone"], 4), h2d_ms_under_kernels=round(r["ms_h2d_loaded"], 4))
         if not args.no_cpu_baseline and world == 1:   # rank 0 at N = 1 only
-            line["cpu_baseline"] = cpu_baseline(args.P, args.H, args.W, max_views=2)
+            line["cpu_baseline"] = cpu_baseline(args, max_views=2)
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist

@@ -22,12 +22,12 @@ EXPORTS = (
     "guava_rasterizer_forward_batch",
     "guava_rasterizer_backward_batch",
     "guava_pack_view_gradients",
-    "guava_rasterizer_set_refiner_output",
-    "guava_rasterizer_set_status_words",
     "guava_image_dot",
+    "guava_selftest_cull",
     "guava_deform_gaussians_forward",
     "guava_deform_gaussians_backward",
     "guava_buffer_layout",
+    "guava_buffer_layout_of_call",
     "guava_set_option",
     "guava_get_option",
     "guava_launch_count",
@@ -50,6 +50,15 @@ class Layout(Structure):
         "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "tile_order", "num_rendered",
         "binning_bytes", "point_list", "keys_unsorted", "keys_sorted",
         "point_offsets", "os_vals_alt", "os_scratch")]
+
+
+class CallOptions(Structure):
+    """guava_call_options (include/guava_rasterizer.h): per-call options of the batched entry."""
+    _fields_ = [("struct_size", c_size_t), ("refiner_output_nhwc_bf16", c_void_p), ("status_words", c_void_p),
+                ("no_host_wait", c_int)]
+
+    def __init__(self, refiner_output=0, status_words=0, no_host_wait=False):
+        super().__init__(ctypes.sizeof(CallOptions), refiner_output or None, status_words or None, int(bool(no_host_wait)))
 
 
 class GuavaLibraryError(RuntimeError):
@@ -92,7 +101,7 @@ def load() -> ctypes.CDLL:
         ALLOC_FN, P, ALLOC_FN, P, ALLOC_FN, P,
         c_int, c_int, P, c_int, c_int,
         P, c_size_t, P, c_size_t, P, c_size_t, P, c_size_t, c_float, P, c_size_t,
-        P, P, P, P, P, c_int, P, c_int, P, POINTER(c_int)]
+        P, P, P, P, P, c_int, P, c_int, P, POINTER(c_int), POINTER(CallOptions)]
     lib.guava_rasterizer_backward_batch.restype = c_int
     lib.guava_rasterizer_backward_batch.argtypes = [
         c_int, c_int, c_int, P, c_int, c_int,
@@ -102,18 +111,19 @@ def load() -> ctypes.CDLL:
         c_int, c_int, P]
     lib.guava_pack_view_gradients.restype = c_int
     lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]
-    lib.guava_rasterizer_set_refiner_output.restype = c_int
-    lib.guava_rasterizer_set_refiner_output.argtypes = [P]
     lib.guava_image_dot.restype = c_int
     lib.guava_image_dot.argtypes = [P, P, c_size_t, P, P]
-    lib.guava_rasterizer_set_status_words.restype = c_int
-    lib.guava_rasterizer_set_status_words.argtypes = [P]
     lib.guava_deform_gaussians_forward.restype = c_int
     lib.guava_deform_gaussians_forward.argtypes = [c_int] * 4 + [P] * 21
     lib.guava_deform_gaussians_backward.restype = c_int
     lib.guava_deform_gaussians_backward.argtypes = [c_int] * 4 + [P] * 12
     lib.guava_buffer_layout.restype = c_int
     lib.guava_buffer_layout.argtypes = [c_int, c_int, c_int, c_int, c_size_t, POINTER(Layout)]
+    lib.guava_selftest_cull.restype = c_int
+    lib.guava_selftest_cull.argtypes = [c_int, P, P, P, P, P]
+    lib.guava_buffer_layout_of_call.restype = c_int
+    lib.guava_buffer_layout_of_call.argtypes = [P, c_int, c_int, c_int, c_int, P, POINTER(Layout), POINTER(c_int),
+                                                POINTER(c_int), POINTER(c_size_t)]
     lib.guava_set_option.restype = c_int
     lib.guava_set_option.argtypes = [c_char_p, c_longlong]
     lib.guava_get_option.restype = c_longlong
@@ -171,6 +181,16 @@ def stage_times_reset() -> None:
 
 def version() -> str:
     return load().guava_version().decode()
+
+
+def buffer_layout_of_call(image_buffer_ptr: int, V: int, P: int, W: int, H: int, stream: int = 0):
+    """(Layout, sort_mode, block_masks, capacity) of a finished forward call, read from its image buffer's header."""
+    L, mode, masks, cap = Layout(), c_int(0), c_int(0), c_size_t(0)
+    rc = load().guava_buffer_layout_of_call(image_buffer_ptr, V, P, W, H, stream, ctypes.byref(L), ctypes.byref(mode),
+                                            ctypes.byref(masks), ctypes.byref(cap))
+    if rc != GUAVA_OK:
+        raise ValueError(last_error())
+    return L, int(mode.value), int(masks.value), int(cap.value)
 
 
 def buffer_layout(V: int, P: int, W: int, H: int, capacity: int = 0) -> Layout:

@@ -31,13 +31,23 @@ static thread_local std::string t_last_error;
 static std::atomic<long long> g_opt_emit_sorted_keys{0};
 static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
-static std::atomic<long long> g_opt_async_forward{0};
 static std::atomic<long long> g_opt_scalar_red{1};   // 1: 4-byte reductions from all 32 lanes (measured faster than gathering 16-byte vectors, profiles/r01_v43)
 static std::atomic<long long> g_opt_block_masks{0};   // experimental, see BLOCK_MASK_SHIFT (internal.cuh)
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
-static thread_local void* t_refiner_output = nullptr;   // consumed by the next forward call of this thread
-static thread_local uint32_t* t_status_host = nullptr;  // caller's pinned status words, consumed likewise
+// Number of SMs of the current device (grids of the persistent kernels are multiples of it); cached per ordinal.
+int sm_count()
+{
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    int n = cached[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
 
 static int fail(int code, const std::string& msg)
 {
@@ -218,6 +228,8 @@ __global__ void reset_cursor_kernel(int n, const uint2* __restrict__ ranges, uin
     if (i == 0) {
         num_rendered[1] = ((unsigned long long)num_rendered[0] > capacity) ? 1u : 0u;
         num_rendered[2] = 0u;
+        num_rendered[6] = (uint32_t)capacity;           // header: the capacity this call's binning buffer has now
+        num_rendered[7] = (uint32_t)(capacity >> 32);
     }
 }
 
@@ -341,14 +353,14 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
                         guava_alloc_fn binningBuffer, void* binning_user,
                         guava_alloc_fn imageBuffer, void* image_user,
                         Inputs in, float* out_color, float* out_invdepth, int* radii,
-                        int debug, cudaStream_t stream, int* num_rendered)
+                        int debug, cudaStream_t stream, int* num_rendered, const guava_call_options* co)
 {
     if (num_rendered) *num_rendered = 0;
-    in.aux_nhwc_bf16 = t_refiner_output;
+    if (co != nullptr && co->struct_size != sizeof(guava_call_options))
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "guava_call_options::struct_size does not match this library");
+    in.aux_nhwc_bf16 = co ? co->refiner_output_nhwc_bf16 : nullptr;
     const int block_masks = g_opt_block_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;
-    t_refiner_output = nullptr;
-    uint32_t* const status_host = t_status_host;
-    t_status_host = nullptr;
+    uint32_t* const status_host = co ? (uint32_t*)co->status_words : nullptr;
     if (((uintptr_t)status_host & 7) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");
     if (((uintptr_t)in.aux_nhwc_bf16 & 15) != 0)
@@ -373,7 +385,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     const size_t n = (size_t)in.V * in.P;
     const bool emit_keys = g_opt_emit_sorted_keys.load() != 0;
     const bool exact = g_opt_exact_binning.load() != 0;
-    const bool async_fwd = g_opt_async_forward.load() != 0 && !exact;
+    const bool async_fwd = co != nullptr && co->no_host_wait != 0 && !exact;
     // "sort_mode": 0 = tile buckets, 1 = global onesweep sort, -1 (default) = by the longest tile list the
     // previous call of this shape produced: lists beyond the register-resident bucket sort (2048) are where
     // the onesweep passes win (measured: profiles/r01_v9_sort_modes.jsonl).  Results are identical.
@@ -442,7 +454,8 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         if (est != 0 && est <= tile_sort_small_limit() * 3 / 4) with_large = false;
     }
     launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap,
-                     with_large ? 0xFFFFFFFFu : tile_sort_small_limit(), stream);
+                     with_large ? 0xFFFFFFFFu : tile_sort_small_limit(),
+                     (uint32_t)sort_mode | ((uint32_t)block_masks << 8) | ((uint32_t)emit_keys << 16), stream);
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 
@@ -471,6 +484,8 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         have_R = true;
         cap = R;
         compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
+        const unsigned long long cap64 = (unsigned long long)cap;   // header words [6], [7] (the scan saw "unbounded")
+        GUAVA_CUDA(cudaMemcpyAsync(im.num_rendered + 6, &cap64, 8, cudaMemcpyHostToDevice, stream));
     }
     char* bin = binningBuffer(binning_user, L.binning_bytes ? L.binning_bytes : 256);
     if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
@@ -542,6 +557,10 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
     if (dL_invdepths != nullptr && dL_dinvdepth == nullptr)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "dL_dinvdepth buffer missing");
+    if (((uintptr_t)dL_drot & 15) != 0)   // written with one 16-byte store per Gaussian
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "dL_drot must be 16-byte aligned");
+    if (((uintptr_t)in.colors & 15) || ((in.colors_vs * sizeof(float)) & 15))
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "colors_precomp must be 16-byte aligned");
     in.gx = (in.W + TILE_X - 1) / TILE_X;
     in.gy = (in.H + TILE_Y - 1) / TILE_Y;
     in.tiles = in.gx * in.gy;
@@ -575,7 +594,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     timer.end();
     GUAVA_STAGE("render_backward", debug);
     timer.begin(6);
-    launch_preprocess_backward(in, g, radii, dL_invdepths != nullptr, dL_dmean2D, dL_dconic, dL_dinvdepth,
+    launch_preprocess_backward(in, g, im.num_rendered, radii, dL_invdepths != nullptr, dL_dmean2D, dL_dconic, dL_dinvdepth,
                                dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot, stream);
     timer.end();
     GUAVA_STAGE("preprocess_backward", debug);
@@ -611,7 +630,7 @@ int guava_rasterizer_forward(
     in.tan_fov_dev = nullptr; in.tan_fovx = tan_fovx; in.tan_fovy = tan_fovy;
     in.background = background; in.antialiasing = antialiasing; in.prefiltered = prefiltered;
     return forward_impl(geometryBuffer, geometry_user, binningBuffer, binning_user, imageBuffer, image_user, in,
-                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered);
+                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered, nullptr);
 }
 
 int guava_rasterizer_backward(
@@ -662,7 +681,7 @@ int guava_rasterizer_forward_batch(
     const float* opacities, size_t opacities_view_stride, const float* scales, size_t scales_view_stride,
     float scale_modifier, const float* rotations, size_t rotations_view_stride, const float* viewmatrix,
     const float* projmatrix, const float* tan_fov, float* out_color, float* out_invdepth, int antialiasing,
-    int* radii, int debug, void* stream, int* num_rendered)
+    int* radii, int debug, void* stream, int* num_rendered, const guava_call_options* options)
 {
     if (!geometryBuffer || !binningBuffer || !imageBuffer)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null allocator");
@@ -680,7 +699,7 @@ int guava_rasterizer_forward_batch(
     in.tan_fov_dev = tan_fov; in.tan_fovx = 0.f; in.tan_fovy = 0.f;
     in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
     return forward_impl(geometryBuffer, geometry_user, binningBuffer, binning_user, imageBuffer, image_user, in,
-                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered);
+                        out_color, out_invdepth, radii, debug, (cudaStream_t)stream, num_rendered, options);
 }
 
 int guava_rasterizer_backward_batch(
@@ -723,7 +742,8 @@ int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const floa
     if (!dL_dmeans3D || !dL_dscales || !dL_drotations || !dL_dopacity || !dL_dcolors || !packed)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
     const size_t want = ((size_t)P + 31) / 32;                     // 8 warps x 4 rows per block and pass
-    const unsigned grid = (unsigned)(want < 148u * 8u ? want : 148u * 8u);
+    const size_t full = (size_t)sm_count() * 8u;
+    const unsigned grid = (unsigned)(want < full ? want : full);
     cudaStream_t st = (cudaStream_t)stream;
 #define GUAVA_PACK(VT) pack_view_gradients_kernel<VT><<<grid, 256, 0, st>>>(V, P, dL_dmeans3D, dL_dscales, dL_drotations, \
                                                                             dL_dopacity, dL_dcolors, packed)
@@ -751,22 +771,42 @@ int guava_image_dot(const float* a, const float* b, size_t n, float* out64, void
     return GUAVA_OK;
 }
 
-int guava_rasterizer_set_status_words(void* pinned_host_u32x2)
-{
-    t_status_host = (uint32_t*)pinned_host_u32x2;
-    return GUAVA_OK;
-}
-
-int guava_rasterizer_set_refiner_output(void* out_color_nhwc_bf16)
-{
-    t_refiner_output = out_color_nhwc_bf16;
-    return GUAVA_OK;
-}
-
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout* out)
 {
     if (!out || V < 0 || P < 0 || width <= 0 || height <= 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "bad layout query");
     compute_layout(V, P, width, height, capacity, g_opt_emit_sorted_keys.load() != 0, out, (int)g_opt_sort_mode.load());
+    return GUAVA_OK;
+}
+
+int guava_buffer_layout_of_call(const char* image_buffer, int V, int P, int width, int height, void* stream,
+                                guava_layout* out, int* sort_mode, int* block_masks, size_t* capacity)
+{
+    if (!out || !image_buffer || V < 0 || P < 0 || width <= 0 || height <= 0)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "bad layout query");
+    guava_layout L0;
+    compute_layout(V, P, width, height, 0, false, &L0, 0);   // the image buffer's layout does not depend on the rest
+    uint32_t hdr[8];
+    GUAVA_CUDA(cudaMemcpyAsync(hdr, image_buffer + L0.num_rendered, sizeof(hdr), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    GUAVA_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    const int mode = (int)(hdr[5] & 0xffu);
+    const size_t cap = (size_t)hdr[6] | ((size_t)hdr[7] << 32);
+    // the sorted keys exist in mode 1 always, in mode 0 when the call ran with "emit_sorted_keys" (header bit 16)
+    compute_layout(V, P, width, height, cap, (hdr[5] >> 16) & 1u, out, mode);
+    if (sort_mode) *sort_mode = mode;
+    if (block_masks) *block_masks = (int)((hdr[5] >> 8) & 1u);
+    if (capacity) *capacity = cap;
+    return GUAVA_OK;
+}
+
+int guava_selftest_cull(int n, const float* splats, const float* block_origins, uint8_t* rejected, uint8_t* passing,
+                        void* stream)
+{
+    if (n < 0) return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if (n == 0) return GUAVA_OK;
+    if (!splats || !block_origins || !rejected || !passing) return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    launch_selftest_cull(n, splats, block_origins, rejected, passing, (cudaStream_t)stream);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(GUAVA_ERR_CUDA, cudaGetErrorString(e));
     return GUAVA_OK;
 }
 
@@ -776,7 +816,6 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "emit_sorted_keys")) return &g_opt_emit_sorted_keys;
     if (!strcmp(name, "exact_binning")) return &g_opt_exact_binning;
     if (!strcmp(name, "capacity_hint")) return &g_opt_capacity_hint;
-    if (!strcmp(name, "async_forward")) return &g_opt_async_forward;
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
     if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
     if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;

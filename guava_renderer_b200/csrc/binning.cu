@@ -64,7 +64,7 @@ size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (t
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ scratch,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
-                 uint32_t list_limit)
+                 uint32_t list_limit, uint32_t call_flags)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
@@ -117,6 +117,9 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
         num_rendered[2] = 0u;   // work counters of the persistent compositing kernels
         num_rendered[3] = 0u;
         num_rendered[4] = longest;   // longest tile list: lets the long-bucket sort exit at once
+        num_rendered[5] = call_flags;                      // what this call resolved its options to, for the backward
+        num_rendered[6] = (uint32_t)capacity;              // call and for guava_buffer_layout_of_call
+        num_rendered[7] = (uint32_t)(capacity >> 32);
         // one aligned 8-byte store: (R, longest) reach the pinned host words together, no system fences
         if (host_R != nullptr)
             *reinterpret_cast<volatile unsigned long long*>(host_R) =
@@ -153,12 +156,12 @@ tile_order_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict_
 }
 
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity,
-                      uint32_t list_limit, cudaStream_t s)
+                      uint32_t list_limit, uint32_t call_flags, cudaStream_t s)
 {
     const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
     tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
-                                              host_mapped_R, (unsigned long long)capacity, list_limit);
+                                              host_mapped_R, (unsigned long long)capacity, list_limit, call_flags);
     tile_order_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.ranges, scratch, img.tile_order);
     count_launch(2);
 }
@@ -462,7 +465,7 @@ void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img,
     count_launch();
     // (lists sorted by the long-bucket kernel keep plain ids: no block of theirs is marked untouched)
     if (!with_large) return;
-    const int big_grid = total_tiles < 148 ? total_tiles : 148;
+    const int big_grid = total_tiles < sm_count() ? total_tiles : sm_count();
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
         img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
     count_launch();

@@ -270,7 +270,7 @@ void launch_deform_forward(const DeformArgs& a, const float* smplx_features, con
     if (np) deform_forward_kernel<<<(unsigned)((np + 255) / 256), 256, 0, s>>>(a, out_xyz, out_rot, out_scale, out_opacity);
     int n = (nf ? 1 : 0) + (np ? 1 : 0);
     if (np && out_features != nullptr) {
-        concat_features_kernel<<<148 * 8, 256, 0, s>>>(a.B, a.Nv, a.N, (const float4*)smplx_features,
+        concat_features_kernel<<<sm_count() * 8, 256, 0, s>>>(a.B, a.Nv, a.N, (const float4*)smplx_features,
                                                        (const float4*)uv_features, (float4*)out_features);
         n++;
     }

@@ -366,7 +366,7 @@ void launch_onesweep_binning(const Inputs& in, const GeomPtrs& g, const ImagePtr
             state + (size_t)p * nparts * 256, 8 * p, (1u << nb) - 1u);
         cur ^= 1;
     }
-    identify_tile_ranges_kernel<<<148 * 4, 256, 0, s>>>(kb[cur], img.num_rendered, img.ranges);
+    identify_tile_ranges_kernel<<<sm_count() * 4, 256, 0, s>>>(kb[cur], img.num_rendered, img.ranges);
     count_launch(passes + 2);
 }
 

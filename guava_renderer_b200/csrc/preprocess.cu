@@ -241,7 +241,8 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 // recomputed from scale/rotation (12 FFMA-chains) instead of being stored by
 // the forward pass and re-read here (24 B/Gaussian each way).
 __global__ void __launch_bounds__(256)
-preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const SplatRec* __restrict__ recs,
+preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_rendered, const int* __restrict__ radii,
+                           const SplatRec* __restrict__ recs,
                            const float* __restrict__ grad_geo,
                            int has_invdepth, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
                            float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
@@ -250,6 +251,7 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
 {
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (gid >= (size_t)in.V * in.P) return;
+    if (num_rendered[1]) return;   // the forward's binning overflowed: no lists, no gradients (see render_backward.cu)
     // Per-Gaussian sums written by the backward compositing kernel: moments of s = dL/dG * G about
     // the pixel offset d = mean2D - pixel, (sum s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2), then
     // sum G*dL/dalpha and sum w*dL/dinvdepth.  backward.cu:612-635 in terms of them.
@@ -447,7 +449,7 @@ preprocess_backward_kernel(const Inputs in, const int* __restrict__ radii, const
     }
 }
 
-void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const int* radii, int has_invdepth,
+void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const uint32_t* num_rendered, const int* radii, int has_invdepth,
                                 float* dL_dmean2D, float* dL_dconic, float* dL_dinvdepth,
                                 float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D,
                                 float* dL_dscale, float* dL_drot, cudaStream_t s)
@@ -455,7 +457,7 @@ void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const int* 
     const size_t n = (size_t)in.V * in.P;
     if (n == 0) return;
     preprocess_backward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
-        in, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
+        in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
         dL_dscale, dL_drot);
     count_launch();
 }

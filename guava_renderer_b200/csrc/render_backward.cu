@@ -91,11 +91,16 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                        const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
-                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ work_counter)
+                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ num_rendered)
 {
     __shared__ BwdStage stage[2];
     __shared__ __align__(16) float ex[4][32];   // blending weights of a survivor, one per pixel: two pairs in flight
 
+    // The forward's binning overflowed (a replayed capture whose capacity was outgrown): its instance kernels
+    // skipped themselves, the lists this kernel would walk were never written.  Gradients stay zero; the caller
+    // learns of it through the status words / num_rendered[1].
+    if (num_rendered[1]) return;
+    uint32_t* const work_counter = num_rendered + 3;
     const int lane = threadIdx.x;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
@@ -404,12 +409,13 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 12; }();   // tuning knob
-    const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
+    const long long full = (long long)sm_count() * ctas_per_sm;
+    const unsigned grid = (unsigned)(total < full ? total : full);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
 #define GUAVA_LAUNCH_BWD(VR, MK)                                                                                          \
     render_backward_kernel<VR, MK><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T,   \
                                                        img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,    \
-                                                       img.num_rendered + 3)
+                                                       img.num_rendered)
     if (block_masks) { if (vec_red) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(0, 1); }
     else             { if (vec_red) GUAVA_LAUNCH_BWD(1, 0); else GUAVA_LAUNCH_BWD(0, 0); }
 #undef GUAVA_LAUNCH_BWD

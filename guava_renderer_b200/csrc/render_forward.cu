@@ -290,13 +290,53 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
   }
 }
 
+// Self-test hook (guava_selftest_cull): one thread per (splat, 8x4 block) sample evaluates splat_may_touch exactly
+// as the compositors do (threshold from preprocess's __logf) AND the per-pixel alpha test at all 32 pixel centres of
+// the block with the compositors' own arithmetic (expf_pair; forward.cu:350-362).  rejected = the footprint test
+// says "cannot touch"; passing = number of pixels at which the splat passes the alpha test.  The culling is
+// output-neutral iff no sample has rejected != 0 && passing != 0.
+__global__ void __launch_bounds__(256)
+selftest_cull_kernel(int n, const float* __restrict__ splats, const float* __restrict__ origins,
+                     uint8_t* __restrict__ rejected, uint8_t* __restrict__ passing)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const float mx = splats[6 * i], my = splats[6 * i + 1], A = splats[6 * i + 2], B = splats[6 * i + 3],
+                C = splats[6 * i + 4], op = splats[6 * i + 5];
+    const float x0 = origins[2 * i], y0 = origins[2 * i + 1];
+    const float lthr = __logf(255.0f * op) + 0.01f;   // SplatRec::lthr, preprocess.cu
+    rejected[i] = splat_may_touch(mx, my, A, B, C, lthr, x0, x0 + 7.0f, y0, y0 + 3.0f) ? 0 : 1;
+    int pass = 0;
+    for (int p = 0; p < 32; p += 2) {
+        const float pxa = x0 + (float)(p & 7), pya = y0 + (float)(p >> 3);
+        const float pxb = x0 + (float)((p + 1) & 7), pyb = y0 + (float)((p + 1) >> 3);
+        const float2 dx = __fadd2_rn(f2(mx), f2(-pxa, -pxb));
+        const float2 dy = __fadd2_rn(f2(my), f2(-pya, -pyb));
+        const float2 qd = __ffma2_rn(dx, __fmul2_rn(dx, f2(A)), __fmul2_rn(dy, __fmul2_rn(dy, f2(C))));
+        const float2 pw = __ffma2_rn(qd, f2(-0.5f), __fmul2_rn(dy, __fmul2_rn(dx, f2(-B))));
+        const float2 ag = __fmul2_rn(f2(op), expf_pair(pw));
+        const float a0 = fminf(ag.x, 0.99f), a1 = fminf(ag.y, 0.99f);
+        pass += (!(pw.x > 0.0f) && !(a0 < 1.0f / 255.0f)) ? 1 : 0;
+        pass += (!(pw.y > 0.0f) && !(a1 < 1.0f / 255.0f)) ? 1 : 0;
+    }
+    passing[i] = (uint8_t)pass;
+}
+
+void launch_selftest_cull(int n, const float* splats, const float* origins, uint8_t* rejected, uint8_t* passing, cudaStream_t s)
+{
+    if (n <= 0) return;
+    selftest_cull_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, splats, origins, rejected, passing);
+    count_launch();
+}
+
 void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
                            float* out_color, float* out_invdepth, int block_masks, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_FWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
-    const unsigned grid = (unsigned)(total < 148LL * ctas_per_sm ? total : 148LL * ctas_per_sm);
+    const long long full = (long long)sm_count() * ctas_per_sm;
+    const unsigned grid = (unsigned)(total < full ? total : full);
     if (block_masks)
         render_forward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
                                                      img.final_T, img.n_contrib, out_color, out_invdepth);

@@ -3,7 +3,7 @@
 At GUAVA sizes one batched forward+backward is < 1 ms of GPU work, i.e. the same order as the host
 time PyTorch needs to enqueue it (~60 tensor ops); the reference additionally blocks on a device->host
 copy per view (rasterizer_impl.cu:284).  `GraphedRenderStep` records the whole launch chain once -- the
-C-ABI forward in its no-host-wait mode (option "async_forward"), the loss, the C-ABI backward and the
+C-ABI forward in its no-host-wait mode (guava_call_options::no_host_wait), the loss, the C-ABI backward and the
 packing of the per-Gaussian gradients -- and replays it with one call, so the step costs what its kernels
 cost.  Inputs are STATIC device tensors (the graph reads their storage on every replay; refresh them
 with `copy_`), exactly as for torch.cuda.graphs whole-network capture.
@@ -71,7 +71,7 @@ class GraphedRenderStep:
         self.color = self.radii = self.invdepth = self.loss = None
         self.grads: Dict[str, torch.Tensor] = {}
         # (num_rendered, longest list | overflow << 31) of the latest replay: the tile scan stores them
-        # straight into these pinned words (guava_rasterizer_set_status_words) -- no copy node in the graph
+        # straight into these pinned words (guava_call_options::status_words) -- no copy node in the graph
         self._status = torch.zeros(2, dtype=torch.int32).pin_memory()
         V = int(settings.viewmatrix.shape[0])
         P = int(means3D.shape[-2])
@@ -90,19 +90,14 @@ class GraphedRenderStep:
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
 
-        prev = _lib.get_option("async_forward")
-        _lib.set_option("async_forward", 1)
-        try:
-            n0 = _lib.launch_count()
-            with torch.cuda.graph(self.graph):
-                self._step()
-            # kernels of libguava_rasterizer_b200.so that one replay launches
-            self.launches_per_replay = _lib.launch_count() - n0
-        finally:
-            _lib.set_option("async_forward", prev)
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(self.graph):
+            self._step(no_host_wait=True)
+        # kernels of libguava_rasterizer_b200.so that one replay launches
+        self.launches_per_replay = _lib.launch_count() - n0
 
     # one step, eager or under capture
-    def _step(self):
+    def _step(self, no_host_wait: bool = False):
         i = self.inputs
         V = int(self.settings.viewmatrix.shape[0])
         P = int(i["xyz"].shape[-2])
@@ -111,10 +106,10 @@ class GraphedRenderStep:
         else:
             leaf = i
         m2 = torch.empty(self._m2_shape, device=self.device, requires_grad=self.training)
-        _rz._tls.status_words = self._status
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
-                                                           leaf["scaling"], leaf["rotation"], self.settings)
+                                                           leaf["scaling"], leaf["rotation"], self.settings,
+                                                           status_words=self._status, no_host_wait=no_host_wait)
         self.color, self.radii, self.invdepth = color, radii, invd
         if not self.training:
             return

@@ -362,7 +362,7 @@ _GRAD_WIDTHS = [32, 3, 1, 3, 6, 3, 4, 4, 1]
 
 class _RasterizeGaussiansBatch(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, means3D, means2D, colors_precomp, opacities, scales, rotations, settings):
+    def forward(ctx, means3D, means2D, colors_precomp, opacities, scales, rotations, settings, call=None):
         lib = _lib.load()
         st = settings
         V = int(st.viewmatrix.shape[0])
@@ -384,18 +384,19 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
             bufs = _CallBuffers(dev)
             _tls.call = bufs
             rendered = ctypes.c_int(0)
-            aux = getattr(_tls, "refiner_output", None)     # set by renderer.render_views(refiner_input=True)
-            _tls.refiner_output = None
+            # per-call options (guava_call_options): refiner hand-off buffer, the caller's pinned status words,
+            # no-host-wait mode -- given by render_views(refiner_input=True) / GraphedRenderStep
+            call = call or {}
+            aux = call.get("refiner_output")
             if aux is not None:
                 if aux.dtype != torch.bfloat16 or tuple(aux.shape) != (V, H, W, NUM_CHANNELS) or not aux.is_contiguous():
                     raise ValueError("refiner output must be a contiguous bfloat16 [V,H,W,32] tensor")
                 if V * P == 0:
                     aux.zero_()
-                _check(lib.guava_rasterizer_set_refiner_output(_ptr(aux)))
-            status = getattr(_tls, "status_words", None)    # set by GraphedRenderStep: its pinned (R, longest|overflow)
-            _tls.status_words = None
-            if status is not None:
-                _check(lib.guava_rasterizer_set_status_words(status.data_ptr()))
+            status = call.get("status_words")
+            copts = _lib.CallOptions(refiner_output=_ptr(aux) if aux is not None else 0,
+                                     status_words=status.data_ptr() if status is not None else 0,
+                                     no_host_wait=bool(call.get("no_host_wait", False)))
             rc = lib.guava_rasterizer_forward_batch(
                 _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
                 V, P, _ptr(bg), W, H,
@@ -403,7 +404,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                 float(st.scale_modifier), _ptr(r), strides[4],
                 _ptr(vm), _ptr(pm), _ptr(tf), _ptr(out_color), _ptr(out_invdepth),
                 int(bool(st.antialiasing)), _ptr(radii), int(bool(st.debug)), _stream_ptr(dev),
-                ctypes.byref(rendered))
+                ctypes.byref(rendered), ctypes.byref(copts))
             _tls.call = None
             _tls.last_buffers = bufs.bufs      # (geometry, binning, image) of the most recent batched forward
             _check(rc)
@@ -460,15 +461,22 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
 
         return (shape_like(g_mean3D, ctx.strides[0], m), g_mean2D, shape_like(g_color, ctx.strides[1], c),
                 shape_like(g_opacity, ctx.strides[2], o), shape_like(g_scale, ctx.strides[3], s),
-                shape_like(g_rot, ctx.strides[4], r), None)
+                shape_like(g_rot, ctx.strides[4], r), None, None)
 
 
 def rasterize_gaussians_batch(means3D, means2D, colors_precomp, opacities, scales, rotations,
-                              settings: BatchRasterizationSettings):
+                              settings: BatchRasterizationSettings, refiner_output: Optional[torch.Tensor] = None,
+                              status_words: Optional[torch.Tensor] = None, no_host_wait: bool = False):
     """means3D [V,P,3] or [P,3]; means2D [V,P,3] (gradient sink only); colors_precomp [V,P,32] or [P,32];
     opacities [V,P,1] or [P,1]; scales [V,P,3] or [P,3]; rotations [V,P,4] or [P,4].
+    Per-call options (guava_call_options): `refiner_output` bf16 [V,H,W,32] written by the compositing
+    kernel's epilogue; `status_words` pinned int32[2] receiving (num_rendered, longest list | overflow << 31);
+    `no_host_wait` enqueues the chain without waiting for num_rendered (CUDA-graph capture).
     Returns (color [V,32,H,W], radii [V,P] int32, invdepth [V,1,H,W])."""
-    return _RasterizeGaussiansBatch.apply(means3D, means2D, colors_precomp, opacities, scales, rotations, settings)
+    call = None
+    if refiner_output is not None or status_words is not None or no_host_wait:
+        call = dict(refiner_output=refiner_output, status_words=status_words, no_host_wait=no_host_wait)
+    return _RasterizeGaussiansBatch.apply(means3D, means2D, colors_precomp, opacities, scales, rotations, settings, call)
 
 
 class GaussianBatchRasterizer(nn.Module):

@@ -66,11 +66,9 @@ def render_views(gaussian_assets: Dict[str, torch.Tensor], cam_params: Dict[str,
     if refiner_input:
         # refiner hand-off: the compositing kernel's epilogue also writes the image as
         # channels-last bf16, the layout/precision a tensor-core first convolution of the refiner wants
-        from . import rasterizer as _rz
         aux = torch.empty(B, H, W, features_color.shape[-1], dtype=torch.bfloat16, device=device)
-        _rz._tls.refiner_output = aux
     rendered_images, radiis, depth_images = rasterize_gaussians_batch(
-        mean_3d, mean_2d, features_color, opacity, scales, rotations, settings)
+        mean_3d, mean_2d, features_color, opacity, scales, rotations, settings, refiner_output=aux)
 
     out = {
         "raw_renders": rendered_images[:, :3],

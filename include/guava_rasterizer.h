@@ -92,7 +92,7 @@ int guava_rasterizer_forward(
  * dL_dinvdepth [P] or NULL must be zero-filled by the caller (as
  * rasterize_points.cu:163-182 does); dL_dmean3D [P,3], dL_dcov3D [P,6],
  * dL_dscale [P,3], dL_drot [P,4] are fully written for visible Gaussians and
- * must be zero-filled for the rest. */
+ * must be zero-filled for the rest.  dL_drot must be 16-byte aligned (one vector store per Gaussian). */
 int guava_rasterizer_backward(
     int P, int D, int M, int R,
     const float *background,
@@ -139,6 +139,31 @@ int guava_rasterizer_mark_visible(
     uint8_t *present,
     void *stream);
 
+/* Per-call options of the batched entry (everything that used to be "applies to the next call" state
+ * lives here: a call's behaviour depends on its own arguments only).  Zero-initialise, set
+ * `struct_size = sizeof(guava_call_options)`, fill what is needed; NULL = all defaults. */
+typedef struct guava_call_options {
+    size_t struct_size;
+    /* Refiner hand-off (models/UbodyAvatar/gaussian_render.py:70-73 feeds the
+     * stacked 32-channel image to the neural refiner): when non-NULL the compositing kernel's epilogue
+     * additionally writes the image as channels-last bf16, [V,H,W,32] (64 bytes per pixel,
+     * round-to-nearest-even of the fp32 values; device pointer, 16-byte aligned) -- no separate
+     * permute/cast pass.  Where V*P == 0 it is not written (as out_color, rasterize_points.cu:88). */
+    void *refiner_output_nhwc_bf16;
+    /* Status words.  The reference returns num_rendered through a blocking device->host copy per view
+     * (rasterizer_impl.cu:284).  Here the tile scan stores two words straight into pinned host memory:
+     * [0] = num_rendered, [1] = longest tile list | (overflow << 31).  NULL: a slot the library owns.
+     * Non-NULL: the caller's OWN two words -- 8-byte aligned, pinned, device-mapped host memory (e.g.
+     * cudaHostAlloc) -- which it reads after synchronising: no copy node, no copy engine, nothing on
+     * the stream after the last kernel (what a captured CUDA graph needs). */
+    void *status_words;
+    /* 1: enqueue the whole chain and return without waiting for num_rendered on the host (CUDA-graph
+     * capture): *num_rendered is set to -1, and a binning overflow (capacity, or a tile list longer than
+     * the sort that was launched) makes every later kernel of the forward AND of the backward skip
+     * itself; it is visible in status_words[1] bit 31 / the image buffer's num_rendered[1]. */
+    int no_host_wait;
+} guava_call_options;
+
 /* Batched multi-view entry (replaces the per-view Python
  * loop of models/UbodyAvatar/gaussian_render.py:37-67).  V views of equal
  * H x W are rasterized by ONE launch chain: tile ids and keys carry the view
@@ -168,7 +193,8 @@ int guava_rasterizer_forward_batch(
     int *radii,                         /* [V,P] */
     int debug,
     void *stream,
-    int *num_rendered);                 /* total over views */
+    int *num_rendered,                  /* total over views */
+    const guava_call_options *options); /* NULL = defaults */
 
 /* Backward of the batched entry.  Gradient tensors are [V,P,...] (one slice
  * per view; the caller sums over views when the Gaussians were shared). */
@@ -236,7 +262,9 @@ typedef struct guava_layout {
     size_t ranges;         /* uint2 per tile   [V*tiles]; values are offsets into point_list */
     size_t tile_cursor;    /* uint32 per tile, one per 128-byte line (scratch) */
     size_t tile_order;     /* uint32[4] per tile, longest list first (work order): tile index, range.x, range.y, 0 */
-    size_t num_rendered;   /* uint32[8]: R, capacity-overflow flag, two work counters, longest tile list, - */
+    size_t num_rendered;   /* uint32[8], the call's header: R, overflow flag, two work counters, longest tile list,
+                              sort mode | block_masks << 8 | sorted keys kept << 16 (as resolved for this call),
+                              binning capacity (lo, hi) */
     /* binning buffer for a capacity of `capacity` instances */
     size_t binning_bytes;
     size_t point_list;     /* uint32 per instance: Gaussian index within its view, sorted */
@@ -253,13 +281,18 @@ typedef struct guava_layout {
 
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout *out);
 
+/* The layout a finished forward call actually used.  Every forward call records what it resolved its
+ * options to (sort mode, block masks, sorted keys kept, binning capacity) in the image buffer's header
+ * (num_rendered[5..7]); this query reads the header back (one 32-byte device->host copy, synchronises
+ * `stream`) and reports the offsets that are valid for THAT call, whatever the process-wide options are
+ * by now.  sort_mode / block_masks / capacity may be NULL. */
+int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int width, int height, void *stream,
+                                guava_layout *out, int *sort_mode, int *block_masks, size_t *capacity);
+
 /* Process-wide options (ints): "emit_sorted_keys" (0/1, default 0),
  * "exact_binning" (0/1, default 0: 1 = wait for num_rendered before sizing the
  * binning buffer, exactly as rasterizer_impl.cu:283-288 does),
  * "capacity_hint" (instances; 0 = automatic),
- * "async_forward" (0/1, default 0: 1 = never wait on the host; *num_rendered is
- * set to -1 and a capacity overflow is only visible in the image buffer's
- * num_rendered[1] flag -- for CUDA-graph capture),
  * "profile_stages" (0/1, default 0: time every kernel with CUDA events, see
  * guava_stage_time),
  * "sort_mode" (0: per-tile buckets sorted in shared memory; 1: the reference's chain rebuilt --
@@ -295,24 +328,15 @@ void guava_stage_time_reset(void);
  * first call (the kernel leaves it zero).  a, b: device pointers, 16-byte aligned, n elements. */
 int guava_image_dot(const float *a, const float *b, size_t n, float *out64, void *stream);
 
-/* Status words.  The reference returns num_rendered through a blocking device->host copy per view
- * (rasterizer_impl.cu:284).  Here the tile scan stores two words straight into pinned host memory:
- * [0] = num_rendered, [1] = longest tile list | (capacity overflow << 31).  By default they go to a slot
- * the library owns; a caller that enqueues the forward without waiting (option "async_forward", CUDA
- * graph capture) hands its OWN two words -- 8-byte aligned, pinned, device-mapped host memory, e.g.
- * cudaHostAlloc -- to the NEXT forward call of the calling thread and reads them after synchronising:
- * no copy node, no copy engine, nothing on the stream after the last kernel.  Consumed by that call;
- * NULL cancels. */
-int guava_rasterizer_set_status_words(void *pinned_host_u32x2);
-
-/* ---- the step immediately after the rasterizer ---------------------------
- * Refiner hand-off.  GUAVA feeds the stacked 32-channel image to its neural refiner
- * (models/UbodyAvatar/gaussian_render.py:70-73).  The NEXT forward call (single-view or batch) made by
- * the calling thread additionally writes the image as channels-last bf16, [V,H,W,32] (64 bytes per
- * pixel, round-to-nearest-even of the fp32 values, device pointer, 16-byte aligned), from the
- * compositing kernel's epilogue -- no separate permute/cast pass.  The setting is consumed by that call;
- * pass NULL to cancel.  Where P == 0 the image is not written (as for out_color, rasterize_points.cu:88). */
-int guava_rasterizer_set_refiner_output(void *out_color_nhwc_bf16);
+/* Self-test hook for the compositors' warp-footprint culling (the one place where this library skips work the
+ * reference does, forward.cu:342-382 / backward.cu:556-636 visit every list entry at every pixel).  For n samples
+ * -- splats [n,6] = (mean2D.x, mean2D.y, conic.x, conic.y, conic.z, opacity), block_origins [n,2] = pixel
+ * coordinates of an 8x4 block's first pixel -- the device evaluates the culling predicate exactly as the
+ * compositors do (rejected[i] = 1: "cannot reach alpha >= 1/255 anywhere in the block") and, with the
+ * compositors' own arithmetic, the reference's per-pixel alpha test at the block's 32 pixel centres
+ * (passing[i] = number of pixels that pass).  Culling is output-neutral iff no sample has rejected && passing. */
+int guava_selftest_cull(int n, const float *splats, const float *block_origins, uint8_t *rejected, uint8_t *passing,
+                        void *stream);
 
 /* ---- the step immediately before the rasterizer ------------------------
  * Fused deformation of GUAVA's two Gaussian groups into the concatenated [B, Nv+N, *] tensors the

@@ -165,6 +165,7 @@ def test_backward_vs_reference_build(ref, case, with_invdepth):
     _, gr = _run_autograd(ref, inp, dL_dcolor, dL_dinv)
     for k in gr:
         assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+        util.grad_gate(k, go[k], gr[k])       # per element: |a-b| <= 1e-4 |b| + 1e-6 max|b|
 
 
 def test_backward_vector_reduction_option_vs_reference_build(ref):
@@ -479,6 +480,7 @@ def test_full_size_configs_vs_reference_build(ref, case, sort_mode):
     _, gr = _run_autograd(ref, inp, dc * 1e4, None)
     for k in gr:
         assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
+        util.grad_gate(k, go[k], gr[k])
 
 
 def test_refiner_handoff_is_the_same_image_in_channels_last_bf16():
@@ -654,3 +656,179 @@ def test_list_longer_than_the_launched_sort_is_recovered():
         grb.set_option("sort_mode", -1)
     for k in ("color", "invdepth", "radii", "n_contrib", "point_list", "ranges"):
         assert np.array_equal(got[k], want[k]), k
+
+
+# ------------------------------------------------------------------ rows a20, a8/a17 of SURVEY.md section 8
+def test_debug_mode_gives_the_same_results(ref):
+    """`debug=True` (CHECK_CUDA, auxiliary.h:178-185: synchronise and check after every stage) must not change a
+    result: forward bitwise equal to the non-debug call, gradients equal to atomic-order tolerance, and equal to
+    the reference build run with ITS debug flag."""
+    case = CASES[1]
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(11)
+    dL = torch.randn(32, case["H"], case["W"], generator=g)
+
+    def run(mod, debug):
+        leaf = {k: inp[k].to(DEV).clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+        m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+        rast = mod.GaussianRasterizer_32(raster_settings=util.settings_for(mod, inp, DEV, False, debug=debug))
+        color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                                  opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"],
+                                  cov3D_precomp=None)
+        (color * dL.to(DEV)).sum().backward()
+        torch.cuda.synchronize()
+        return color.detach().cpu().numpy(), radii.cpu().numpy(), {k: v.grad.cpu().numpy() for k, v in leaf.items()}
+
+    c0, r0, g0 = run(ours, False)
+    c1, r1, g1 = run(ours, True)
+    cr, rr, gr = run(ref, True)
+    assert np.array_equal(c0, c1) and np.array_equal(r0, r1) and np.array_equal(r1, rr)
+    assert np.abs(c1 - cr).max() <= 1e-5
+    for k in g0:
+        assert util.rel_err(g1[k], g0[k]) <= 1e-5, k
+        util.grad_gate(k, g1[k], gr[k])
+
+
+_TRAP_SCRIPT = r"""
+import os, sys, torch
+sys.path.insert(0, {root!r})
+from tests import util
+import diff_gaussian_rasterization_32 as ours
+inp = util.inputs_for(512, 64, 64, seed=8)
+inp["xyz"][::3, 2] -= 40.0            # a third of the points behind the near plane: in_frustum() rejects them
+rs = util.settings_for(ours, inp, "cuda:0", False, debug=True)._replace(prefiltered=True)
+d = lambda k: inp[k].to("cuda:0")
+try:
+    ours.GaussianRasterizer_32(rs)(means3D=d("xyz"), means2D=d("xyz"), opacities=d("opacity"), colors_precomp=d("features"),
+                                  scales=d("scaling"), rotations=d("rotation"))
+    torch.cuda.synchronize()
+except RuntimeError as e:
+    print("RAISED:", e, flush=True)
+    os._exit(0 if "preprocess" in str(e) else 3)      # the context is poisoned: skip the interpreter's CUDA teardown
+os._exit(4)
+"""
+
+
+def test_prefiltered_trap_is_reported_by_debug_mode():
+    """auxiliary.h:166-172: with `prefiltered` set, a point that fails the frustum test prints a message and
+    executes __trap(); in debug mode the stage check turns that into an exception naming the stage
+    (CHECK_CUDA).  The trap poisons the CUDA context, so this runs in its own process."""
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, "-c", _TRAP_SCRIPT.format(root=util.ROOT)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout[-400:], r.stderr[-400:])
+    assert "RAISED:" in r.stdout and "CUDA ERROR" in r.stdout
+
+
+def test_cov3d_precomp_backward_vs_reference_build(ref):
+    """The cov3D_precomp input path end to end (forward.cu:206-215, backward.cu:147-326): images and the
+    gradients the reference returns for it -- dL_dcov3D above all (__init__.py:137) -- against the reference
+    build.  The covariances are the reference's own (GeometryState::cov3D of a scales+rotations call)."""
+    case = dict(P=3000, H=96, W=128, seed=12, scale_mult=0.8)
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(0, 1, 32)
+    R, _, _, geom, binning, img, _ = util.c_forward(ref, inp, DEV)
+    cov = torch.from_numpy(util.decode_reference(geom, binning, img, case["P"], case["H"], case["W"], R)["cov3D"]).to(DEV)
+    g = torch.Generator().manual_seed(5)
+    dL = torch.randn(32, case["H"], case["W"], generator=g).to(DEV)
+    dLi = torch.randn(1, case["H"], case["W"], generator=g).to(DEV)
+
+    def run(mod):
+        leaf = {k: inp[k].to(DEV).clone().requires_grad_(True) for k in ("xyz", "features", "opacity")}
+        c3 = cov.clone().requires_grad_(True)
+        m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+        rast = mod.GaussianRasterizer_32(raster_settings=util.settings_for(mod, inp, DEV))
+        color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                                  opacities=leaf["opacity"], scales=None, rotations=None, cov3D_precomp=c3)
+        ((color * dL).sum() + (invd * dLi).sum()).backward()
+        torch.cuda.synchronize()
+        out = {k: v.grad.cpu().numpy() for k, v in leaf.items()}
+        out["cov3D"] = c3.grad.cpu().numpy()
+        out["means2D"] = m2.grad.cpu().numpy()
+        return color.detach().cpu().numpy(), radii.cpu().numpy(), out
+
+    co, ro, go = run(ours)
+    cr, rr, gr = run(ref)
+    assert np.array_equal(ro, rr) and np.abs(co - cr).max() <= 1e-5
+    assert np.abs(gr["cov3D"]).max() > 0
+    for k in gr:
+        util.grad_gate(k, go[k], gr[k])
+
+
+def test_footprint_culling_is_output_neutral_on_the_device():
+    """Brute force on the device (guava_selftest_cull): for random splats against random 8x4 blocks, whenever the
+    compositors' footprint test rejects a splat, the reference's alpha test (forward.cu:350-362), evaluated with
+    the compositors' own arithmetic, fails at all 32 pixel centres.  Splat shapes cover the benchmark's (sigma
+    0.5..30 px, any orientation, opacity 0.002..0.999) plus degenerate conics; means lie inside, beside and far
+    from the block."""
+    import ctypes
+    lib = grb._lib_mod.load()
+    n = 2_000_000
+    g = torch.Generator().manual_seed(123)
+    sig = torch.exp(torch.rand(n, 2, generator=g) * 4.1 - 0.7)                 # 0.5 .. 30 px
+    th = torch.rand(n, generator=g) * 3.14159265
+    c, s_ = torch.cos(th), torch.sin(th)
+    a = (c / sig[:, 0]) ** 2 + (s_ / sig[:, 1]) ** 2
+    cc = (s_ / sig[:, 0]) ** 2 + (c / sig[:, 1]) ** 2
+    b = c * s_ * (1 / sig[:, 0] ** 2 - 1 / sig[:, 1] ** 2)
+    op = torch.sigmoid(1.0 + 2.0 * torch.randn(n, generator=g)).clamp(0.002, 0.999)
+    org = torch.stack([torch.randint(0, 64, (n,), generator=g) * 8.0, torch.randint(0, 128, (n,), generator=g) * 4.0], 1)
+    # distance of the mean from the block: within a few sigma of the boundary, where the decision is made
+    reach = sig.max(1).values * torch.sqrt(2 * torch.log(255 * op).clamp_min(0.0) + 1e-3)
+    off = (torch.rand(n, 2, generator=g) * 2 - 1) * (reach[:, None] * 1.4 + 6.0)
+    mean = org + torch.tensor([3.5, 1.5]) + off
+    splats = torch.stack([mean[:, 0], mean[:, 1], a, b, cc, op], 1).contiguous()
+    splats[:1000, 2] = 0.0                      # degenerate / not positive definite: must be kept
+    splats[1000:2000, 3] = splats[1000:2000, 2] * 4
+    splats[2000:3000, 4] = float("nan")
+    sp, og = splats.to(DEV), org.contiguous().to(DEV)
+    rej = torch.zeros(n, dtype=torch.uint8, device=DEV)
+    pas = torch.zeros(n, dtype=torch.uint8, device=DEV)
+    rc = lib.guava_selftest_cull(n, sp.data_ptr(), og.data_ptr(), rej.data_ptr(), pas.data_ptr(),
+                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, grb._lib_mod.last_error()
+    torch.cuda.synchronize()
+    rej, pas = rej.cpu().numpy(), pas.cpu().numpy()
+    assert not np.any((rej != 0) & (pas != 0)), int(np.sum((rej != 0) & (pas != 0)))
+    assert not rej[:3000].any()                                   # degenerate conics and NaNs are always kept
+    # the sample exercises the test: a good share rejected, a good share kept, and the test is tight
+    frac_rej = float((rej != 0).mean())
+    kept_untouched = float(((rej == 0) & (pas == 0)).mean())
+    assert 0.2 < frac_rej < 0.95, frac_rej
+    assert kept_untouched < 0.6, kept_untouched
+
+
+def test_graphed_training_step_that_overflows_leaves_zero_gradients_and_reports_it():
+    """A replayed TRAINING step whose captured binning capacity is too small: the forward's instance kernels skip
+    themselves, and so must the backward compositor and the backward preprocess -- they would otherwise walk lists
+    that were never written.  No CUDA error, all gradients zero, and check() raises."""
+    V, P, H, W = 2, 4000, 96, 96
+    views = [util.inputs_for(P, H, W, seed=950 + v, view=v, num_views=V, scale_mult=1.5) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    tanfov = torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=DEV), 1.0,
+                                        stack("viewmatrix"), stack("projmatrix"))
+    g = torch.Generator().manual_seed(4)
+    dL = torch.randn(V, 32, H, W, generator=g).to(DEV)
+    args = (stack("xyz"), stack("features"), stack("opacity"), stack("scaling"), stack("rotation"), st)
+    ok = grb.GraphedRenderStep(*args, dL_dcolor=dL)
+    ok.replay()
+    ok.check()
+    assert float(ok.packed.abs().sum()) > 0
+    grb.set_option("capacity_hint", 64)
+    try:
+        small = grb.GraphedRenderStep(*args, dL_dcolor=dL)
+        for _ in range(3):
+            small.replay()
+        torch.cuda.synchronize()                                  # no sticky CUDA error
+        assert float(small.packed.abs().sum()) == 0.0
+        for k, v in small.grads.items():
+            assert float(v.abs().sum()) == 0.0, k
+        with pytest.raises(RuntimeError, match="capacity"):
+            small.check()
+    finally:
+        grb.set_option("capacity_hint", 0)
+    ok.replay()
+    ok.check()
+    assert float(ok.packed.abs().sum()) > 0

@@ -54,10 +54,11 @@ def c_forward(mod, inp, device, antialiasing=False, scale_modifier=1.0):
 
 
 def decode_ours(geom, binning, img, V, P, W, H, capacity=None):
-    """numpy views of the arrays inside our three opaque buffers (guava_buffer_layout).
-    `capacity`: the binning capacity the call ran with (tests pin it with the
-    "capacity_hint" option); needed only to locate the optional sorted keys."""
-    L = grb.buffer_layout(V, P, W, H, 0)
+    """numpy views of the arrays inside our three opaque buffers.  The layout is the one THE CALL used
+    (guava_buffer_layout_of_call reads the sort mode, the block-mask flag and the binning capacity the call
+    resolved from the image buffer's header), not what the process-wide options say by now; `capacity` is
+    accepted for older callers and ignored."""
+    L, mode, masks, cap = grb._lib_mod.buffer_layout_of_call(img.data_ptr(), V, P, W, H)
     g = geom.cpu().numpy()
     i = img.cpu().numpy()
     b = binning.cpu().numpy()
@@ -76,17 +77,17 @@ def decode_ours(geom, binning, img, V, P, W, H, capacity=None):
         num_rendered=int(i[L.num_rendered:L.num_rendered + 4].view(np.uint32)[0]),
     )
     R = out["num_rendered"]
-    out["point_list"] = b[0:R * 4].view(np.uint32).copy()
-    if grb.get_option("sort_mode") == 1:
+    hdr = i[L.num_rendered:L.num_rendered + 32].view(np.uint32)
+    out["sort_mode"], out["block_masks"], out["capacity"] = mode, masks, cap
+    plist = b[L.point_list:L.point_list + R * 4].view(np.uint32).copy()
+    if masks:   # bits 24..31 of an entry: the tile's 8x4 pixel blocks the splat provably cannot touch
+        out["point_list_masks"] = plist >> 24
+        plist &= 0xFFFFFF
+    out["point_list"] = plist
+    if mode == 1:
         out["point_offsets"] = g[L.point_offsets:L.point_offsets + n * 4].view(np.uint32).copy()
-    if capacity is not None and (grb.get_option("emit_sorted_keys") or grb.get_option("sort_mode") == 1):
-        cap = max(int(capacity), R) if R > int(capacity) else int(capacity)
-        if R > int(capacity):
-            cap = R
-        Lc = grb.buffer_layout(V, P, W, H, cap)
-        # same offset in both sort modes (the onesweep scratch lies behind it)
-        if Lc.keys_sorted + R * 8 <= b.size and (Lc.binning_bytes == b.size or grb.get_option("sort_mode") != 0):
-            out["keys"] = b[Lc.keys_sorted:Lc.keys_sorted + R * 8].view(np.uint64).copy()
+    if mode == 1 or ((hdr[5] >> 16) & 1):
+        out["keys"] = b[L.keys_sorted:L.keys_sorted + R * 8].view(np.uint64).copy()
     return out
 
 
@@ -152,8 +153,40 @@ def import_reference():
 
 
 def rel_err(a, b):
-    """max |a-b| / max|b| (tensor-scale relative error)."""
+    """max |a-b| / max|b| (tensor-scale relative error; a secondary statistic -- the gate is grad_gate)."""
     a = np.asarray(a, np.float64)
     b = np.asarray(b, np.float64)
     den = np.abs(b).max()
     return float(np.abs(a - b).max() / den) if den > 0 else float(np.abs(a).max())
+
+
+def grad_stats(a, b, rtol=1e-4, atol_scale=1e-6):
+    """Per-element comparison of a gradient tensor against the reference's:
+        |a - b| <= rtol * |b| + atol_scale * max|b|
+    Returns dict(viol = fraction of elements outside that bound, out3 = fraction outside 1e-3 relative
+    (+ the same absolute floor), tensor = the tensor-scale error rel_err)."""
+    a = np.asarray(a, np.float64).reshape(-1)
+    b = np.asarray(b, np.float64).reshape(-1)
+    m = np.abs(b).max() if b.size else 0.0
+    d = np.abs(a - b)
+    n = max(a.size, 1)
+    return dict(viol=float((d > rtol * np.abs(b) + atol_scale * m).sum() / n),
+                out3=float((d > 1e-3 * np.abs(b) + atol_scale * m).sum() / n),
+                tensor=rel_err(a, b), max_abs=float(m))
+
+
+# The reference's own backward is not bit-reproducible: 39 fp32 atomicAdd per contributing (pixel, Gaussian)
+# pair land in arbitrary order (backward.cu:593-635), so two runs of the UNMODIFIED reference on identical
+# inputs differ per element.  `test_reference_gradient_jitter_yardstick` measures that on the box; the gate
+# below allows the same kind of deviation: every element within 1e-4 relative + 1e-6 of the tensor's
+# maximum, except a small fraction (accumulation-order noise on cancelling sums), none of which may be
+# outside 1e-3 relative by more than JITTER_OUT3.
+GRAD_VIOL_MAX = 2e-3
+GRAD_OUT3_MAX = 1e-4
+
+
+def grad_gate(name, a, b, viol_max=GRAD_VIOL_MAX, out3_max=GRAD_OUT3_MAX):
+    st = grad_stats(a, b)
+    assert st["tensor"] <= 1e-4, (name, st)
+    assert st["viol"] <= viol_max and st["out3"] <= out3_max, (name, st)
+    return st
