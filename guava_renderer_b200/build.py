@@ -50,7 +50,32 @@ def _run(cmd, verbose):
         print(r.stdout)
     if r.returncode != 0:
         sys.stderr.write(r.stdout)
-        raise RuntimeError("nvcc failed: " + " ".join(cmd))
+        raise RuntimeError("build command failed: " + " ".join(cmd))
+
+
+TORCH_SO = os.path.join(LIBDIR, "_guava_torch.so")
+
+
+def build_torch_binding(force: bool = False, verbose: bool = False) -> str:
+    """csrc/torch_binding.cpp -> lib/_guava_torch.so: the compiled `_C` module (pybind, g++ only -- torch headers are
+    kept out of the .cu files), linked against libguava_rasterizer_b200.so next to it (rpath $ORIGIN)."""
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    src = os.path.join(CSRC, "torch_binding.cpp")
+    if not (force or _stale(TORCH_SO, [src, os.path.join(INCLUDE, "guava_rasterizer.h"), SO])):
+        return TORCH_SO
+    tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    inc = [p for p in ce.include_paths() if os.path.isdir(p)]     # no device_type argument: CPU-side headers suffice ...
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")   # ... plus cuda_runtime_api.h for ATen/cuda
+    cmd = ["g++", "-shared", "-fPIC", "-O2", "-std=c++17", "-o", TORCH_SO, src,
+           "-DTORCH_EXTENSION_NAME=_guava_torch", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           "-D_GLIBCXX_USE_CXX11_ABI=" + str(int(torch._C._GLIBCXX_USE_CXX11_ABI)),
+           "-I" + INCLUDE, "-I" + cuda_inc, "-I" + sysconfig.get_paths()["include"]] + ["-I" + p for p in inc] + \
+          ["-L" + tlib, "-L" + LIBDIR, "-lguava_rasterizer_b200", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
+           "-ltorch_python", "-Wl,-rpath,$ORIGIN", "-Wl,-rpath," + tlib, "-Wno-deprecated-declarations"]
+    _run(cmd, verbose)
+    return TORCH_SO
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -70,6 +95,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         list(ex.map(lambda c: _run(c, verbose), jobs))
     if force or jobs or _stale(SO, objs):
         _run(["nvcc", "-shared", "-o", SO] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"], verbose)
+    build_torch_binding(force, verbose)
     return SO
 
 

@@ -33,6 +33,7 @@ static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_scalar_red{1};   // 1: 4-byte reductions from all 32 lanes (measured faster than gathering 16-byte vectors, profiles/r01_v43)
 static std::atomic<long long> g_opt_block_masks{0};   // experimental, see BLOCK_MASK_SHIFT (internal.cuh)
+static std::atomic<long long> g_opt_os_identify_ranges{0};   // sort mode 1: recompute the tile ranges from the sorted keys (identifyTileRanges restated) although the tile scan already wrote them
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
 // Number of SMs of the current device (grids of the persistent kernels are multiples of it); cached per ordinal.
@@ -501,7 +502,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
             timer.begin(3);
             launch_onesweep_binning(in, g, im, (uint32_t*)(geom + L.point_offsets), (uint64_t*)(bin + L.keys_sorted),
                                     b.point_list, b.keys_unsorted, (uint32_t*)(bin + L.os_vals_alt),
-                                    (uint32_t*)(bin + L.os_scratch), cap, stream);
+                                    (uint32_t*)(bin + L.os_scratch), cap, g_opt_os_identify_ranges.load() != 0, stream);
             timer.end();
             GUAVA_STAGE("onesweep", debug);
         } else {
@@ -820,6 +821,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
     if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;
     if (!strcmp(name, "block_masks")) return &g_opt_block_masks;
+    if (!strcmp(name, "os_identify_ranges")) return &g_opt_os_identify_ranges;
     return nullptr;
 }
 

@@ -16,6 +16,8 @@ arithmetic happens in libguava_rasterizer_b200.so.
 from __future__ import annotations
 
 import ctypes
+import importlib.util
+import os
 import threading
 from typing import NamedTuple, Optional
 
@@ -224,13 +226,37 @@ def mark_visible_C(means3D, viewmatrix, projmatrix):
 
 
 class _CModule:
-    """Stand-in for the reference's pybind module `_C` (ext.cpp:15-18)."""
+    """The reference's `_C` module (ext.cpp:15-18) over ctypes: the same three functions, marshalled in Python.
+    Kept as the binding of last resort for hosts without a C++ toolchain and for the ABI tests; the default `_C`
+    is the compiled module below."""
     rasterize_gaussians = staticmethod(rasterize_gaussians_C)
     rasterize_gaussians_backward = staticmethod(rasterize_gaussians_backward_C)
     mark_visible = staticmethod(mark_visible_C)
 
 
-_C = _CModule()
+TORCH_SO_PATH = os.path.join(os.path.dirname(_lib.SO_PATH), "_guava_torch.so")
+
+
+def _load_compiled_binding():
+    """lib/_guava_torch.so (csrc/torch_binding.cpp, built by build.py with g++): the pybind module that replaces the
+    reference's `_C` -- rasterize_gaussians / rasterize_gaussians_backward / mark_visible with the reference's
+    positional arguments, plus the batched pair.  Per-call host cost is microseconds, as for the reference's own
+    binding; the ctypes marshalling cost ~0.4 ms per forward+backward."""
+    _lib.load()          # the C ABI library first: fails loudly when the CUDA library itself is missing
+    if not os.path.isfile(TORCH_SO_PATH):
+        raise _lib.GuavaLibraryError(
+            f"{TORCH_SO_PATH} is missing: the torch binding has not been built (run `python guava_renderer_b200/build.py`); "
+            "set GUAVA_BINDING=ctypes to use the ctypes binding of the same C ABI instead")
+    spec = importlib.util.spec_from_file_location("_guava_torch", TORCH_SO_PATH)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+BINDING = os.environ.get("GUAVA_BINDING", "compiled")
+if BINDING not in ("compiled", "ctypes"):
+    raise ValueError("GUAVA_BINDING must be 'compiled' or 'ctypes'")
+_C = _load_compiled_binding() if BINDING == "compiled" else _CModule()
 
 
 # --------------------------------------------------------------------------
@@ -268,6 +294,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         if grad_out_color is None:
             grad_out_color = torch.zeros(NUM_CHANNELS, int(rs.image_height), int(rs.image_width),
                                          dtype=torch.float32, device=ctx.saved_tensors[1].device)
+        if grad_out_depth is None:      # "no invdepth gradients": size(0) == 0, rasterize_points.cu:176-182
+            grad_out_depth = torch.empty(0, dtype=torch.float32)
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
          geomBuffer, binningBuffer, imgBuffer) = ctx.saved_tensors
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
@@ -363,96 +391,111 @@ _GRAD_WIDTHS = [32, 3, 1, 3, 6, 3, 4, 4, 1]
 class _RasterizeGaussiansBatch(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, colors_precomp, opacities, scales, rotations, settings, call=None):
-        lib = _lib.load()
         st = settings
         V = int(st.viewmatrix.shape[0])
         P = int(means3D.shape[-2])
         H, W = int(st.image_height), int(st.image_width)
         dev = means3D.device
-        with _device_of(means3D):
-            fopts = dict(dtype=torch.float32, device=dev)
-            out_color = torch.empty(V, NUM_CHANNELS, H, W, **fopts)
-            out_invdepth = torch.empty(V, 1, H, W, **fopts)
-            radii = torch.empty(V, P, dtype=torch.int32, device=dev)
-            if V * P == 0:
-                out_color.zero_(); out_invdepth.zero_()
-            m, c, o = _f32c(means3D), _aligned16(colors_precomp), _f32c(opacities)
-            s, r = _f32c(scales), _f32c(rotations)
-            bg, vm, pm, tf = _f32c(st.bg), _f32c(st.viewmatrix), _f32c(st.projmatrix), _f32c(st.tanfov)
-            strides = (_vstride(m, V, P * 3), _vstride(c, V, P * NUM_CHANNELS), _vstride(o, V, P),
-                       _vstride(s, V, P * 3), _vstride(r, V, P * 4))
-            bufs = _CallBuffers(dev)
-            _tls.call = bufs
-            rendered = ctypes.c_int(0)
-            # per-call options (guava_call_options): refiner hand-off buffer, the caller's pinned status words,
-            # no-host-wait mode -- given by render_views(refiner_input=True) / GraphedRenderStep
-            call = call or {}
-            aux = call.get("refiner_output")
-            if aux is not None:
-                if aux.dtype != torch.bfloat16 or tuple(aux.shape) != (V, H, W, NUM_CHANNELS) or not aux.is_contiguous():
-                    raise ValueError("refiner output must be a contiguous bfloat16 [V,H,W,32] tensor")
+        # per-call options (guava_call_options): refiner hand-off buffer, the caller's pinned status words,
+        # no-host-wait mode -- given by render_views(refiner_input=True) / GraphedRenderStep
+        call = call or {}
+        aux = call.get("refiner_output")
+        status = call.get("status_words")
+        no_wait = bool(call.get("no_host_wait", False))
+        m, c, o = _f32c(means3D), _f32c(colors_precomp), _f32c(opacities)
+        s, r = _f32c(scales), _f32c(rotations)
+        bg, vm, pm, tf = _f32c(st.bg), _f32c(st.viewmatrix), _f32c(st.projmatrix), _f32c(st.tanfov)
+        strides = (_vstride(m, V, P * 3), _vstride(c, V, P * NUM_CHANNELS), _vstride(o, V, P),
+                   _vstride(s, V, P * 3), _vstride(r, V, P * 4))
+        if BINDING == "compiled":
+            rendered, out_color, radii, geom, binning, img, out_invdepth = _C.rasterize_gaussians_batch(
+                bg, m, c, o, s, r, float(st.scale_modifier), vm, pm, tf, H, W, bool(st.antialiasing), bool(st.debug),
+                aux, status.data_ptr() if status is not None else 0, no_wait)
+            bufs = [geom, binning, img]
+        else:
+            lib = _lib.load()
+            with _device_of(means3D):
+                fopts = dict(dtype=torch.float32, device=dev)
+                out_color = torch.empty(V, NUM_CHANNELS, H, W, **fopts)
+                out_invdepth = torch.empty(V, 1, H, W, **fopts)
+                radii = torch.empty(V, P, dtype=torch.int32, device=dev)
                 if V * P == 0:
-                    aux.zero_()
-            status = call.get("status_words")
-            copts = _lib.CallOptions(refiner_output=_ptr(aux) if aux is not None else 0,
-                                     status_words=status.data_ptr() if status is not None else 0,
-                                     no_host_wait=bool(call.get("no_host_wait", False)))
-            rc = lib.guava_rasterizer_forward_batch(
-                _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
-                V, P, _ptr(bg), W, H,
-                _ptr(m), strides[0], _ptr(c), strides[1], _ptr(o), strides[2], _ptr(s), strides[3],
-                float(st.scale_modifier), _ptr(r), strides[4],
-                _ptr(vm), _ptr(pm), _ptr(tf), _ptr(out_color), _ptr(out_invdepth),
-                int(bool(st.antialiasing)), _ptr(radii), int(bool(st.debug)), _stream_ptr(dev),
-                ctypes.byref(rendered), ctypes.byref(copts))
-            _tls.call = None
-            _tls.last_buffers = bufs.bufs      # (geometry, binning, image) of the most recent batched forward
-            _check(rc)
+                    out_color.zero_(); out_invdepth.zero_()
+                c = _aligned16(c)
+                cb = _CallBuffers(dev)
+                _tls.call = cb
+                rendered = ctypes.c_int(0)
+                if aux is not None:
+                    if aux.dtype != torch.bfloat16 or tuple(aux.shape) != (V, H, W, NUM_CHANNELS) or not aux.is_contiguous():
+                        raise ValueError("refiner output must be a contiguous bfloat16 [V,H,W,32] tensor")
+                    if V * P == 0:
+                        aux.zero_()
+                copts = _lib.CallOptions(refiner_output=_ptr(aux) if aux is not None else 0,
+                                         status_words=status.data_ptr() if status is not None else 0, no_host_wait=no_wait)
+                rc = lib.guava_rasterizer_forward_batch(
+                    _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
+                    V, P, _ptr(bg), W, H,
+                    _ptr(m), strides[0], _ptr(c), strides[1], _ptr(o), strides[2], _ptr(s), strides[3],
+                    float(st.scale_modifier), _ptr(r), strides[4],
+                    _ptr(vm), _ptr(pm), _ptr(tf), _ptr(out_color), _ptr(out_invdepth),
+                    int(bool(st.antialiasing)), _ptr(radii), int(bool(st.debug)), _stream_ptr(dev),
+                    ctypes.byref(rendered), ctypes.byref(copts))
+                _tls.call = None
+                _check(rc)
+                rendered = int(rendered.value)
+                bufs = cb.bufs
+        _tls.last_buffers = bufs      # (geometry, binning, image) of the most recent batched forward
         # unused outputs' upstream gradients arrive as None, not as zero-filled tensors
         ctx.set_materialize_grads(False)
         ctx.settings = st
-        ctx.num_rendered = int(rendered.value)
+        ctx.num_rendered = int(rendered)
         ctx.strides = strides
         ctx.dims = (V, P, H, W)
-        ctx.save_for_backward(m, c, o, s, r, bg, vm, pm, tf, radii, bufs.bufs[0], bufs.bufs[1], bufs.bufs[2])
+        ctx.save_for_backward(m, c, o, s, r, bg, vm, pm, tf, radii, bufs[0], bufs[1], bufs[2])
         ctx.mark_non_differentiable(radii)
         return out_color, radii, out_invdepth
 
     @staticmethod
     def backward(ctx, grad_color, _, grad_invdepth):
-        lib = _lib.load()
         st = ctx.settings
         V, P, H, W = ctx.dims
         m, c, o, s, r, bg, vm, pm, tf, radii, geom, binning, img = ctx.saved_tensors
         dev = m.device
-        with _device_of(m):
-            has_inv = grad_invdepth is not None
-            widths = _GRAD_WIDTHS if has_inv else _GRAD_WIDTHS[:8]
-            n = V * P
-            if grad_color is None:
-                grad_color = torch.zeros(V, NUM_CHANNELS, H, W, dtype=torch.float32, device=dev)
-            # one fill for all gradient tensors.  (Issuing it during the forward on a side stream was
-            # measured slower inside the captured step: the fork/join costs more than the 9 us fill.)
-            flat = torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
-            parts, off = [], 0
-            for w in widths:
-                parts.append(flat[off:off + n * w].view(V, P, w))
-                off += n * w
-            g_color, g_mean2D, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot, g_conic = parts[:8]
-            g_invd = parts[8] if has_inv else None
-            if n:
-                gc = _f32c(grad_color)
-                gi = _f32c(grad_invdepth) if has_inv else None
-                rc = lib.guava_rasterizer_backward_batch(
-                    V, P, int(ctx.num_rendered), _ptr(bg), W, H,
-                    _ptr(m), ctx.strides[0], _ptr(c), ctx.strides[1], _ptr(o), ctx.strides[2],
-                    _ptr(s), ctx.strides[3], float(st.scale_modifier), _ptr(r), ctx.strides[4],
-                    _ptr(vm), _ptr(pm), _ptr(tf), _ptr(radii), _ptr(geom), _ptr(binning), _ptr(img),
-                    _ptr(gc), _ptr(gi),
-                    _ptr(g_mean2D), _ptr(g_conic), _ptr(g_opacity), _ptr(g_color), _ptr(g_invd),
-                    _ptr(g_mean3D), _ptr(g_cov3D), _ptr(g_scale), _ptr(g_rot),
-                    int(bool(st.antialiasing)), int(bool(st.debug)), _stream_ptr(dev))
-                _check(rc)
+        has_inv = grad_invdepth is not None
+        if grad_color is None:
+            grad_color = torch.zeros(V, NUM_CHANNELS, H, W, dtype=torch.float32, device=dev)
+        if BINDING == "compiled":
+            g_mean2D, g_color, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot = _C.rasterize_gaussians_batch_backward(
+                bg, m, radii, c, o, s, r, float(st.scale_modifier), vm, pm, tf, grad_color,
+                grad_invdepth if has_inv else None, geom, int(ctx.num_rendered), binning, img,
+                bool(st.antialiasing), bool(st.debug))
+        else:
+            lib = _lib.load()
+            with _device_of(m):
+                widths = _GRAD_WIDTHS if has_inv else _GRAD_WIDTHS[:8]
+                n = V * P
+                # one fill for all gradient tensors.  (Issuing it during the forward on a side stream was
+                # measured slower inside the captured step: the fork/join costs more than the 9 us fill.)
+                flat = torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
+                parts, off = [], 0
+                for w in widths:
+                    parts.append(flat[off:off + n * w].view(V, P, w))
+                    off += n * w
+                g_color, g_mean2D, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot, g_conic = parts[:8]
+                g_invd = parts[8] if has_inv else None
+                if n:
+                    gc = _f32c(grad_color)
+                    gi = _f32c(grad_invdepth) if has_inv else None
+                    rc = lib.guava_rasterizer_backward_batch(
+                        V, P, int(ctx.num_rendered), _ptr(bg), W, H,
+                        _ptr(m), ctx.strides[0], _ptr(c), ctx.strides[1], _ptr(o), ctx.strides[2],
+                        _ptr(s), ctx.strides[3], float(st.scale_modifier), _ptr(r), ctx.strides[4],
+                        _ptr(vm), _ptr(pm), _ptr(tf), _ptr(radii), _ptr(geom), _ptr(binning), _ptr(img),
+                        _ptr(gc), _ptr(gi),
+                        _ptr(g_mean2D), _ptr(g_conic), _ptr(g_opacity), _ptr(g_color), _ptr(g_invd),
+                        _ptr(g_mean3D), _ptr(g_cov3D), _ptr(g_scale), _ptr(g_rot),
+                        int(bool(st.antialiasing)), int(bool(st.debug)), _stream_ptr(dev))
+                    _check(rc)
 
         def shape_like(g, stride, ref):
             # a tensor shared across views receives the sum of its per-view gradients

@@ -832,3 +832,62 @@ def test_graphed_training_step_that_overflows_leaves_zero_gradients_and_reports_
     ok.replay()
     ok.check()
     assert float(ok.packed.abs().sum()) > 0
+
+
+_CTYPES_SCRIPT = r"""
+import os, sys, torch, numpy as np
+sys.path.insert(0, {root!r})
+from tests import util
+import guava_renderer_b200 as grb
+import diff_gaussian_rasterization_32 as ours
+assert grb.rasterizer.BINDING == os.environ["GUAVA_BINDING"]
+inp = util.inputs_for(3000, 200, 152, seed=21, scale_mult=1.5)
+inp["bg"] = torch.linspace(-1, 1, 32)
+g = torch.Generator().manual_seed(9)
+dL = torch.randn(32, 200, 152, generator=g).to("cuda:0")
+leaf = {{k: inp[k].to("cuda:0").clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}}
+m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+rast = ours.GaussianRasterizer_32(raster_settings=util.settings_for(ours, inp, "cuda:0"))
+color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"], opacities=leaf["opacity"],
+                          scales=leaf["scaling"], rotations=leaf["rotation"], cov3D_precomp=None)
+(color * dL).sum().backward()
+vis = rast.markVisible(leaf["xyz"].detach())
+V = 2
+st = grb.BatchRasterizationSettings(200, 152, torch.tensor([[inp["tanfovx"], inp["tanfovy"]]] * V, device="cuda:0"),
+                                    inp["bg"].to("cuda:0")[None].repeat(V, 1), 1.0, inp["viewmatrix"].to("cuda:0")[None].repeat(V, 1, 1),
+                                    inp["projmatrix"].to("cuda:0")[None].repeat(V, 1, 1))
+bl = {{k: inp[k].to("cuda:0").clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}}
+bc, br, bi = grb.rasterize_gaussians_batch(bl["xyz"], torch.zeros(V, 3000, 3, device="cuda:0"), bl["features"], bl["opacity"],
+                                           bl["scaling"], bl["rotation"], st)
+bc.backward(torch.stack([dL, dL]))
+torch.cuda.synchronize()
+np.savez(sys.argv[1], color=color.detach().cpu().numpy(), radii=radii.cpu().numpy(), invd=invd.detach().cpu().numpy(),
+         vis=vis.cpu().numpy(), bcolor=bc.detach().cpu().numpy(), **{{"g_" + k: v.grad.cpu().numpy() for k, v in leaf.items()}},
+         **{{"b_" + k: v.grad.cpu().numpy() for k, v in bl.items()}}, g_means2D=m2.grad.cpu().numpy())
+"""
+
+
+def test_compiled_and_ctypes_bindings_agree(tmp_path):
+    """The default `_C` is the compiled torch binding (csrc/torch_binding.cpp, what replaces DGR32/ext.cpp +
+    rasterize_points.cu); GUAVA_BINDING=ctypes selects the ctypes binding of the same C ABI.  The reference's call
+    sequence (gaussian_render.py:37-67), markVisible and the batched entry (shared cloud, 2 views) through each, in
+    separate processes: forward outputs bit for bit, gradients to atomic-order tolerance."""
+    import subprocess
+    import sys
+    out = {}
+    for b in ("compiled", "ctypes"):
+        path = str(tmp_path / (b + ".npz"))
+        env = dict(os.environ, GUAVA_BINDING=b)
+        r = subprocess.run([sys.executable, "-c", _CTYPES_SCRIPT.format(root=util.ROOT), path], capture_output=True, text=True,
+                           timeout=600, env=env)
+        assert r.returncode == 0, (b, r.stderr[-800:])
+        out[b] = np.load(path)
+    a, c = out["compiled"], out["ctypes"]
+    for k in ("color", "radii", "invd", "vis", "bcolor"):
+        assert np.array_equal(a[k], c[k]), k
+    assert np.array_equal(a["bcolor"][0], a["color"]) and np.array_equal(a["bcolor"][1], a["color"])
+    for k in a.files:
+        if k.startswith(("g_", "b_")):
+            assert util.rel_err(a[k], c[k]) <= 1e-5, k
+    for k in ("xyz", "features", "opacity", "scaling", "rotation"):     # shared cloud: the two views' gradients are summed
+        assert util.rel_err(a["b_" + k], 2.0 * a["g_" + k]) <= 1e-5, k
