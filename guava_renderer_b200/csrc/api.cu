@@ -31,7 +31,7 @@ static thread_local std::string t_last_error;
 static std::atomic<long long> g_opt_emit_sorted_keys{0};
 static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
-static std::atomic<long long> g_opt_scalar_red{1};   // 1: 4-byte reductions from all 32 lanes (measured faster than gathering 16-byte vectors, profiles/r01_v43)
+static std::atomic<long long> g_opt_tma_staging{0};   // compositors stage feature rows with cp.async.bulk.tensor gather4 (1) or LDGSTS (0)
 static std::atomic<long long> g_opt_block_masks{0};   // experimental, see BLOCK_MASK_SHIFT (internal.cuh)
 static std::atomic<long long> g_opt_os_identify_ranges{0};   // sort mode 1: recompute the tile ranges from the sorted keys (identifyTileRanges restated) although the tile scan already wrote them
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
@@ -502,7 +502,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
             timer.begin(3);
             launch_onesweep_binning(in, g, im, (uint32_t*)(geom + L.point_offsets), (uint64_t*)(bin + L.keys_sorted),
                                     b.point_list, b.keys_unsorted, (uint32_t*)(bin + L.os_vals_alt),
-                                    (uint32_t*)(bin + L.os_scratch), cap, g_opt_os_identify_ranges.load() != 0, stream);
+                                    (uint32_t*)(bin + L.os_scratch), cap, g_opt_os_identify_ranges.load() != 0, block_masks, stream);
             timer.end();
             GUAVA_STAGE("onesweep", debug);
         } else {
@@ -516,7 +516,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         GUAVA_STAGE("tile_sort", debug);
         }
         timer.begin(4);
-        launch_render_forward(in, g, im, b, out_color, out_invdepth, block_masks, stream);
+        launch_render_forward(in, g, im, b, out_color, out_invdepth, block_masks, g_opt_tma_staging.load() != 0, stream);
         timer.end();
         GUAVA_STAGE("render_forward", debug);
         if (async_fwd) { R = 0xFFFFFFFFu; break; }
@@ -586,12 +586,10 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     b.keys_sorted = nullptr;
     b.capacity = 0;
 
-    // 16-byte vector reductions need 16-byte aligned rows (dL_dcolor rows are 128 bytes)
-    const int vec_red = (((uintptr_t)dL_dcolor & 15) == 0) && g_opt_scalar_red.load() == 0;
     StageTimer timer(stream);
     timer.begin(5);
     GUAVA_CUDA(cudaMemsetAsync(g.grad_geo, 0, (size_t)in.V * in.P * 32, stream));
-    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, vec_red, block_masks, stream);
+    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, block_masks, g_opt_tma_staging.load() != 0, stream);
     timer.end();
     GUAVA_STAGE("render_backward", debug);
     timer.begin(6);
@@ -818,7 +816,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "exact_binning")) return &g_opt_exact_binning;
     if (!strcmp(name, "capacity_hint")) return &g_opt_capacity_hint;
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
-    if (!strcmp(name, "scalar_red")) return &g_opt_scalar_red;
+    if (!strcmp(name, "tma_staging")) return &g_opt_tma_staging;
     if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;
     if (!strcmp(name, "block_masks")) return &g_opt_block_masks;
     if (!strcmp(name, "os_identify_ranges")) return &g_opt_os_identify_ranges;

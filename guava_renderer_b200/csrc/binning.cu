@@ -281,22 +281,6 @@ __device__ __forceinline__ uint32_t next_pow2(uint32_t n)
 // is register-to-register for j < E, a warp shuffle for j < 32*E, and goes through shared memory
 // (transposed layout, conflict-free) only for the few steps with j >= 32*E -- 6 of 55 steps at
 // N = 1024 -- where the first version synchronised the block after every step.
-// Option "block_masks": bits 24..31 of a point_list entry = the 8x4 pixel blocks of the tile (block b = column
-// b & 1, row b >> 1, as the compositors number them) that the splat provably cannot touch -- the compositors'
-// own test (splat_may_touch), evaluated once per list entry instead of once per (block, entry) and kernel.
-__device__ __forceinline__ uint32_t untouched_blocks(const SplatRec* __restrict__ recs, uint32_t id, float tx0, float ty0)
-{
-    const float4* __restrict__ rp = reinterpret_cast<const float4*>(recs + id);
-    const float4 c0 = rp[0], c1 = rp[1];
-    uint32_t bits = 0;
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const float wx0 = tx0 + (float)((b & 1) * 8), wy0 = ty0 + (float)((b >> 1) * 4);
-        if (!splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f)) bits |= 1u << b;
-    }
-    return bits << BLOCK_MASK_SHIFT;
-}
-
 template <int E, int MASKS>
 __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__ src, uint32_t n, uint64_t* skeys,
                                                     uint32_t* __restrict__ point_list, uint64_t* __restrict__ keys_sorted,
@@ -406,10 +390,12 @@ tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __r
 static constexpr uint32_t SORT_SMALL = 2048;    // 16 KB of keys, 256 threads
 static constexpr uint32_t SORT_LARGE = 16384;   // 128 KB of keys, 1024 threads
 
+template <int MASKS>
 __global__ void __launch_bounds__(1024)
 tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
                        uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                       uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles,
+                       const SplatRec* __restrict__ mask_recs, int P, int gx)
 {
     extern __shared__ uint64_t skeys[];
     if (num_rendered[1] || num_rendered[4] <= SORT_SMALL) return;
@@ -419,12 +405,22 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
         const uint32_t n = r.y - r.x;
         if (n <= SORT_SMALL) continue;   // block-uniform
         const uint64_t tile_hi = (uint64_t)(tile % tiles_per_view) << 32;
+        const SplatRec* mr = nullptr;
+        float tx0 = 0.0f, ty0 = 0.0f;
+        if (MASKS) {
+            const uint32_t view = (uint32_t)tile / (uint32_t)tiles_per_view, t = (uint32_t)tile % (uint32_t)tiles_per_view;
+            mr = mask_recs + (size_t)view * P;
+            tx0 = (float)((t % (uint32_t)gx) * TILE_X);
+            ty0 = (float)((t / (uint32_t)gx) * TILE_Y);
+        }
         if (n <= SORT_LARGE) {
             for (uint32_t k = tid; k < n; k += 1024) skeys[k] = keys[r.x + k];
             bitonic_sort_ascending(skeys, n, next_pow2(n), tid, 1024);
             for (uint32_t k = tid; k < n; k += 1024) {
                 const uint64_t key = skeys[k];
-                point_list[r.x + k] = (uint32_t)key;
+                uint32_t id = (uint32_t)key;
+                if (MASKS) id |= untouched_blocks(mr, id, tx0, ty0);
+                point_list[r.x + k] = id;
                 if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
             }
         } else {
@@ -432,7 +428,9 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
             bitonic_sort_ascending(seg, n, next_pow2(n), tid, 1024);
             for (uint32_t k = tid; k < n; k += 1024) {
                 const uint64_t key = seg[k];
-                point_list[r.x + k] = (uint32_t)key;
+                uint32_t id = (uint32_t)key;
+                if (MASKS) id |= untouched_blocks(mr, id, tx0, ty0);
+                point_list[r.x + k] = id;
                 if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
             }
         }
@@ -452,7 +450,9 @@ void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img,
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
-        cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(tile_sort_large_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(SORT_LARGE * sizeof(uint64_t)));
+        cudaFuncSetAttribute(tile_sort_large_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
@@ -463,11 +463,14 @@ void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img,
         tile_sort_small_kernel<0><<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted,
                                                               b.point_list, b.keys_sorted, in.tiles, nullptr, 0, 0);
     count_launch();
-    // (lists sorted by the long-bucket kernel keep plain ids: no block of theirs is marked untouched)
     if (!with_large) return;
     const int big_grid = total_tiles < sm_count() ? total_tiles : sm_count();
-    tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
-        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
+    if (block_masks)
+        tile_sort_large_kernel<1><<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
+            img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles, g.rec, in.P, in.gx);
+    else
+        tile_sort_large_kernel<0><<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
+            img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles, nullptr, 0, 0);
     count_launch();
 }
 

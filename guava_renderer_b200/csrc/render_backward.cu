@@ -35,7 +35,9 @@
 //    rows, the 32 blending weights -- goes through shared memory.
 #include "internal.cuh"
 #include "tma.cuh"
+#include <cuda.h>
 #include <cstdlib>
+#include <cstring>
 
 namespace guava {
 
@@ -71,23 +73,16 @@ __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&
     }
 }
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d)
-{
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-                 : "memory");
-}
-
 // One warp (= one CTA) per 8x4 pixel block, as in the forward kernel: no block
 // barrier, private double-buffered stage of culled survivors.
-// VEC_RED: 0 (default) = 4-byte reductions, one 128-byte request from all 32 lanes per (warp, Gaussian)
-// plus 28 lanes for the packed record; 1 = 16-byte vector reductions (red.global.add.v4.f32) from 8 lanes,
-// which costs three gathering shuffles per splat on the data pipe and measured 2 % slower
-// (option "scalar_red" = 0 selects it; profiles/r01_v43).
+// Gradients leave the SM as 4-byte reductions: one 128-byte request from all 32 lanes per (warp, Gaussian) for
+// dL_dcolors plus 28 lanes for the packed record.  (16-byte vector reductions, red.global.add.v4.f32 from 8 lanes,
+// cost three gathering shuffles per splat on the data pipe and measured 2 % slower, profiles/r01_v43; removed.)
 // MASKS = 1 (option "block_masks"): see render_forward.cu -- the list entries carry the forward's block masks, no
-// footprint test is run here.
-template <int VEC_RED, int MASKS>
+// footprint test is run here.  TMA = 1 (option "tma_staging"): feature rows staged by cp.async.bulk.tensor gather4.
+template <int MASKS, int TMA>
 __global__ void __launch_bounds__(32, 12)
-render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
+render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                        const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
@@ -95,6 +90,8 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 {
     __shared__ BwdStage stage[2];
     __shared__ __align__(16) float ex[4][32];   // blending weights of a survivor, one per pixel: two pairs in flight
+    __shared__ __align__(16) uint32_t srows[2][32];   // TMA: tensor-map row of the survivor in each slot
+    __shared__ __align__(8) uint64_t bars[2];         // TMA: one transaction barrier per stage
 
     // The forward's binning overflowed (a replayed capture whose capacity was outgrown): its instance kernels
     // skipped themselves, the lists this kernel would walk were never written.  Gradients stay zero; the caller
@@ -106,6 +103,15 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     const size_t HW = (size_t)in.H * in.W;
     uint32_t parity = 0;   // ex buffers (parity, parity+1) & 3 are used by the next pair
     float* const exbase = &ex[0][0];
+    uint32_t phase = 0;    // TMA: bit s = parity the next wait on bars[s] uses
+    if (TMA) {
+        if (lane == 0) {
+            tma::mbar_init(&bars[0], 1);
+            tma::mbar_init(&bars[1], 1);
+            tma::fence_mbar_init();
+        }
+        __syncwarp();
+    }
 
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
     const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
@@ -177,6 +183,7 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
+    const uint32_t vrow0 = (uint32_t)(((size_t)v * in.colors_vs) / NUM_CHANNELS);   // TMA: first tensor-map row of this view
 
     constexpr uint32_t NO_ID = 0xffffffffu;
     // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front); same software
@@ -212,18 +219,36 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
                 q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
                 (&st.rd[0].x)[slot] = c1.z;
-                // the lane's own 128-byte feature row as eight 16-byte asynchronous copies, piece order rotated by
-                // the slot so that the lanes of one instruction fall on distinct bank groups (render_forward.cu)
-                const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
-                char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
+                if (TMA) {
+                    srows[c & 1][slot] = vrow0 + id;
+                } else {
+                    // the lane's own 128-byte feature row as eight 16-byte asynchronous copies, piece order rotated by
+                    // the slot so that the lanes of one instruction fall on distinct bank groups (render_forward.cu)
+                    const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
+                    char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const int piece = ((j + slot) & 7) * 16;
-                    tma::cp_async16(dstf + piece, src + piece);
+                    for (int j = 0; j < 8; j++) {
+                        const int piece = ((j + slot) & 7) * 16;
+                        tma::cp_async16(dstf + piece, src + piece);
+                    }
+                }
+            }
+            if (TMA) {   // four survivor rows per gather4, last group padded with the first survivor's row (render_forward.cu)
+                const int nsurv = __popc(mask);
+                const int ngroups = (nsurv + 3) >> 2;
+                const uint32_t first_row = vrow0 + __shfl_sync(0xffffffffu, id, __ffs(mask) - 1);
+                if (lane < 3 && nsurv + lane < 4 * ngroups) srows[c & 1][nsurv + lane] = first_row;
+                __syncwarp();
+                if (lane == 0) {
+                    tma::mbar_arrive_expect_tx(&bars[c & 1], (uint32_t)ngroups * 512u);
+                    for (int gq = 0; gq < ngroups; gq++) {
+                        const uint4 r = *reinterpret_cast<const uint4*>(&srows[c & 1][4 * gq]);
+                        tma::tensor_gather4_g2s(&st.feat[4 * gq][0], &fmap, 0, (int)r.x, (int)r.y, (int)r.z, (int)r.w, &bars[c & 1]);
+                    }
                 }
             }
         }
-        tma::cp_async_commit();   // one group per chunk, empty or not: the waits count groups
+        if (!TMA) tma::cp_async_commit();   // one group per chunk, empty or not: the waits count groups
         return mask;
     };
 
@@ -242,14 +267,19 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
         // id_cur: ids of chunk c (for the gradient addresses); id_next / a0,a1: chunk c+1
         uint32_t mask_next = 0u;
         if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
-        else tma::cp_async_commit();
+        else if (!TMA) tma::cp_async_commit();
         const uint32_t id_after = id_next;
         id_next = id_nn;
         load_rec(id_next, a0, a1);
         id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
-            tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+            if (TMA) {
+                tma::mbar_wait(&bars[s], (phase >> s) & 1u);
+                phase ^= 1u << s;
+            } else {
+                tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+            }
             __syncwarp();
             const BwdStage& stg = stage[s];
             int kp = 0;
@@ -371,53 +401,43 @@ render_backward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
                 const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
-                if (VEC_RED) {
-                    const float a1 = __shfl_down_sync(0xffffffffu, col0, 1);
-                    const float a2 = __shfl_down_sync(0xffffffffu, col0, 2);
-                    const float a3 = __shfl_down_sync(0xffffffffu, col0, 3);
-                    const float b1 = __shfl_down_sync(0xffffffffu, col1, 1);
-                    const float b2 = __shfl_down_sync(0xffffffffu, col1, 2);
-                    const float b3 = __shfl_down_sync(0xffffffffu, col1, 3);
-                    if ((lane & 3) == 0) {
-                        if (any0) red_add_v4(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0, a1, a2, a3);
-                        if (any1) red_add_v4(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1, b1, b2, b3);
-                    }
-                    if (any0 && lane < 28) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
-                    if (any1 && lane < 28) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
-                } else {
-                    const bool geo_lane = lane < 28;   // lanes 4k..4k+3: partials of moment k (moment 7 is unused)
-                    if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
-                    if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
-                    if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
-                    if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
-                }
+                const bool geo_lane = lane < 28;   // lanes 4k..4k+3: partials of moment k (moment 7 is unused)
+                if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
+                if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
+                if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
+                if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
             }
         }
         mask_cur = mask_next;
         id_cur = id_after;
         __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
     }
-    tma::cp_async_wait<0>();
+    if (!TMA) tma::cp_async_wait<0>();
     __syncwarp();   // nothing in flight when the next block reuses the stages
   }
 }
 
+bool make_feature_tensor_map(const Inputs& in, CUtensorMap* out);   // render_forward.cu
+
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
-                            const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor, int vec_red,
-                            int block_masks, cudaStream_t s)
+                            const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor,
+                            int block_masks, int tma_staging, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
+    CUtensorMap fmap;
+    memset(&fmap, 0, sizeof(fmap));
+    if (tma_staging && !make_feature_tensor_map(in, &fmap)) tma_staging = 0;
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 12; }();   // tuning knob
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
-#define GUAVA_LAUNCH_BWD(VR, MK)                                                                                          \
-    render_backward_kernel<VR, MK><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.final_T,   \
-                                                       img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo,    \
-                                                       img.num_rendered)
-    if (block_masks) { if (vec_red) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(0, 1); }
-    else             { if (vec_red) GUAVA_LAUNCH_BWD(1, 0); else GUAVA_LAUNCH_BWD(0, 0); }
+#define GUAVA_LAUNCH_BWD(MK, TM)                                                                                          \
+    render_backward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,          \
+                                                       img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,   \
+                                                       g.grad_geo, img.num_rendered)
+    if (block_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
+    else             { if (tma_staging) GUAVA_LAUNCH_BWD(0, 1); else GUAVA_LAUNCH_BWD(0, 0); }
 #undef GUAVA_LAUNCH_BWD
     cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();

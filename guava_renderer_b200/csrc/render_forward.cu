@@ -29,8 +29,10 @@
 //    (forward.cu:371-372).
 #include "internal.cuh"
 #include "tma.cuh"
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <cstdlib>
+#include <cstring>
 
 namespace guava {
 
@@ -46,19 +48,33 @@ struct __align__(128) FwdStage {
 
 // MASKS = 1 (option "block_masks"): the tile sort has marked, in bits 24..31 of every list entry, the blocks the
 // splat cannot touch; the footprint test is that bit, and records are gathered for survivors only.
-template <int MASKS>
+// TMA = 1 (option "tma_staging"): the survivors' 128-byte feature rows are fetched by the TMA unit -- one elected
+// lane issues cp.async.bulk.tensor...tile::gather4 over a [rows, 32] tensor map of colors_precomp, four survivor rows
+// per instruction, completion on a per-stage mbarrier -- instead of eight 16-byte LDGSTS per survivor lane.
+template <int MASKS, int TMA>
 __global__ void __launch_bounds__(32, 16)
-render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
+render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                       const uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
     __shared__ FwdStage stage[2];
+    __shared__ __align__(16) uint32_t srows[2][32];   // TMA: tensor-map row of the survivor in each slot
+    __shared__ __align__(8) uint64_t bars[2];         // TMA: one transaction barrier per stage
 
     if (num_rendered[1]) return;   // binning overflowed; the host re-runs
     const int lane = threadIdx.x;
     const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t phase = 0;            // TMA: bit s = parity the next wait on bars[s] uses
+    if (TMA) {
+        if (lane == 0) {
+            tma::mbar_init(&bars[0], 1);
+            tma::mbar_init(&bars[1], 1);
+            tma::fence_mbar_init();
+        }
+        __syncwarp();
+    }
 
     // Persistent warps: the grid is sized to fill the machine once and every warp pulls
     // 8x4 pixel blocks from a global work counter (num_rendered[2], zeroed by the tile
@@ -96,6 +112,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
 
     const SplatRec* __restrict__ vrecs = recs + (size_t)v * in.P;
     const float* __restrict__ vfeat = in.colors + (size_t)v * in.colors_vs;
+    const uint32_t vrow0 = (uint32_t)(((size_t)v * in.colors_vs) / NUM_CHANNELS);   // TMA: first tensor-map row of this view
 
     constexpr uint32_t NO_ID = 0xffffffffu;
     // Software pipeline over 32-entry chunks of the tile list.  While chunk c is blended,
@@ -136,19 +153,48 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
                 q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
                 q = &st.dpos[0].x + o; q[0] = c1.z; q[2] = __uint_as_float((uint32_t)(c << 5) + (uint32_t)lane + 1u);
-                // the lane's own 128-byte feature row as eight 16-byte asynchronous copies; the piece order is
-                // rotated by the slot so that the 32 lanes of one instruction fall on distinct bank groups
-                const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
-                char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
+                if (TMA) {
+                    srows[c & 1][slot] = vrow0 + id;
+                } else {
+                    // the lane's own 128-byte feature row as eight 16-byte asynchronous copies; the piece order is
+                    // rotated by the slot so that the 32 lanes of one instruction fall on distinct bank groups
+                    const char* src = reinterpret_cast<const char*>(vfeat + (size_t)id * NUM_CHANNELS);
+                    char* dstf = reinterpret_cast<char*>(&st.feat[slot][0]);
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const int piece = ((j + slot) & 7) * 16;
-                    tma::cp_async16(dstf + piece, src + piece);
+                    for (int j = 0; j < 8; j++) {
+                        const int piece = ((j + slot) & 7) * 16;
+                        tma::cp_async16(dstf + piece, src + piece);
+                    }
+                }
+            }
+            if (TMA) {
+                // four survivor rows per instruction; the last group is padded with the first survivor's row (its
+                // copies land in unused slots), so every instruction completes exactly 512 bytes
+                const int nsurv = __popc(mask);
+                const int ngroups = (nsurv + 3) >> 2;
+                const uint32_t first_row = vrow0 + __shfl_sync(0xffffffffu, id, __ffs(mask) - 1);
+                if (lane < 3 && nsurv + lane < 4 * ngroups) srows[c & 1][nsurv + lane] = first_row;
+                __syncwarp();
+                if (lane == 0) {
+                    tma::mbar_arrive_expect_tx(&bars[c & 1], (uint32_t)ngroups * 512u);
+                    for (int gq = 0; gq < ngroups; gq++) {
+                        const uint4 r = *reinterpret_cast<const uint4*>(&srows[c & 1][4 * gq]);
+                        tma::tensor_gather4_g2s(&st.feat[4 * gq][0], &fmap, 0, (int)r.x, (int)r.y, (int)r.z, (int)r.w, &bars[c & 1]);
+                    }
                 }
             }
         }
-        tma::cp_async_commit();   // one group per chunk, empty or not: the waits below count groups
+        if (!TMA) tma::cp_async_commit();   // one group per chunk, empty or not: the waits below count groups
         return mask;
+    };
+    // the rows of a staged chunk have landed (and, LDGSTS: every older group)
+    auto wait_rows = [&](int s) {
+        if (TMA) {
+            tma::mbar_wait(&bars[s], (phase >> s) & 1u);
+            phase ^= 1u << s;
+        } else {
+            tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+        }
     };
 
     float T = 1.0f;
@@ -171,13 +217,13 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
     for (int c = 0; c < nchunks; c++) {
         uint32_t mask_next = 0u;
         if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
-        else tma::cp_async_commit();
+        else if (!TMA) tma::cp_async_commit();
         id_next = id_nn;
         load_rec(id_next, a0, a1);
         id_nn = load_id(c + 3);
         const int s = c & 1;
         if (mask_cur != 0u) {
-            tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+            wait_rows(s);
             __syncwarp();              // ... and the staging lanes' stores and copies are visible to every lane
             const FwdStage& st = stage[s];
             const float4* __restrict__ featp = reinterpret_cast<const float4*>(&st.feat[0][0]);
@@ -244,8 +290,9 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
                 if (__all_sync(0xffffffffu, done)) warp_done = true;
             }
         }
-        if (warp_done) {
-            tma::cp_async_wait<0>();   // never leave the block with a copy still in flight
+        if (warp_done) {   // never leave the block with a copy still in flight
+            if (TMA) { if (mask_next != 0u) wait_rows(s ^ 1); }
+            else tma::cp_async_wait<0>();
             break;
         }
         mask_cur = mask_next;
@@ -285,7 +332,7 @@ render_forward_kernel(const Inputs in, const SplatRec* __restrict__ recs,
             }
         }
     }
-    tma::cp_async_wait<0>();
+    if (!TMA) tma::cp_async_wait<0>();
     __syncwarp();   // the stages are reused by the next block
   }
 }
@@ -329,20 +376,50 @@ void launch_selftest_cull(int n, const float* splats, const float* origins, uint
     count_launch();
 }
 
+// Tensor map of colors_precomp as a [rows, 32] fp32 matrix with a {32, 1} box: what tile::gather4 indexes by row.
+// Encoded on the host per call (the base address is the caller's tensor); cuTensorMapEncodeTiled is taken from the
+// driver through the runtime, so the library does not link against libcuda.
+bool make_feature_tensor_map(const Inputs& in, CUtensorMap* out)
+{
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            fn = nullptr;
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
+    if (encode == nullptr || (in.colors_vs % NUM_CHANNELS) != 0) return false;
+    const cuuint64_t rows = (cuuint64_t)(in.V > 0 ? in.V - 1 : 0) * (in.colors_vs / NUM_CHANNELS) + (cuuint64_t)in.P;
+    const cuuint64_t dims[2] = {NUM_CHANNELS, rows};
+    const cuuint64_t strides[1] = {NUM_CHANNELS * sizeof(float)};
+    const cuuint32_t box[2] = {NUM_CHANNELS, 1};
+    const cuuint32_t estr[2] = {1, 1};
+    return encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(in.colors), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
-                           float* out_color, float* out_invdepth, int block_masks, cudaStream_t s)
+                           float* out_color, float* out_invdepth, int block_masks, int tma_staging, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
+    CUtensorMap fmap;
+    memset(&fmap, 0, sizeof(fmap));
+    if (tma_staging && !make_feature_tensor_map(in, &fmap)) tma_staging = 0;   // no driver entry point: LDGSTS staging
     const long long total = (long long)in.tiles * 8 * in.V;
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_FWD_CTAS"); return e ? atoi(e) : 16; }();   // tuning knob
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
-    if (block_masks)
-        render_forward_kernel<1><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
-                                                     img.final_T, img.n_contrib, out_color, out_invdepth);
-    else
-        render_forward_kernel<0><<<grid, 32, 0, s>>>(in, g.rec, img.ranges, img.tile_order, b.point_list, img.num_rendered,
-                                                     img.final_T, img.n_contrib, out_color, out_invdepth);
+#define GUAVA_LAUNCH_FWD(MK, TM)                                                                                        \
+    render_forward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,             \
+                                                      img.num_rendered, img.final_T, img.n_contrib, out_color, out_invdepth)
+    if (block_masks) { if (tma_staging) GUAVA_LAUNCH_FWD(1, 1); else GUAVA_LAUNCH_FWD(1, 0); }
+    else             { if (tma_staging) GUAVA_LAUNCH_FWD(0, 1); else GUAVA_LAUNCH_FWD(0, 0); }
+#undef GUAVA_LAUNCH_FWD
     count_launch();
 }
 

@@ -59,6 +59,19 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
         : "memory");
 }
 
+// TMA tensor copy, sm_100 gather form: FOUR rows of a 2-D tensor, given by their row coordinates, land in
+// consecutive box-sized pieces of shared memory (here: four 128-byte feature rows -> 512 bytes) with one
+// instruction from one lane (SASS: UTMALDG...GATHER4); completion on the mbarrier's transaction count.  `tmap` is the
+// generic address of a CUtensorMap kernel parameter (__grid_constant__); the box of the map is {row length, 1}.
+__device__ __forceinline__ void tensor_gather4_g2s(void* smem_dst, const void* tmap, int col, int r0, int r1, int r2, int r3,
+                                                   uint64_t* bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::
+            "r"(smem_addr(smem_dst)), "l"(tmap), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(smem_addr(bar))
+        : "memory");
+}
+
 // 16-byte asynchronous copy global -> shared (LDGSTS), completion by commit/wait groups of the issuing thread
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
 {

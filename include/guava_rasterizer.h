@@ -300,9 +300,12 @@ int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int widt
  * identifyTileRanges, rasterizer_impl.cu:280-320; identical keys, values and ranges; -1 (default): 1 when
  * the previous call of the same shape produced a tile list longer than 2048 instances, else 0;
  * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes),
- * "scalar_red" (0/1, default 1: the backward compositor adds dL_dcolors with one 4-byte reduction per
- * lane -- a 128-byte request per (pixel block, Gaussian); 0 = gather 16-byte vectors into 8 lanes first,
- * needs 16-byte aligned dL_dcolors, measured 1 % slower),
+ * "tma_staging" (0/1: the compositors fetch the survivors' 128-byte feature rows with TMA tensor copies --
+ * cp.async.bulk.tensor.2d ... tile::gather4 over a [rows,32] tensor map of colors_precomp, four rows per
+ * instruction from one elected lane, mbarrier completion -- instead of eight 16-byte cp.async per lane; same bytes,
+ * same results; needs colors_view_stride % 32 == 0),
+ * "os_identify_ranges" (0/1, default 0: sort mode 1 re-derives the tile ranges from the sorted keys --
+ * identifyTileRanges, rasterizer_impl.cu:116-138, restated -- although the tile scan has already written them),
  * "block_masks" (0/1, default 0; EXPERIMENTAL, compiled but not yet run on hardware: the tile sort evaluates the
  * compositors' footprint test once per list entry and stores the blocks a splat cannot touch in bits 24..31 of the
  * point_list entries, which then are not plain indices; P < 2^24; must not change between a forward call and its

@@ -168,48 +168,38 @@ def test_backward_vs_reference_build(ref, case, with_invdepth):
         util.grad_gate(k, go[k], gr[k])       # per element: |a-b| <= 1e-4 |b| + 1e-6 max|b|
 
 
-def test_backward_vector_reduction_option_vs_reference_build(ref):
-    """Option scalar_red = 0: dL_dcolors leaves the SM as 16-byte vector reductions from 8 lanes instead of the
-    default 4-byte reductions from all 32; same gradients."""
-    case = GRAD_CASES[0]
-    inp = util.inputs_for(**case)
-    inp["bg"] = torch.linspace(-1, 1, 32)
-    g = torch.Generator().manual_seed(9)
-    dL_dcolor = torch.randn(32, case["H"], case["W"], generator=g)
-    dL_dinv = torch.randn(1, case["H"], case["W"], generator=g)
-    assert grb.get_option("scalar_red") == 1
-    grb.set_option("scalar_red", 0)
-    try:
-        _, go = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
-    finally:
-        grb.set_option("scalar_red", 1)
-    _, gr = _run_autograd(ref, inp, dL_dcolor, dL_dinv)
-    for k in gr:
-        assert util.rel_err(go[k], gr[k]) <= 1e-4, (k, util.rel_err(go[k], gr[k]))
-
-
-@pytest.mark.skipif(os.environ.get("GUAVA_TEST_EXPERIMENTAL") != "1",
-                    reason="option block_masks was written after round 1's GPU minutes were spent: compiled, the default "
-                           "kernels' SASS is unchanged, but it has not run on hardware; GUAVA_TEST_EXPERIMENTAL=1 enables")
+@pytest.mark.parametrize("opts", [dict(block_masks=1), dict(tma_staging=1), dict(block_masks=1, tma_staging=1)],
+                         ids=["block_masks", "tma_staging", "block_masks+tma_staging"])
 @pytest.mark.parametrize("case", GRAD_CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
-def test_block_masks_option_gives_the_same_results(case):
-    """Experimental option block_masks: the footprint test of the compositors is evaluated once per list entry in the
-    tile sort and carried in bits 24..31 of point_list; same survivors, so the image is bit-identical and the
-    gradients agree to reduction order."""
+def test_compositor_options_give_the_same_results(case, opts, sort_mode):
+    """Options of the compositors that must not change a result.  block_masks: the footprint test is evaluated once
+    per list entry by the binning stage and carried in bits 24..31 of point_list (same survivors).  tma_staging: the
+    survivors' feature rows are staged by cp.async.bulk.tensor gather4 instead of LDGSTS (same bytes).  Image
+    bit-identical, gradients equal to reduction order, in both binning modes."""
     inp = util.inputs_for(**case)
     inp["bg"] = torch.linspace(-1, 1, 32)
     g = torch.Generator().manual_seed(9)
     dL_dcolor = torch.randn(32, case["H"], case["W"], generator=g)
     dL_dinv = torch.randn(1, case["H"], case["W"], generator=g)
-    c0, g0 = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
-    grb.set_option("sort_mode", 0)
-    grb.set_option("block_masks", 1)
+    base = {k: grb.get_option(k) for k in opts}
+    for k in opts:
+        grb.set_option(k, 0)
     try:
+        c0, g0 = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
+        o0 = _ours_forward(inp)
+        for k, v in opts.items():
+            grb.set_option(k, v)
         c1, g1 = _run_autograd(ours, inp, dL_dcolor, dL_dinv)
+        o1 = _ours_forward(inp)
     finally:
-        grb.set_option("block_masks", 0)
-        grb.set_option("sort_mode", -1)
+        for k, v in base.items():
+            grb.set_option(k, v)
     assert np.array_equal(c0, c1)
+    for k in ("point_list", "keys", "ranges", "n_contrib", "radii", "color", "invdepth"):
+        assert np.array_equal(o0[k], o1[k]), k
+    assert np.array_equal(_bits(o0["final_T"]), _bits(o1["final_T"]))
+    if opts.get("block_masks"):
+        assert o1["block_masks"] == 1 and o1["point_list_masks"].any()
     for k in g0:
         assert util.rel_err(g1[k], g0[k]) <= 1e-5, (k, util.rel_err(g1[k], g0[k]))
 
