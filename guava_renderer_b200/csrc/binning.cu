@@ -55,20 +55,24 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t x, uint32
 
 // Scan scratch (zeroed with the tile counters, which it follows in the image buffer): ticket, longest list,
 // 256 length bins, 256 bin cursors, one look-back word per 1024-tile block.
-constexpr int SCAN_TICKET = 0, SCAN_LONGEST = 1, SCAN_BINS = 32, SCAN_BINCUR = 288, SCAN_STATE = 544;
+constexpr int SCAN_TICKET = 0, SCAN_LONGEST = 1, SCAN_DONE = 2, SCAN_BINS = 32, SCAN_BINCUR = 288, SCAN_STATE = 544;
 size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (total_tiles + 1023) / 1024 + 1); }
 
-// Kernel 1: one block per 1024 tiles, chained by a decoupled look-back (blocks ordered by ticket): exclusive
-// scan of the per-tile counts = tile ranges (identifyTileRanges) and bucket cursors, the histogram of list
-// lengths for kernel 2, the longest list, and -- by the last block of the chain -- R and the overflow flag.
+// One block per 1024 tiles, chained by a decoupled look-back (blocks ordered by ticket): exclusive scan of the
+// per-tile counts = tile ranges (identifyTileRanges) and bucket cursors, the histogram of list lengths, the longest
+// list, and -- by the last block of the chain -- R and the overflow flag.  The block that FINISHES last then writes
+// the work items in longest-list-first order (counting sort on the length bin), in which the persistent compositing
+// kernels pull their blocks so that the long lists -- each a serial chain through one warp -- start first and the
+// short ones fill the tail.  (Until round 2 that was a second, dependent launch: 6 us of latency per step.)
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ scratch,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
-                 uint32_t list_limit, uint32_t call_flags)
+                 uint32_t list_limit, uint32_t call_flags, uint4* __restrict__ tile_order)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
-    __shared__ uint32_t s_bid, s_carry;
+    __shared__ uint32_t bin_base[256];
+    __shared__ uint32_t s_bid, s_carry, s_last;
     const int tid = threadIdx.x, lane = tid & 31;
     if (tid < 256) bins[tid] = 0u;
     if (tid == 0) s_bid = atomicAdd(scratch + SCAN_TICKET, 1u);
@@ -125,34 +129,33 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
             *reinterpret_cast<volatile unsigned long long*>(host_R) =
                 (unsigned long long)R | ((unsigned long long)(longest | (overflow ? 0x80000000u : 0u)) << 32);
     }
-}
 
-// Kernel 2: work items in longest-list-first order (counting sort on the length bin), in which the persistent
-// compositing kernels pull their blocks so that the long lists -- each a serial chain through one warp --
-// start first and the short ones fill the tail.
-__global__ void __launch_bounds__(1024)
-tile_order_kernel(int n, const uint2* __restrict__ ranges, uint32_t* __restrict__ scratch, uint4* __restrict__ tile_order)
-{
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t bin_base[256];
-    const int tid = threadIdx.x, lane = tid & 31;
+    // ---- work order: by the block that finishes last (all ranges and all length bins are then complete)
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(scratch + SCAN_DONE, 1u) == (uint32_t)nblocks - 1u ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
     {
         uint32_t dummy;
-        const uint32_t mine = tid < 256 ? scratch[SCAN_BINS + tid] : 0u;
+        const uint32_t mine = tid < 256 ? __ldcg(scratch + SCAN_BINS + tid) : 0u;
         const uint32_t ex = block_exclusive_scan_1024(mine, warp_sums, tid, dummy);
-        if (tid < 256) bin_base[tid] = ex;
+        if (tid < 256) { bin_base[tid] = ex; bins[tid] = 0u; }   // bins: now the cursors of the counting sort
     }
     __syncthreads();
-    const int k = blockIdx.x * 1024 + tid;
-    const uint2 r = k < n ? ranges[k] : make_uint2(0u, 0u);
-    const uint32_t c = r.y - r.x;
-    const uint32_t bin = k < n ? 255u - min(c >> 3, 255u) : 256u;   // 256: no tile
-    const uint32_t peers = __match_any_sync(0xffffffffu, bin);
-    const int leader = __ffs(peers) - 1;
-    uint32_t pos = 0;
-    if (lane == leader && bin < 256u) pos = bin_base[bin] + atomicAdd(scratch + SCAN_BINCUR + bin, (uint32_t)__popc(peers));
-    pos = __shfl_sync(0xffffffffu, pos, leader);
-    if (bin < 256u) tile_order[pos + __popc(peers & ((1u << lane) - 1u))] = make_uint4((uint32_t)k, r.x, r.y, 0u);
+    for (int k0 = 0; k0 < n; k0 += 1024) {
+        const int kk = k0 + tid;
+        const uint2 r = kk < n ? __ldcg(ranges + kk) : make_uint2(0u, 0u);
+        const uint32_t cc = r.y - r.x;
+        const uint32_t bin = kk < n ? 255u - min(cc >> 3, 255u) : 256u;   // 256: no tile
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        const int leader = __ffs(peers) - 1;
+        uint32_t pos = 0;
+        if (lane == leader && bin < 256u) pos = bin_base[bin] + atomicAdd(&bins[bin], (uint32_t)__popc(peers));
+        pos = __shfl_sync(0xffffffffu, pos, leader);
+        if (bin < 256u) tile_order[pos + __popc(peers & ((1u << lane) - 1u))] = make_uint4((uint32_t)kk, r.x, r.y, 0u);
+    }
 }
 
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity,
@@ -161,9 +164,9 @@ void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapp
     const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
     tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
-                                              host_mapped_R, (unsigned long long)capacity, list_limit, call_flags);
-    tile_order_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.ranges, scratch, img.tile_order);
-    count_launch(2);
+                                              host_mapped_R, (unsigned long long)capacity, list_limit, call_flags,
+                                              img.tile_order);
+    count_launch();
 }
 
 // -------------------------------------------------------------------- scatter

@@ -103,12 +103,51 @@ __device__ __forceinline__ void cov2d_forward(float mx, float my, float mz, floa
     cyy = ffma(Tb2, B2, ffma(Tb0, B0, fmul(Tb1, B1)));
 }
 
+// The caller's [P,3] tensors (means3D, scales) are arrays of 12-byte structures: read thread-per-Gaussian they are
+// stride-12 scalar loads.  A block's 256 Gaussians are one contiguous 3072-byte run, so the block fetches it as 192
+// coalesced 16-byte vectors into shared memory and every thread picks its three floats from there (stride 3 words:
+// conflict-free); [P,4] rotations are one 16-byte load per thread.  Falls back to scalar loads when the run is not
+// 16-byte aligned or the block straddles two views.
+__device__ __forceinline__ void load_xyz_block(const float* __restrict__ base, size_t vs, int P, size_t gid0, int count,
+                                               float* smem, int tid, float& x, float& y, float& z, bool valid)
+{
+    const int v0 = (int)(gid0 / P), v1 = (int)((gid0 + count - 1) / P);
+    const float* __restrict__ src = base + (size_t)v0 * vs + 3 * (gid0 - (size_t)v0 * P);
+    const bool vec = v0 == v1 && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0u);   // block-uniform
+    if (vec) {
+        const int nf = count * 3, nv = nf >> 2;
+        if (tid < nv) reinterpret_cast<float4*>(smem)[tid] = __ldg(reinterpret_cast<const float4*>(src) + tid);
+        if (tid < nf - 4 * nv) smem[4 * nv + tid] = __ldg(src + 4 * nv + tid);
+        __syncthreads();
+        if (valid) { x = smem[3 * tid]; y = smem[3 * tid + 1]; z = smem[3 * tid + 2]; }
+    } else if (valid) {
+        const size_t gid = gid0 + tid;
+        const int v = (int)(gid / P);
+        const float* __restrict__ p = base + (size_t)v * vs + 3 * (gid - (size_t)v * P);
+        x = p[0]; y = p[1]; z = p[2];
+    }
+}
+
 __global__ void __launch_bounds__(256)
 preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restrict__ tile_count,
                           int* __restrict__ radii)
 {
-    const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (gid >= (size_t)in.V * in.P) return;
+    __shared__ __align__(16) float s_xyz[256 * 3];
+    __shared__ __align__(16) float s_scl[256 * 3];
+    const size_t n_total = (size_t)in.V * in.P;
+    const size_t gid0 = (size_t)blockIdx.x * 256;
+    const size_t gid = gid0 + threadIdx.x;
+    const int count = (int)min((size_t)256, n_total - gid0);
+    const bool valid = gid < n_total;
+    // Every input of a Gaussian is requested before the first early exit: the grid is a single wave, so
+    // each dependent round trip to HBM behind a branch (scale/rotation after the frustum test, opacity after
+    // the rect test) lengthened the whole kernel by one memory latency.  Culled Gaussians read 32 bytes in vain.
+    float mx = 0.0f, my = 0.0f, mz = 0.0f;
+    float sr[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+    load_xyz_block(in.means3D, in.means3D_vs, in.P, gid0, count, s_xyz, threadIdx.x, mx, my, mz, valid);
+    if (in.cov3D_precomp == nullptr)
+        load_xyz_block(in.scales, in.scales_vs, in.P, gid0, count, s_scl, threadIdx.x, sr[0], sr[1], sr[2], valid);
+    if (!valid) return;
     const int v = (int)(gid / in.P);
     const int i = (int)(gid - (size_t)v * in.P);
 
@@ -118,17 +157,14 @@ preprocess_forward_kernel(const Inputs in, const GeomPtrs g, uint32_t* __restric
 
     const float* __restrict__ Vm = in.viewmatrix + 16 * v;
     const float* __restrict__ Pm = in.projmatrix + 16 * v;
-    const float* __restrict__ mp = in.means3D + (size_t)v * in.means3D_vs + 3 * (size_t)i;
-    const float mx = mp[0], my = mp[1], mz = mp[2];
-    // Every input of this Gaussian is requested before the first early exit: the grid is a single wave, so
-    // each dependent round trip to HBM behind a branch (scale/rotation after the frustum test, opacity after
-    // the rect test) lengthened the whole kernel by one memory latency.  Culled Gaussians read 32 bytes in vain.
-    float sr[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
     if (in.cov3D_precomp == nullptr) {
-        const float* __restrict__ sp = in.scales + (size_t)v * in.scales_vs + 3 * (size_t)i;
         const float* __restrict__ qp = in.rotations + (size_t)v * in.rotations_vs + 4 * (size_t)i;
-        sr[0] = sp[0]; sr[1] = sp[1]; sr[2] = sp[2];
-        sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
+        if ((reinterpret_cast<uintptr_t>(qp) & 15u) == 0u) {   // [P,4]: one 16-byte load per Gaussian
+            const float4 q = __ldg(reinterpret_cast<const float4*>(qp));
+            sr[3] = q.x; sr[4] = q.y; sr[5] = q.z; sr[6] = q.w;
+        } else {
+            sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
+        }
     }
     const float opacity = in.opacities[(size_t)v * in.opacities_vs + i];
     float tan_fovx = in.tan_fovx, tan_fovy = in.tan_fovy;

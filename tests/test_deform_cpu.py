@@ -49,3 +49,26 @@ def test_face_frames_are_orthonormal_and_deform_is_rigid_per_face():
     assert torch.allclose(c, (a["uv_face_bary"][None, :, :, None] * fv).sum(2), atol=1e-6)
     # unit input quaternions stay unit
     assert torch.allclose(out["rotation"].norm(dim=-1), torch.ones(2, P), atol=1e-5)
+
+
+def _deform_golden():
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "deform", "deform_ref.npz"))
+    a = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("in_")}
+    return z, a
+
+
+def test_oracle_against_golden_from_the_reference_source():
+    """tests/golden/deform/deform_ref.npz holds what the REFERENCE'S OWN SOURCE produces (utils/graphics_utils.py:52-80 and
+    the body of Ubody_Gaussian.forward, ubody_gaussian.py:245-289, extracted with ast and executed by
+    tests/golden/make_deform_golden.py; roma's four helpers bound to the restatement).  The oracle's line-by-line
+    restatement must reproduce it."""
+    z, a = _deform_golden()
+    out = do.deform(**a)
+    for k in ("xyz", "rotation", "scaling", "opacity", "features_color"):
+        want = torch.from_numpy(z["out_" + k])
+        assert out[k].shape == want.shape
+        assert float((out[k] - want).abs().max()) <= 1e-6 * max(1.0, float(want.abs().max())), k
+    R, s = do.compute_face_orientation(a["vertices"], a["faces"])
+    assert float((R - torch.from_numpy(z["face_orientation"])).abs().max()) <= 1e-6
+    assert float((s - torch.from_numpy(z["face_scale"])).abs().max()) <= 1e-6

@@ -72,3 +72,20 @@ def test_deform_feeds_the_rasterizer_and_rejects_host_tensors():
     out = grb.render_views(assets, cams)
     out["rendered_images"].sum().backward()
     assert torch.isfinite(out["rendered_images"]).all() and gpu["uv_local_xyz"].grad is not None
+
+
+def test_deform_kernels_against_golden_from_the_reference_source():
+    """The CUDA path against tests/golden/deform/deform_ref.npz -- outputs of the reference's own source for this row
+    (see tests/golden/make_deform_golden.py; roma's helpers restated)."""
+    import os
+    import guava_renderer_b200 as grb
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "deform", "deform_ref.npz"))
+    a = {k[3:]: torch.from_numpy(z[k]).to("cuda:0") for k in z.files if k.startswith("in_")}
+    mesh = ("vertices", "ver_transform_mat", "faces", "uv_binding_face", "uv_face_bary")
+    out = grb.deform_gaussians(*[a[k] for k in mesh], **{k: a[k] for k in LEAVES})
+    torch.cuda.synchronize()
+    for k in KEYS:
+        o, r = out[k].detach().cpu(), torch.from_numpy(z["out_" + k])
+        if k == "rotation":   # q and -q are the same rotation
+            o = o * torch.sign((o * r).sum(-1, keepdim=True))
+        assert float((o - r).abs().max()) <= 1e-5 * max(1.0, float(r.abs().max())), k

@@ -428,7 +428,7 @@ def test_pack_view_gradients_and_graphed_step():
     for _ in range(2):
         step.replay()
     step.check()
-    assert step.launches_per_replay >= 9
+    assert step.launches_per_replay >= 8
     assert torch.equal(step.color, color.detach()) and torch.equal(step.radii, radii)
     assert util.rel_err(step.packed.cpu().numpy(), ref.cpu().numpy()) <= 1e-4
     assert abs(float(step.loss) - float((color.detach() * dL).sum())) <= 1e-3 * abs(float(step.loss)) + 1e-3

@@ -169,3 +169,17 @@ def test_collective_footprint_cap_keeps_an_explicit_setting(monkeypatch):
     monkeypatch.setenv("NCCL_MAX_CTAS", "16")
     sharding.limit_collective_footprint()
     assert os.environ["NCCL_MAX_CTAS"] == "16"
+
+
+def test_compiled_torch_binding_is_built_and_exports_the_reference_entry_points():
+    """lib/_guava_torch.so (csrc/torch_binding.cpp) is the default `_C`: the reference's three pybind functions
+    (DGR32/ext.cpp:15-18) plus the batched pair.  Loading needs no GPU; calling does."""
+    import guava_renderer_b200 as grb
+    from guava_renderer_b200 import rasterizer
+    assert os.path.isfile(rasterizer.TORCH_SO_PATH)
+    if rasterizer.BINDING == "compiled":
+        for name in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible",
+                     "rasterize_gaussians_batch", "rasterize_gaussians_batch_backward"):
+            assert callable(getattr(grb._C, name)), name
+    import diff_gaussian_rasterization_32 as dgr
+    assert dgr._C is grb._C
