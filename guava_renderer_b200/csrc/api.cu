@@ -32,7 +32,7 @@ static std::atomic<long long> g_opt_emit_sorted_keys{0};
 static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_tma_staging{0};   // compositors stage feature rows with cp.async.bulk.tensor gather4 (1) or LDGSTS (0)
-static std::atomic<long long> g_opt_block_masks{0};   // experimental, see BLOCK_MASK_SHIFT (internal.cuh)
+static std::atomic<long long> g_opt_taken_masks{0};   // see BLOCK_MASK_SHIFT (internal.cuh)
 static std::atomic<long long> g_opt_os_identify_ranges{0};   // sort mode 1: recompute the tile ranges from the sorted keys (identifyTileRanges restated) although the tile scan already wrote them
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 
@@ -360,7 +360,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     if (co != nullptr && co->struct_size != sizeof(guava_call_options))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "guava_call_options::struct_size does not match this library");
     in.aux_nhwc_bf16 = co ? co->refiner_output_nhwc_bf16 : nullptr;
-    const int block_masks = g_opt_block_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;
+    const int block_masks = g_opt_taken_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // ids must fit 24 bits
     uint32_t* const status_host = co ? (uint32_t*)co->status_words : nullptr;
     if (((uintptr_t)status_host & 7) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");
@@ -388,10 +388,11 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     const bool exact = g_opt_exact_binning.load() != 0;
     const bool async_fwd = co != nullptr && co->no_host_wait != 0 && !exact;
     // "sort_mode": 0 = tile buckets, 1 = global onesweep sort, -1 (default) = by the longest tile list the
-    // previous call of this shape produced: lists beyond the register-resident bucket sort (2048) are where
-    // the onesweep passes win (measured: profiles/r01_v9_sort_modes.jsonl).  Results are identical.
+    // previous call of this shape produced: lists beyond the register-resident bucket sorts (4096) are where
+    // the onesweep passes win (measured: profiles/r02_v2_sort_vs_cub.jsonl -- at P = 202 k, lists of 2-3 k, the
+    // buckets take 0.128 ms against 0.158 ms; at C5, lists of 3-8 k, 1.26 against 0.72).  Results are identical.
     int sort_mode = (int)g_opt_sort_mode.load();
-    if (sort_mode < 0) sort_mode = longest_estimate((size_t)in.V * in.P, in.W, in.H) > 2048u ? 1 : 0;
+    if (sort_mode < 0) sort_mode = longest_estimate((size_t)in.V * in.P, in.W, in.H) > 4096u ? 1 : 0;
     GUAVA_CUDA(ensure_slots());
 
     guava_layout L;
@@ -502,7 +503,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
             timer.begin(3);
             launch_onesweep_binning(in, g, im, (uint32_t*)(geom + L.point_offsets), (uint64_t*)(bin + L.keys_sorted),
                                     b.point_list, b.keys_unsorted, (uint32_t*)(bin + L.os_vals_alt),
-                                    (uint32_t*)(bin + L.os_scratch), cap, g_opt_os_identify_ranges.load() != 0, block_masks, stream);
+                                    (uint32_t*)(bin + L.os_scratch), cap, g_opt_os_identify_ranges.load() != 0, stream);
             timer.end();
             GUAVA_STAGE("onesweep", debug);
         } else {
@@ -511,7 +512,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         timer.end();
         GUAVA_STAGE("scatter", debug);
         timer.begin(3);
-        launch_tile_sort(in, g, im, b, with_large, block_masks, stream);
+        launch_tile_sort(in, g, im, b, with_large, stream);
         timer.end();
         GUAVA_STAGE("tile_sort", debug);
         }
@@ -550,7 +551,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
                          float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream)
 {
     if ((size_t)in.V * in.P == 0) return GUAVA_OK;
-    const int block_masks = g_opt_block_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // as in the forward call
+    const int block_masks = g_opt_taken_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // as in the forward call
     if (!geom || !bin || !img || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
         !dL_dmean3D || !dL_dcov3D || !radii)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
@@ -818,7 +819,7 @@ static std::atomic<long long>* find_option(const char* name)
     if (!strcmp(name, "profile_stages")) return &g_opt_profile_stages;
     if (!strcmp(name, "tma_staging")) return &g_opt_tma_staging;
     if (!strcmp(name, "sort_mode")) return &g_opt_sort_mode;
-    if (!strcmp(name, "block_masks")) return &g_opt_block_masks;
+    if (!strcmp(name, "taken_masks")) return &g_opt_taken_masks;
     if (!strcmp(name, "os_identify_ranges")) return &g_opt_os_identify_ranges;
     return nullptr;
 }

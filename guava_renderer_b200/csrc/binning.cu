@@ -284,13 +284,12 @@ __device__ __forceinline__ uint32_t next_pow2(uint32_t n)
 // is register-to-register for j < E, a warp shuffle for j < 32*E, and goes through shared memory
 // (transposed layout, conflict-free) only for the few steps with j >= 32*E -- 6 of 55 steps at
 // N = 1024 -- where the first version synchronised the block after every step.
-template <int E, int MASKS>
+template <int E, int T = 256>
 __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__ src, uint32_t n, uint64_t* skeys,
                                                     uint32_t* __restrict__ point_list, uint64_t* __restrict__ keys_sorted,
-                                                    uint64_t tile_hi, int tid,
-                                                    const SplatRec* __restrict__ mask_recs, float tx0, float ty0)
+                                                    uint64_t tile_hi, int tid)
 {
-    constexpr int N = 256 * E;
+    constexpr int N = T * E;
     uint64_t key[E];
 #pragma unroll
     for (int e = 0; e < E; e++) {
@@ -329,11 +328,11 @@ __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__
                 const bool keep_max = ((tid & tj) == 0) != (((tid * E) & k) == 0);
                 __syncthreads();
 #pragma unroll
-                for (int e = 0; e < E; e++) skeys[e * 256 + tid] = key[e];
+                for (int e = 0; e < E; e++) skeys[e * T + tid] = key[e];
                 __syncthreads();
 #pragma unroll
                 for (int e = 0; e < E; e++) {
-                    const uint64_t other = skeys[e * 256 + (tid ^ tj)];
+                    const uint64_t other = skeys[e * T + (tid ^ tj)];
                     const bool take_other = (other < key[e]) != keep_max;
                     key[e] = take_other ? other : key[e];
                 }
@@ -344,25 +343,21 @@ __device__ __forceinline__ void tile_sort_registers(const uint64_t* __restrict__
     for (int e = 0; e < E; e++) {
         const uint32_t i = (uint32_t)(tid * E + e);
         if (i < n) {
-            uint32_t id = (uint32_t)key[e];
-            if (MASKS) id |= untouched_blocks(mask_recs, id, tx0, ty0);
-            point_list[i] = id;
+            point_list[i] = (uint32_t)key[e];
             if (keys_sorted != nullptr) keys_sorted[i] = tile_hi | (key[e] >> 32);
         }
     }
 }
 
-template <int MASKS>
 __global__ void __launch_bounds__(256)
 tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __restrict__ num_rendered,
                        const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                       uint64_t* __restrict__ keys_sorted, int tiles_per_view,
-                       const SplatRec* __restrict__ mask_recs, int P, int gx)
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view)
 {
     __shared__ uint64_t skeys[2048];
     if (num_rendered[1]) return;
     // blocks take the tiles longest list first (the compositors' work order): all non-empty buckets are
-    // resident in one wave at the GUAVA shapes, and this deals the 2048-key sorts evenly over the SMs
+    // resident in one wave at the GUAVA shapes, and this deals the long sorts evenly over the SMs
     // instead of leaving them clustered where the image centre falls in row-major tile order
     const uint4 item = tile_order[blockIdx.x];
     const uint2 r = make_uint2(item.y, item.z);
@@ -371,19 +366,10 @@ tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __r
     const int tid = threadIdx.x;
     const uint64_t tile_hi = (uint64_t)(item.x % (uint32_t)tiles_per_view) << 32;
     uint64_t* ks = keys_sorted != nullptr ? keys_sorted + r.x : nullptr;
-    // block masks (option): records of this tile's view, pixel origin of the tile
-    const SplatRec* mr = nullptr;
-    float tx0 = 0.0f, ty0 = 0.0f;
-    if (MASKS) {
-        const uint32_t view = item.x / (uint32_t)tiles_per_view, tile = item.x % (uint32_t)tiles_per_view;
-        mr = mask_recs + (size_t)view * P;
-        tx0 = (float)((tile % (uint32_t)gx) * TILE_X);
-        ty0 = (float)((tile / (uint32_t)gx) * TILE_Y);
-    }
-    if (n <= 256) tile_sort_registers<1, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
-    else if (n <= 512) tile_sort_registers<2, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
-    else if (n <= 1024) tile_sort_registers<4, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
-    else tile_sort_registers<8, MASKS>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid, mr, tx0, ty0);
+    if (n <= 256) tile_sort_registers<1>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else if (n <= 512) tile_sort_registers<2>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else if (n <= 1024) tile_sort_registers<4>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
+    else tile_sort_registers<8>(keys + r.x, n, skeys, point_list + r.x, ks, tile_hi, tid);
 }
 
 // Buckets longer than SORT_SMALL are rare (none at the GUAVA shapes): one persistent
@@ -391,14 +377,13 @@ tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __r
 // memory up to SORT_LARGE keys, beyond that with the same network in place in global
 // memory (L2-resident).  When there is nothing to do the launch costs a few microseconds.
 static constexpr uint32_t SORT_SMALL = 2048;    // 16 KB of keys, 256 threads
+static constexpr uint32_t SORT_MID = 4096;      // 1024 threads x 4 keys in registers (the real GUAVA training size, P = 202 k, has lists of 2-3 k)
 static constexpr uint32_t SORT_LARGE = 16384;   // 128 KB of keys, 1024 threads
 
-template <int MASKS>
 __global__ void __launch_bounds__(1024)
 tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ num_rendered,
                        uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                       uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles,
-                       const SplatRec* __restrict__ mask_recs, int P, int gx)
+                       uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
 {
     extern __shared__ uint64_t skeys[];
     if (num_rendered[1] || num_rendered[4] <= SORT_SMALL) return;
@@ -408,22 +393,17 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
         const uint32_t n = r.y - r.x;
         if (n <= SORT_SMALL) continue;   // block-uniform
         const uint64_t tile_hi = (uint64_t)(tile % tiles_per_view) << 32;
-        const SplatRec* mr = nullptr;
-        float tx0 = 0.0f, ty0 = 0.0f;
-        if (MASKS) {
-            const uint32_t view = (uint32_t)tile / (uint32_t)tiles_per_view, t = (uint32_t)tile % (uint32_t)tiles_per_view;
-            mr = mask_recs + (size_t)view * P;
-            tx0 = (float)((t % (uint32_t)gx) * TILE_X);
-            ty0 = (float)((t / (uint32_t)gx) * TILE_Y);
-        }
-        if (n <= SORT_LARGE) {
+        if (n <= SORT_MID) {
+            // same register-resident network as the small buckets, 1024 threads x 4 keys: 15 of its 78 steps go through
+            // shared memory, where the network below synchronises the block after every step
+            tile_sort_registers<4, 1024>(keys + r.x, n, skeys, point_list + r.x, keys_sorted != nullptr ? keys_sorted + r.x : nullptr,
+                                         tile_hi, tid);
+        } else if (n <= SORT_LARGE) {
             for (uint32_t k = tid; k < n; k += 1024) skeys[k] = keys[r.x + k];
             bitonic_sort_ascending(skeys, n, next_pow2(n), tid, 1024);
             for (uint32_t k = tid; k < n; k += 1024) {
                 const uint64_t key = skeys[k];
-                uint32_t id = (uint32_t)key;
-                if (MASKS) id |= untouched_blocks(mr, id, tx0, ty0);
-                point_list[r.x + k] = id;
+                point_list[r.x + k] = (uint32_t)key;
                 if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
             }
         } else {
@@ -431,9 +411,7 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
             bitonic_sort_ascending(seg, n, next_pow2(n), tid, 1024);
             for (uint32_t k = tid; k < n; k += 1024) {
                 const uint64_t key = seg[k];
-                uint32_t id = (uint32_t)key;
-                if (MASKS) id |= untouched_blocks(mr, id, tx0, ty0);
-                point_list[r.x + k] = id;
+                point_list[r.x + k] = (uint32_t)key;
                 if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
             }
         }
@@ -444,7 +422,7 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
 uint32_t tile_sort_small_limit() { return SORT_SMALL; }
 
 void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b, bool with_large,
-                      int block_masks, cudaStream_t s)
+                      cudaStream_t s)
 {
     const int total_tiles = in.V * in.tiles;
     if (total_tiles == 0) return;
@@ -453,27 +431,17 @@ void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img,
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
-        cudaFuncSetAttribute(tile_sort_large_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(SORT_LARGE * sizeof(uint64_t)));
-        cudaFuncSetAttribute(tile_sort_large_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)(SORT_LARGE * sizeof(uint64_t)));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
-    if (block_masks)
-        tile_sort_small_kernel<1><<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted,
-                                                              b.point_list, b.keys_sorted, in.tiles, g.rec, in.P, in.gx);
-    else
-        tile_sort_small_kernel<0><<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted,
-                                                              b.point_list, b.keys_sorted, in.tiles, nullptr, 0, 0);
+    tile_sort_small_kernel<<<total_tiles, 256, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted, b.point_list,
+                                                       b.keys_sorted, in.tiles);
     count_launch();
     if (!with_large) return;
     const int big_grid = total_tiles < sm_count() ? total_tiles : sm_count();
-    if (block_masks)
-        tile_sort_large_kernel<1><<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
-            img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles, g.rec, in.P, in.gx);
-    else
-        tile_sort_large_kernel<0><<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
-            img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles, nullptr, 0, 0);
+    tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
+        img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
     count_launch();
 }
 

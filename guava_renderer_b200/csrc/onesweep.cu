@@ -376,24 +376,6 @@ identify_tile_ranges_kernel(const uint64_t* __restrict__ keys, const uint32_t* _
     }
 }
 
-// Option "block_masks" in sort mode 1: one pass over the sorted pairs that ORs, into bits 24..31 of every point_list
-// entry, the tile's 8x4 pixel blocks the splat cannot touch (untouched_blocks, internal.cuh) -- what the bucket path
-// does in the epilogue of its tile sorts.
-__global__ void __launch_bounds__(256)
-block_mask_kernel(const uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, const uint32_t* __restrict__ num_rendered,
-                  const SplatRec* __restrict__ recs, int P, int tiles_per_view, int gx)
-{
-    if (num_rendered[1]) return;
-    const uint32_t R = num_rendered[0];
-    for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < R; i += gridDim.x * 256u) {
-        const uint32_t gtile = (uint32_t)(keys[i] >> 32);
-        const uint32_t view = gtile / (uint32_t)tiles_per_view, t = gtile % (uint32_t)tiles_per_view;
-        const uint32_t id = vals[i];
-        vals[i] = id | untouched_blocks(recs + (size_t)view * P, id, (float)((t % (uint32_t)gx) * TILE_X),
-                                        (float)((t / (uint32_t)gx) * TILE_Y));
-    }
-}
-
 int onesweep_passes(int total_tiles, int* total_bits)
 {
     int bit = 0;
@@ -458,7 +440,7 @@ static void launch_pass(const OsBuffers& bufs, const ImagePtrs& img, uint32_t* t
 // kernel below remains as the like-for-like restatement and runs only with option "os_identify_ranges".
 void launch_onesweep_binning(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, uint32_t* point_offsets,
                              uint64_t* keys0, uint32_t* vals0, uint64_t* keys1, uint32_t* vals1, uint32_t* scratch,
-                             size_t capacity, int identify_ranges, int block_masks, cudaStream_t s)
+                             size_t capacity, int identify_ranges, cudaStream_t s)
 {
     const size_t n = (size_t)in.V * in.P;
     const int total_tiles = in.V * in.tiles;
@@ -498,10 +480,6 @@ void launch_onesweep_binning(const Inputs& in, const GeomPtrs& g, const ImagePtr
     if (identify_ranges) {
         cudaMemsetAsync(img.ranges, 0, (size_t)total_tiles * sizeof(uint2), s);
         identify_tile_ranges_kernel<<<sm_count() * 4, 256, 0, s>>>(keys0, img.num_rendered, img.ranges);
-        count_launch();
-    }
-    if (block_masks) {
-        block_mask_kernel<<<sm_count() * 8, 256, 0, s>>>(keys0, vals0, img.num_rendered, g.rec, in.P, in.tiles, in.gx);
         count_launch();
     }
 }

@@ -78,9 +78,12 @@ __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&
 // Gradients leave the SM as 4-byte reductions: one 128-byte request from all 32 lanes per (warp, Gaussian) for
 // dL_dcolors plus 28 lanes for the packed record.  (16-byte vector reductions, red.global.add.v4.f32 from 8 lanes,
 // cost three gathering shuffles per splat on the data pipe and measured 2 % slower, profiles/r01_v43; removed.)
-// MASKS = 1 (option "block_masks"): see render_forward.cu -- the list entries carry the forward's block masks, no
-// footprint test is run here.  TMA = 1 (option "tma_staging"): feature rows staged by cp.async.bulk.tensor gather4.
-template <int MASKS, int TMA>
+// MASKS = 1 (option "taken_masks"): see render_forward.cu -- the forward has marked, per block, the list entries it got
+// nothing from; they are skipped here without a footprint test, record gather or staging.
+// TMA = 1 (option "tma_staging"): feature rows staged by cp.async.bulk.tensor gather4.
+// INV = 0: no upstream gradient for the inverse depth (GUAVA's losses never read the depth output,
+// utils/loss_utils.py:89-138): the per-splat 1/depth operand, its term of the dot product and the seventh moment drop out.
+template <int MASKS, int TMA, int INV>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
@@ -160,7 +163,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
             bgdot = fmaf(bg[2 * ch], g[ch].x, bgdot);
             bgdot = fmaf(bg[2 * ch + 1], g[ch].y, bgdot);
         }
-        if (dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
+        if (INV && dL_dinvdepth_pix != nullptr && inside) g_inv = dL_dinvdepth_pix[(size_t)v * HW + pix];
     }
     // ... and channel `lane` of all 32 pixels (column), through an XOR-swizzled 32x32 tile
     // in the not-yet-used staging memory (conflict-free both ways).
@@ -218,7 +221,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 q = &st.xy[0].x + o;   q[0] = c0.x; q[2] = c0.y;
                 q = &st.cab[0].x + o;  q[0] = c0.z; q[2] = -c0.w;
                 q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
-                (&st.rd[0].x)[slot] = c1.z;
+                if (INV) (&st.rd[0].x)[slot] = c1.z;
                 if (TMA) {
                     srows[c & 1][slot] = vrow0 + id;
                 } else {
@@ -300,7 +303,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 // both alpha chains as packed f32x2 instructions: per half the very operations, in the very order, of
                 // the forward kernel's eval_pair (bit-identical alpha); the second half is stale data if !has1
                 const float4 pa = stg.xy[kp], pb = stg.cab[kp], pc = stg.cop[kp];
-                const float2 rdp = stg.rd[kp];
+                const float2 rdp = INV ? stg.rd[kp] : make_float2(0.0f, 0.0f);
                 const float2 dxp = __fadd2_rn(f2(pa.x, pa.y), f2(-pxf));
                 const float2 dyp = __fadd2_rn(f2(pa.z, pa.w), f2(-pyf));
                 const float2 qd = __ffma2_rn(dxp, __fmul2_rn(dxp, f2(pb.x, pb.y)), __fmul2_rn(dyp, __fmul2_rn(dyp, f2(pc.x, pc.y))));
@@ -330,8 +333,8 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                     dd = __ffma2_rn(make_float2(h.z, h.w), g[2 * q + 1], dd);
                 }
                 const float2 ds0 = __fadd2_rn(da, db), ds1 = __fadd2_rn(dc, dd);
-                const float d0 = fmaf(rdepth0, g_inv, ds0.x + ds0.y);
-                const float d1 = fmaf(rdepth1, g_inv, ds1.x + ds1.y);
+                const float d0 = INV ? fmaf(rdepth0, g_inv, ds0.x + ds0.y) : ds0.x + ds0.y;
+                const float d1 = INV ? fmaf(rdepth1, g_inv, ds1.x + ds1.y) : ds1.x + ds1.y;
 
                 // Per-pixel partials: the blending weight w and moments of s = dL/dG * G about the
                 // pixel offset d (the conic / mean2D / opacity gradients are linear in them;
@@ -366,7 +369,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const float2 s2 = __fmul2_rn(f2(pc.z, pc.w), f2(mo0, mo1));
                 const float2 sx2 = __fmul2_rn(s2, dxp), sy2 = __fmul2_rn(s2, dyp);   // s*dx, s*dy
                 const float2 sxx2 = __fmul2_rn(sx2, dxp), sxy2 = __fmul2_rn(sx2, dyp), syy2 = __fmul2_rn(sy2, dyp);
-                const float2 wg2 = __fmul2_rn(f2(w0, w1), f2(g_inv));
+                const float2 wg2 = INV ? __fmul2_rn(f2(w0, w1), f2(g_inv)) : make_float2(0.0f, 0.0f);
                 float* exb0 = exbase + (parity & 3u) * 32;
                 float* exb1 = exbase + ((parity + 1u) & 3u) * 32;
                 parity += 2u;
@@ -401,7 +404,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
                 const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
-                const bool geo_lane = lane < 28;   // lanes 4k..4k+3: partials of moment k (moment 7 is unused)
+                const bool geo_lane = lane < (INV ? 28 : 24);   // lanes 4k..4k+3: partials of moment k (7 is unused, 6 = invdepth)
                 if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
                 if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
                 if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
@@ -421,7 +424,7 @@ bool make_feature_tensor_map(const Inputs& in, CUtensorMap* out);   // render_fo
 
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
                             const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor,
-                            int block_masks, int tma_staging, cudaStream_t s)
+                            int taken_masks, int tma_staging, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     CUtensorMap fmap;
@@ -432,13 +435,15 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
-#define GUAVA_LAUNCH_BWD(MK, TM)                                                                                          \
-    render_backward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,          \
-                                                       img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor,   \
-                                                       g.grad_geo, img.num_rendered)
-    if (block_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
+#define GUAVA_LAUNCH_BWD2(MK, TM, IV)                                                                                     \
+    render_backward_kernel<MK, TM, IV><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,      \
+                                                           img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix,         \
+                                                           dL_dcolor, g.grad_geo, img.num_rendered)
+#define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1); else GUAVA_LAUNCH_BWD2(MK, TM, 0); } while (0)
+    if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_BWD(0, 1); else GUAVA_LAUNCH_BWD(0, 0); }
 #undef GUAVA_LAUNCH_BWD
+#undef GUAVA_LAUNCH_BWD2
     cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();
 }

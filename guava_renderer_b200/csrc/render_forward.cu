@@ -46,8 +46,10 @@ struct __align__(128) FwdStage {
     float4 dpos[16];                // rdepth0 rdepth1 list-position0 list-position1 (positions as bits, 1-based)
 };
 
-// MASKS = 1 (option "block_masks"): the tile sort has marked, in bits 24..31 of every list entry, the blocks the
-// splat cannot touch; the footprint test is that bit, and records are gathered for survivors only.
+// MASKS = 1 (option "taken_masks"): every list entry this block got nothing from -- rejected by the footprint test, or
+// a survivor that no pixel took -- is marked in bit 24 + sub of its point_list word (one coalesced RED.OR per 32-entry
+// chunk), for the backward compositor to skip; the ids this kernel reads are masked to their low 24 bits because the
+// other seven blocks of the tile are marking the same words.
 // TMA = 1 (option "tma_staging"): the survivors' 128-byte feature rows are fetched by the TMA unit -- one elected
 // lane issues cp.async.bulk.tensor...tile::gather4 over a [rows, 32] tensor map of colors_precomp, four survivor rows
 // per instruction, completion on a per-stage mbarrier -- instead of eight 16-byte LDGSTS per survivor lane.
@@ -55,7 +57,7 @@ template <int MASKS, int TMA>
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
-                      const uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
+                      uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
@@ -121,28 +123,30 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     // rows are requested at the top of the next iteration.
     auto load_id = [&](int c) -> uint32_t {
         const int k = (c << 5) + lane;
-        return k < len ? point_list[range.x + k] : NO_ID;
+        return k < len ? (MASKS ? (point_list[range.x + k] & BLOCK_MASK_ID) : point_list[range.x + k]) : NO_ID;
     };
     // Unconditional (lanes past the end of the list re-read record 0 and are masked by `keep`): a predicated
     // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
     // those moves stalled the warp for the whole L2 round trip right after the load was issued
     // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
-    // (MASKS: `id` is the raw list entry; entries of other blocks re-read record 0 like the lanes past the end)
-    auto is_kept = [&](uint32_t id) -> bool { return id != NO_ID && ((id >> (BLOCK_MASK_SHIFT + sub)) & 1u) == 0u; };
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? id : 0u);
+        const uint32_t r = id != NO_ID ? id : 0u;
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + r);
         c0 = rp[0];
         c1 = rp[1];
     };
     // Test chunk c (one list entry per lane) and stage the survivors into stage[c & 1].
     // Returns the survivor mask (bit = lane = list offset within the chunk).
+    // MASKS: bit = lane of the entries of the chunk being blended / being staged that this block gets nothing from
+    uint32_t marks_cur = 0u, marks_next = 0u;
+    auto flush_marks = [&](int c, uint32_t marks) {   // one RED.OR over the chunk's 32 consecutive words
+        if (MASKS && ((marks >> lane) & 1u)) atomicOr(&point_list[range.x + (uint32_t)(c << 5) + (uint32_t)lane], 1u << (BLOCK_MASK_SHIFT + sub));
+    };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
-        const bool keep = MASKS ? is_kept(id)
-                                : (id != NO_ID &&
-                                   splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
-        if (MASKS) id &= BLOCK_MASK_ID;
+        const bool keep = id != NO_ID &&
+                          splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f);
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
+        if (MASKS) marks_next = __ballot_sync(0xffffffffu, id != NO_ID) & ~mask;   // rejected by the footprint test
         if (mask != 0u) {
             FwdStage& st = stage[c & 1];
             if (keep) {
@@ -211,11 +215,13 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     uint32_t id_nn = load_id(1);
     load_rec(id_next, a0, a1);
     uint32_t mask_cur = stage_chunk(0, id_next, a0, a1);
+    marks_cur = marks_next;
     id_next = id_nn;
     load_rec(id_next, a0, a1);
     id_nn = load_id(2);
     for (int c = 0; c < nchunks; c++) {
         uint32_t mask_next = 0u;
+        marks_next = 0u;
         if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
         else if (!TMA) tma::cp_async_commit();
         id_next = id_nn;
@@ -267,7 +273,13 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
                 if (take1 && test_T1 < 0.0001f) { done = true; take1 = false; }
                 const float w1 = take1 ? fmul(alpha1, T) : 0.0f;
                 if (take1) { T = test_T1; last_contributor = __float_as_uint(pd.w); }
-                if (__any_sync(0xffffffffu, take0)) {
+                const bool any0 = __any_sync(0xffffffffu, take0);
+                const bool any1 = __any_sync(0xffffffffu, take1);
+                if (MASKS) {   // a survivor no pixel of the block takes contributes nothing in the backward either
+                    if (!any0) marks_cur |= 1u << ((__float_as_uint(pd.z) - 1u) & 31u);
+                    if (has1 && !any1) marks_cur |= 1u << ((__float_as_uint(pd.w) - 1u) & 31u);
+                }
+                if (any0) {
                     const float2 w2 = make_float2(w0, w0);
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
@@ -277,7 +289,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
                     }
                     D = fmaf(w0, pd.x, D);
                 }
-                if (__any_sync(0xffffffffu, take1)) {
+                if (any1) {
                     const float2 w2 = make_float2(w1, w1);
 #pragma unroll
                     for (int q = 0; q < NUM_CHANNELS / 4; q++) {
@@ -290,6 +302,8 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
                 if (__all_sync(0xffffffffu, done)) warp_done = true;
             }
         }
+        flush_marks(c, marks_cur);
+        marks_cur = marks_next;
         if (warp_done) {   // never leave the block with a copy still in flight
             if (TMA) { if (mask_next != 0u) wait_rows(s ^ 1); }
             else tma::cp_async_wait<0>();
@@ -404,7 +418,7 @@ bool make_feature_tensor_map(const Inputs& in, CUtensorMap* out)
 }
 
 void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
-                           float* out_color, float* out_invdepth, int block_masks, int tma_staging, cudaStream_t s)
+                           float* out_color, float* out_invdepth, int taken_masks, int tma_staging, cudaStream_t s)
 {
     if (in.tiles == 0 || in.V == 0) return;
     CUtensorMap fmap;
@@ -417,7 +431,7 @@ void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs&
 #define GUAVA_LAUNCH_FWD(MK, TM)                                                                                        \
     render_forward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,             \
                                                       img.num_rendered, img.final_T, img.n_contrib, out_color, out_invdepth)
-    if (block_masks) { if (tma_staging) GUAVA_LAUNCH_FWD(1, 1); else GUAVA_LAUNCH_FWD(1, 0); }
+    if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_FWD(1, 1); else GUAVA_LAUNCH_FWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_FWD(0, 1); else GUAVA_LAUNCH_FWD(0, 0); }
 #undef GUAVA_LAUNCH_FWD
     count_launch();

@@ -298,7 +298,8 @@ int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int widt
  * "sort_mode" (0: per-tile buckets sorted in shared memory; 1: the reference's chain rebuilt --
  * chained scan + duplicateWithKeys + onesweep LSD radix sort of the 64-bit tile|depth keys +
  * identifyTileRanges, rasterizer_impl.cu:280-320; identical keys, values and ranges; -1 (default): 1 when
- * the previous call of the same shape produced a tile list longer than 2048 instances, else 0;
+ * the previous call of the same shape produced a tile list longer than 4096 instances, else 0 -- the one place
+ * where a call's kernel path depends on an earlier call; the results do not;
  * guava_buffer_layout reports the mode-0 layout for -1, whose offsets are valid in both modes),
  * "tma_staging" (0/1: the compositors fetch the survivors' 128-byte feature rows with TMA tensor copies --
  * cp.async.bulk.tensor.2d ... tile::gather4 over a [rows,32] tensor map of colors_precomp, four rows per
@@ -306,10 +307,10 @@ int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int widt
  * same results; needs colors_view_stride % 32 == 0),
  * "os_identify_ranges" (0/1, default 0: sort mode 1 re-derives the tile ranges from the sorted keys --
  * identifyTileRanges, rasterizer_impl.cu:116-138, restated -- although the tile scan has already written them),
- * "block_masks" (0/1, default 0; EXPERIMENTAL, compiled but not yet run on hardware: the tile sort evaluates the
- * compositors' footprint test once per list entry and stores the blocks a splat cannot touch in bits 24..31 of the
- * point_list entries, which then are not plain indices; P < 2^24; must not change between a forward call and its
- * backward call).
+ * "taken_masks" (0/1: the forward compositor marks, in bit 24 + b of a point_list entry, that 8x4 pixel block b of
+ * the tile got nothing from that entry -- rejected by the footprint test or taken by no pixel -- and the backward
+ * compositor walks only the unmarked entries; point_list entries then are not plain indices (index = low 24 bits);
+ * P < 2^24; must not change between a forward call and its backward call).
  * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);

@@ -168,12 +168,12 @@ def test_backward_vs_reference_build(ref, case, with_invdepth):
         util.grad_gate(k, go[k], gr[k])       # per element: |a-b| <= 1e-4 |b| + 1e-6 max|b|
 
 
-@pytest.mark.parametrize("opts", [dict(block_masks=1), dict(tma_staging=1), dict(block_masks=1, tma_staging=1)],
-                         ids=["block_masks", "tma_staging", "block_masks+tma_staging"])
+@pytest.mark.parametrize("opts", [dict(taken_masks=1), dict(tma_staging=1), dict(taken_masks=1, tma_staging=1)],
+                         ids=["taken_masks", "tma_staging", "taken_masks+tma_staging"])
 @pytest.mark.parametrize("case", GRAD_CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
 def test_compositor_options_give_the_same_results(case, opts, sort_mode):
-    """Options of the compositors that must not change a result.  block_masks: the footprint test is evaluated once
-    per list entry by the binning stage and carried in bits 24..31 of point_list (same survivors).  tma_staging: the
+    """Options of the compositors that must not change a result.  taken_masks: the forward marks, in bits 24..31 of
+    point_list, the entries each 8x4 block got nothing from, and the backward skips them.  tma_staging: the
     survivors' feature rows are staged by cp.async.bulk.tensor gather4 instead of LDGSTS (same bytes).  Image
     bit-identical, gradients equal to reduction order, in both binning modes."""
     inp = util.inputs_for(**case)
@@ -198,10 +198,10 @@ def test_compositor_options_give_the_same_results(case, opts, sort_mode):
     for k in ("point_list", "keys", "ranges", "n_contrib", "radii", "color", "invdepth"):
         assert np.array_equal(o0[k], o1[k]), k
     assert np.array_equal(_bits(o0["final_T"]), _bits(o1["final_T"]))
-    if opts.get("block_masks"):
+    if opts.get("taken_masks"):
         assert o1["block_masks"] == 1 and o1["point_list_masks"].any()
-    for k in g0:
-        assert util.rel_err(g1[k], g0[k]) <= 1e-5, (k, util.rel_err(g1[k], g0[k]))
+    for k in g0:     # two runs differ by the order of their floating-point reductions
+        assert util.rel_err(g1[k], g0[k]) <= 5e-5, (k, util.rel_err(g1[k], g0[k]))
 
 
 @pytest.mark.parametrize("antialiasing", [False, True])
@@ -770,7 +770,7 @@ def test_footprint_culling_is_output_neutral_on_the_device():
     mean = org + torch.tensor([3.5, 1.5]) + off
     splats = torch.stack([mean[:, 0], mean[:, 1], a, b, cc, op], 1).contiguous()
     splats[:1000, 2] = 0.0                      # degenerate / not positive definite: must be kept
-    splats[1000:2000, 3] = splats[1000:2000, 2] * 4
+    splats[1000:2000, 3] = 4.0 * torch.sqrt(splats[1000:2000, 2] * splats[1000:2000, 4])   # B^2 = 16 A C: indefinite
     splats[2000:3000, 4] = float("nan")
     sp, og = splats.to(DEV), org.contiguous().to(DEV)
     rej = torch.zeros(n, dtype=torch.uint8, device=DEV)

@@ -1,7 +1,7 @@
 # One GPU-box session: full GPU test suite, A/B of the compositor options, both bench arms, other workloads,
-# sort micro-benchmark.  Outputs under gpurun_out/$TAG.
+# sort micro-benchmark, then the profiler passes on the default configuration.  Outputs under gpurun_out/$TAG.
 set -x
-TAG=${TAG:-r02_v2}
+TAG=${TAG:-r02_v3}
 O=gpurun_out/$TAG; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm --format=csv > $O/gpu.txt
 rm -f gpurun_out/grad_parity_stats.jsonl
@@ -9,17 +9,24 @@ timeout 1500 python -m pytest tests -m gpu -q > $O/pytest_gpu.log 2>&1
 cp gpurun_out/grad_parity_stats.jsonl $O/ 2>/dev/null
 B="timeout 200 python bench.py --steps 100 --warmup 10 --no-cpu-baseline"
 $B > $O/bench_base.json 2> $O/bench_base.err
-GUAVA_OPT_BLOCK_MASKS=1 $B > $O/bench_masks.json 2> $O/bench_masks.err
-GUAVA_OPT_TMA_STAGING=1 $B > $O/bench_tma.json 2> $O/bench_tma.err
-GUAVA_OPT_BLOCK_MASKS=1 GUAVA_OPT_TMA_STAGING=1 $B > $O/bench_masks_tma.json 2> $O/bench_masks_tma.err
-$B --eager > $O/bench_eager.json 2> $O/bench_eager.err
+GUAVA_OPT_TAKEN_MASKS=1 $B > $O/bench_taken.json 2> $O/bench_taken.err
+$B > $O/bench_base2.json 2> $O/bench_base2.err
+GUAVA_OPT_TAKEN_MASKS=1 $B > $O/bench_taken2.json 2> $O/bench_taken2.err
+$B --P 202000 > $O/bench_202k.json 2> $O/bench_202k.err
+GUAVA_OPT_TAKEN_MASKS=1 $B --P 202000 > $O/bench_202k_taken.json 2> $O/bench_202k_taken.err
+GUAVA_OPT_SORT_MODE=1 $B --P 202000 > $O/bench_202k_onesweep.json 2> $O/bench_202k_onesweep.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > $O/bench_ref.json 2> $O/bench_ref.err
+timeout 300 python bench.py --impl reference --steps 20 --warmup 5 --P 202000 --no-cpu-baseline > $O/bench_ref_202k.json 2> $O/bench_ref_202k.err
 timeout 200 python bench.py --steps 20 --warmup 5 > $O/bench_own_driverlike.json 2> $O/bench_own_driverlike.err
-for part in 2048 4096 6144; do GUAVA_OS_PART=$part $B --P 202000 > $O/bench_202k_part$part.json 2> $O/bench_202k_part$part.err; done
-timeout 200 python bench.py --workload C2 --steps 20 --warmup 5 --no-cpu-baseline > $O/bench_c2.json 2> $O/bench_c2.err
-timeout 300 python bench.py --workload C4 --steps 3 --warmup 3 --no-cpu-baseline > $O/bench_c4.json 2> $O/bench_c4.err
-timeout 300 python bench.py --workload C4 --impl reference --steps 3 --warmup 3 > $O/bench_c4_ref.json 2> $O/bench_c4_ref.err
 timeout 300 python tools/sort_vs_cub.py > $O/sort_vs_cub.jsonl 2> $O/sort_vs_cub.err
-tail -40 $O/pytest_gpu.log
-for f in $O/bench_*.json; do echo $f; head -c 300 $f; echo; done
-tail -2 $O/*.err
+timeout 300 python tools/bench_configs.py > $O/configs.jsonl 2> $O/configs.err
+tail -15 $O/pytest_gpu.log
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline"
+$CMD > $O/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1
+echo "ncu launches exit $?"
+$CMD > $O/plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on \
+    -k regex:"render_|preprocess_|tile_|scatter_|pack_|image_dot" -s 30 -c 20 -f -o $O/prof $CMD > $O/ncu_full.log 2>&1
+echo "ncu full exit $?"
+ls -la $O

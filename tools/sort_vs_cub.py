@@ -112,7 +112,8 @@ def main():
         same_vals = bool(np.array_equal(vals_out.cpu().numpy().view(np.uint32), dec["point_list"]))
         same_depth = bool(np.array_equal(ko & np.uint64(0xFFFFFFFF), ours_k & np.uint64(0xFFFFFFFF)))
         same_tile = bool(np.array_equal(ko >> np.uint64(32), ours_k >> np.uint64(32)))
-        row.update(R=R, sorted_bits=32 + bit, cub_sort_pairs_ms=round(ms, 4), cub_inclusive_sum_ms=round(ms_scan, 4),
+        rg = dec["ranges"].astype(np.int64)
+        row.update(R=R, longest_tile_list=int((rg[:, 1] - rg[:, 0]).max()), sorted_bits=32 + bit, cub_sort_pairs_ms=round(ms, 4), cub_inclusive_sum_ms=round(ms_scan, 4),
                    cub_result_equals_ours={"values": same_vals, "depth_bits": same_depth, "tile": same_tile},
                    hbm_ms_of_one_pass_24B_per_pair=round(24 * R / 6548.8e9 * 1e3, 4))
         print(json.dumps(row), flush=True)
