@@ -32,7 +32,7 @@ static std::atomic<long long> g_opt_emit_sorted_keys{0};
 static std::atomic<long long> g_opt_exact_binning{0};
 static std::atomic<long long> g_opt_capacity_hint{0};
 static std::atomic<long long> g_opt_tma_staging{0};   // compositors stage feature rows with cp.async.bulk.tensor gather4 (1) or LDGSTS (0)
-static std::atomic<long long> g_opt_taken_masks{0};   // see BLOCK_MASK_SHIFT (internal.cuh)
+static std::atomic<long long> g_opt_taken_masks{1};   // see BLOCK_MASK_SHIFT (internal.cuh); 0 = the round-1 compositors, kept for A/B
 static std::atomic<long long> g_opt_os_identify_ranges{0};   // sort mode 1: recompute the tile ranges from the sorted keys (identifyTileRanges restated) although the tile scan already wrote them
 static std::atomic<long long> g_opt_sort_mode{-1};   // 0 = tile buckets (binning.cu), 1 = global onesweep sort (onesweep.cu)
 

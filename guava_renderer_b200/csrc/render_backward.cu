@@ -189,6 +189,8 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     const uint32_t vrow0 = (uint32_t)(((size_t)v * in.colors_vs) / NUM_CHANNELS);   // TMA: first tensor-map row of this view
 
     constexpr uint32_t NO_ID = 0xffffffffu;
+    // MASKS = 0 after a forward that DID mark (the option changed in between): the index is still the low 24 bits
+    const uint32_t id_mask = (uint32_t)in.P <= BLOCK_MASK_ID ? BLOCK_MASK_ID : 0xffffffffu;
     // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front); same software
     // pipeline as the forward kernel (ids two chunks ahead, SplatRecs one chunk ahead).
     auto load_id = [&](int c) -> uint32_t {
@@ -201,7 +203,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
     auto is_kept = [&](uint32_t id) -> bool { return id != NO_ID && ((id >> (BLOCK_MASK_SHIFT + sub)) & 1u) == 0u; };
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? id : 0u);
+        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? (id & id_mask) : 0u);
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + r);
         c0 = rp[0];
         c1 = rp[1];
@@ -210,7 +212,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
         const bool keep = MASKS ? is_kept(id)
                                 : (id != NO_ID &&
                                    splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
-        if (MASKS) id &= BLOCK_MASK_ID;
+        id &= MASKS ? BLOCK_MASK_ID : id_mask;
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             BwdStage& st = stage[c & 1];
@@ -401,8 +403,8 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const float col0 = cs0.x + cs0.y;
                 const float col1 = cs1.x + cs1.y;
 
-                const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
-                const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : 0xffffffffu));
+                const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : id_mask));
+                const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : id_mask));
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
                 const bool geo_lane = lane < (INV ? 28 : 24);   // lanes 4k..4k+3: partials of moment k (7 is unused, 6 = invdepth)
                 if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);

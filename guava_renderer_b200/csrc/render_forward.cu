@@ -137,10 +137,14 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     };
     // Test chunk c (one list entry per lane) and stage the survivors into stage[c & 1].
     // Returns the survivor mask (bit = lane = list offset within the chunk).
-    // MASKS: bit = lane of the entries of the chunk being blended / being staged that this block gets nothing from
+    // MASKS: bit = lane of the entries of the chunk being blended / being staged that the footprint test rejected;
+    // `untaken`: bit = slot of the chunk's survivors that no pixel of the block took (filled by the blend loop)
     uint32_t marks_cur = 0u, marks_next = 0u;
-    auto flush_marks = [&](int c, uint32_t marks) {   // one RED.OR over the chunk's 32 consecutive words
-        if (MASKS && ((marks >> lane) & 1u)) atomicOr(&point_list[range.x + (uint32_t)(c << 5) + (uint32_t)lane], 1u << (BLOCK_MASK_SHIFT + sub));
+    auto flush_marks = [&](int c, uint32_t culled, uint32_t survivors, uint32_t untaken) {   // one RED.OR over the chunk's 32 consecutive words
+        if (!MASKS) return;
+        const int slot = __popc(survivors & lt_mask);
+        const bool mine = ((culled >> lane) & 1u) || ((((survivors >> lane) & 1u) != 0u) && (((untaken >> slot) & 1u) != 0u));
+        if (mine) atomicOr(&point_list[range.x + (uint32_t)(c << 5) + (uint32_t)lane], 1u << (BLOCK_MASK_SHIFT + sub));
     };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
         const bool keep = id != NO_ID &&
@@ -228,6 +232,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
         load_rec(id_next, a0, a1);
         id_nn = load_id(c + 3);
         const int s = c & 1;
+        uint32_t untaken = 0u, ubit = 1u;   // MASKS
         if (mask_cur != 0u) {
             wait_rows(s);
             __syncwarp();              // ... and the staging lanes' stores and copies are visible to every lane
@@ -276,8 +281,9 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
                 const bool any0 = __any_sync(0xffffffffu, take0);
                 const bool any1 = __any_sync(0xffffffffu, take1);
                 if (MASKS) {   // a survivor no pixel of the block takes contributes nothing in the backward either
-                    if (!any0) marks_cur |= 1u << ((__float_as_uint(pd.z) - 1u) & 31u);
-                    if (has1 && !any1) marks_cur |= 1u << ((__float_as_uint(pd.w) - 1u) & 31u);
+                    untaken |= any0 ? 0u : ubit;
+                    untaken |= (has1 && !any1) ? (ubit << 1) : 0u;
+                    ubit <<= 2;
                 }
                 if (any0) {
                     const float2 w2 = make_float2(w0, w0);
@@ -302,7 +308,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
                 if (__all_sync(0xffffffffu, done)) warp_done = true;
             }
         }
-        flush_marks(c, marks_cur);
+        flush_marks(c, marks_cur, mask_cur, untaken);
         marks_cur = marks_next;
         if (warp_done) {   // never leave the block with a copy still in flight
             if (TMA) { if (mask_next != 0u) wait_rows(s ^ 1); }

@@ -307,10 +307,11 @@ int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int widt
  * same results; needs colors_view_stride % 32 == 0),
  * "os_identify_ranges" (0/1, default 0: sort mode 1 re-derives the tile ranges from the sorted keys --
  * identifyTileRanges, rasterizer_impl.cu:116-138, restated -- although the tile scan has already written them),
- * "taken_masks" (0/1: the forward compositor marks, in bit 24 + b of a point_list entry, that 8x4 pixel block b of
+ * "taken_masks" (0/1, default 1: the forward compositor marks, in bit 24 + b of a point_list entry, that 8x4 pixel block b of
  * the tile got nothing from that entry -- rejected by the footprint test or taken by no pixel -- and the backward
  * compositor walks only the unmarked entries; point_list entries then are not plain indices (index = low 24 bits);
- * P < 2^24; must not change between a forward call and its backward call).
+ * applies when P < 2^24; 0 = the compositors of round 1, kept for A/B; the backward reads indices through the
+ * 24-bit mask either way, so changing the option between a forward call and its backward call costs speed, not correctness).
  * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);

@@ -1,7 +1,7 @@
 # One GPU-box session: full GPU test suite, A/B of the compositor options, both bench arms, other workloads,
 # sort micro-benchmark, then the profiler passes on the default configuration.  Outputs under gpurun_out/$TAG.
 set -x
-TAG=${TAG:-r02_v3}
+TAG=${TAG:-r02_v4}
 O=gpurun_out/$TAG; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm --format=csv > $O/gpu.txt
 rm -f gpurun_out/grad_parity_stats.jsonl
@@ -9,12 +9,12 @@ timeout 1500 python -m pytest tests -m gpu -q > $O/pytest_gpu.log 2>&1
 cp gpurun_out/grad_parity_stats.jsonl $O/ 2>/dev/null
 B="timeout 200 python bench.py --steps 100 --warmup 10 --no-cpu-baseline"
 $B > $O/bench_base.json 2> $O/bench_base.err
-GUAVA_OPT_TAKEN_MASKS=1 $B > $O/bench_taken.json 2> $O/bench_taken.err
+GUAVA_OPT_TAKEN_MASKS=0 $B > $O/bench_nomasks.json 2> $O/bench_nomasks.err
 $B > $O/bench_base2.json 2> $O/bench_base2.err
-GUAVA_OPT_TAKEN_MASKS=1 $B > $O/bench_taken2.json 2> $O/bench_taken2.err
+GUAVA_OPT_TAKEN_MASKS=0 $B > $O/bench_nomasks2.json 2> $O/bench_nomasks2.err
+$B --eager > $O/bench_eager.json 2> $O/bench_eager.err
 $B --P 202000 > $O/bench_202k.json 2> $O/bench_202k.err
-GUAVA_OPT_TAKEN_MASKS=1 $B --P 202000 > $O/bench_202k_taken.json 2> $O/bench_202k_taken.err
-GUAVA_OPT_SORT_MODE=1 $B --P 202000 > $O/bench_202k_onesweep.json 2> $O/bench_202k_onesweep.err
+GUAVA_OPT_TAKEN_MASKS=0 $B --P 202000 > $O/bench_202k_nomasks.json 2> $O/bench_202k_nomasks.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > $O/bench_ref.json 2> $O/bench_ref.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 --P 202000 --no-cpu-baseline > $O/bench_ref_202k.json 2> $O/bench_ref_202k.err
 timeout 200 python bench.py --steps 20 --warmup 5 > $O/bench_own_driverlike.json 2> $O/bench_own_driverlike.err
