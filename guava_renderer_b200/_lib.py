@@ -49,7 +49,7 @@ class Layout(Structure):
         "geom_bytes", "splat_rec", "depths", "rects", "tiles_touched", "grad_geo",
         "image_bytes", "final_T", "n_contrib", "ranges", "tile_cursor", "tile_order", "num_rendered",
         "binning_bytes", "point_list", "keys_unsorted", "keys_sorted",
-        "point_offsets", "os_vals_alt", "os_scratch")]
+        "point_offsets", "os_vals_alt", "os_scratch", "taken_marks")]
 
 
 class CallOptions(Structure):

@@ -126,7 +126,8 @@ struct StageTimer {
     }
 };
 
-static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emit_keys, guava_layout* L, int sort_mode = 0)
+static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emit_keys, guava_layout* L, int sort_mode = 0,
+                           bool taken_masks = false)
 {
     const size_t n = (size_t)V * P;
     const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
@@ -150,6 +151,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->image_bytes = o;
     o = 0;
     L->point_list = o;    o = align_up(o + capacity * 4);
+    L->taken_marks = o;   o = align_up(o + (taken_masks ? capacity * 8 : 0));   // right behind point_list: the backward finds it from the capacity in the call's header
     L->keys_unsorted = o; o = align_up(o + capacity * 8);
     L->keys_sorted = o;   o = align_up(o + ((emit_keys || sort_mode == 1) ? capacity * 8 : 0));
     L->os_vals_alt = o;   o = align_up(o + (sort_mode == 1 ? capacity * 4 : 0));
@@ -360,7 +362,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     if (co != nullptr && co->struct_size != sizeof(guava_call_options))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "guava_call_options::struct_size does not match this library");
     in.aux_nhwc_bf16 = co ? co->refiner_output_nhwc_bf16 : nullptr;
-    const int block_masks = g_opt_taken_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // ids must fit 24 bits
+    const int block_masks = g_opt_taken_masks.load() != 0;
     uint32_t* const status_host = co ? (uint32_t*)co->status_words : nullptr;
     if (((uintptr_t)status_host & 7) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");
@@ -397,7 +399,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
 
     guava_layout L;
     size_t cap = capacity_estimate(n, in.W, in.H);
-    compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
+    compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode, block_masks != 0);
     char* geom = geometryBuffer(geometry_user, L.geom_bytes);
     char* img = imageBuffer(image_user, L.image_bytes);
     if (!geom || !img) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
@@ -485,7 +487,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         if (rc) return rc;
         have_R = true;
         cap = R;
-        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode, block_masks != 0);
         const unsigned long long cap64 = (unsigned long long)cap;   // header words [6], [7] (the scan saw "unbounded")
         GUAVA_CUDA(cudaMemcpyAsync(im.num_rendered + 6, &cap64, 8, cudaMemcpyHostToDevice, stream));
     }
@@ -497,6 +499,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         b.point_list = (uint32_t*)(bin + L.point_list);
         b.keys_unsorted = (uint64_t*)(bin + L.keys_unsorted);
         b.keys_sorted = emit_keys ? (uint64_t*)(bin + L.keys_sorted) : nullptr;
+        b.taken_marks = block_masks ? (uint8_t*)(bin + L.taken_marks) : nullptr;
         b.capacity = cap;
         if (sort_mode == 1) {
             if (cap >= (1u << 30)) return fail(GUAVA_ERR_INVALID_ARGUMENT, "sort_mode 1 supports < 2^30 instances");
@@ -531,7 +534,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         // the scan skipped itself
         with_large = true;
         if ((size_t)R > cap) cap = (size_t)R;
-        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode);
+        compute_layout(in.V, in.P, in.W, in.H, cap, emit_keys, &L, sort_mode, block_masks != 0);
         bin = binningBuffer(binning_user, L.binning_bytes);
         if (!bin) return fail(GUAVA_ERR_ALLOC, "allocator returned NULL");
         reset_cursor_kernel<<<(total_tiles + 255) / 256, 256, 0, stream>>>(total_tiles, im.ranges, im.tile_cursor,
@@ -551,7 +554,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
                          float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream)
 {
     if ((size_t)in.V * in.P == 0) return GUAVA_OK;
-    const int block_masks = g_opt_taken_masks.load() != 0 && (uint32_t)in.P <= BLOCK_MASK_ID;   // as in the forward call
+    const int block_masks = g_opt_taken_masks.load() != 0;   // a backward after a forward that did not mark finds that in the header
     if (!geom || !bin || !img || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
         !dL_dmean3D || !dL_dcov3D || !radii)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
@@ -585,6 +588,7 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     b.point_list = (uint32_t*)(bin + L.point_list);   // offset 0 for every capacity
     b.keys_unsorted = nullptr;
     b.keys_sorted = nullptr;
+    b.taken_marks = nullptr;   // located by the kernel: behind point_list, whose length (the capacity) is in the header
     b.capacity = 0;
 
     StageTimer timer(stream);
@@ -791,7 +795,7 @@ int guava_buffer_layout_of_call(const char* image_buffer, int V, int P, int widt
     const int mode = (int)(hdr[5] & 0xffu);
     const size_t cap = (size_t)hdr[6] | ((size_t)hdr[7] << 32);
     // the sorted keys exist in mode 1 always, in mode 0 when the call ran with "emit_sorted_keys" (header bit 16)
-    compute_layout(V, P, width, height, cap, (hdr[5] >> 16) & 1u, out, mode);
+    compute_layout(V, P, width, height, cap, (hdr[5] >> 16) & 1u, out, mode, ((hdr[5] >> 8) & 1u) != 0);
     if (sort_mode) *sort_mode = mode;
     if (block_masks) *block_masks = (int)((hdr[5] >> 8) & 1u);
     if (capacity) *capacity = cap;

@@ -87,7 +87,8 @@ template <int MASKS, int TMA, int INV>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
-                       const uint32_t* __restrict__ point_list, const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                       const uint32_t* __restrict__ point_list, const uint8_t* __restrict__ taken_marks,
+                       const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ num_rendered)
 {
@@ -101,6 +102,14 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     // learns of it through the status words / num_rendered[1].
     if (num_rendered[1]) return;
     uint32_t* const work_counter = num_rendered + 3;
+    // MASKS: the forward's marks lie behind point_list (api.cu compute_layout), whose length is in the call's header;
+    // a forward that ran without marking says so there, and every entry is then walked (slow, correct)
+    const uint8_t* marks = nullptr;
+    if (MASKS && ((num_rendered[5] >> 8) & 1u) != 0u) {
+        const size_t cap = (size_t)num_rendered[6] | ((size_t)num_rendered[7] << 32);
+        marks = reinterpret_cast<const uint8_t*>(point_list) + ((cap * 4 + 255) / 256) * 256;
+    }
+    (void)taken_marks;
     const int lane = threadIdx.x;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const size_t HW = (size_t)in.H * in.W;
@@ -189,30 +198,30 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     const uint32_t vrow0 = (uint32_t)(((size_t)v * in.colors_vs) / NUM_CHANNELS);   // TMA: first tensor-map row of this view
 
     constexpr uint32_t NO_ID = 0xffffffffu;
-    // MASKS = 0 after a forward that DID mark (the option changed in between): the index is still the low 24 bits
-    const uint32_t id_mask = (uint32_t)in.P <= BLOCK_MASK_ID ? BLOCK_MASK_ID : 0xffffffffu;
     // chunk c, lane L  <->  list position  total-1-(32c+L)   (back to front); same software
     // pipeline as the forward kernel (ids two chunks ahead, SplatRecs one chunk ahead).
     auto load_id = [&](int c) -> uint32_t {
         const int k = (c << 5) + lane;
-        return k < total ? point_list[range.x + (uint32_t)(total - 1 - k)] : NO_ID;
+        if (k >= total) return NO_ID;
+        const uint32_t p = range.x + (uint32_t)(total - 1 - k);
+        const uint32_t id = point_list[p];
+        // MASKS: an entry the forward marked for this block is no entry at all (both loads are in flight together)
+        if (MASKS && marks != nullptr) return marks[(size_t)p * 8 + sub] != 0 ? NO_ID : id;
+        return id;
     };
     // Unconditional (lanes past the end of the list re-read record 0 and are masked by `keep`): a predicated
     // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
     // those moves stalled the warp for the whole L2 round trip right after the load was issued
     // (profiles/r01_v8: 7.7 % / 5 % of the forward / backward kernel's stall samples on that one instruction).
-    auto is_kept = [&](uint32_t id) -> bool { return id != NO_ID && ((id >> (BLOCK_MASK_SHIFT + sub)) & 1u) == 0u; };
     auto load_rec = [&](uint32_t id, float4& c0, float4& c1) {
-        const uint32_t r = MASKS ? (is_kept(id) ? (id & BLOCK_MASK_ID) : 0u) : (id != NO_ID ? (id & id_mask) : 0u);
+        const uint32_t r = id != NO_ID ? id : 0u;
         const float4* __restrict__ rp = reinterpret_cast<const float4*>(vrecs + r);
         c0 = rp[0];
         c1 = rp[1];
     };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
-        const bool keep = MASKS ? is_kept(id)
-                                : (id != NO_ID &&
-                                   splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
-        id &= MASKS ? BLOCK_MASK_ID : id_mask;
+        const bool keep = id != NO_ID &&
+                          (MASKS || splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
             BwdStage& st = stage[c & 1];
@@ -403,8 +412,8 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const float col0 = cs0.x + cs0.y;
                 const float col1 = cs1.x + cs1.y;
 
-                const size_t gi0 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl0) & (MASKS ? BLOCK_MASK_ID : id_mask));
-                const size_t gi1 = gbase + (__shfl_sync(0xffffffffu, id_cur, jl1) & (MASKS ? BLOCK_MASK_ID : id_mask));
+                const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
+                const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
                 const bool geo_lane = lane < (INV ? 28 : 24);   // lanes 4k..4k+3: partials of moment k (7 is unused, 6 = invdepth)
                 if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
@@ -439,8 +448,8 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
 #define GUAVA_LAUNCH_BWD2(MK, TM, IV)                                                                                     \
     render_backward_kernel<MK, TM, IV><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,      \
-                                                           img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix,         \
-                                                           dL_dcolor, g.grad_geo, img.num_rendered)
+                                                           b.taken_marks, img.final_T, img.n_contrib, dL_dpix,            \
+                                                           dL_dinvdepth_pix, dL_dcolor, g.grad_geo, img.num_rendered)
 #define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1); else GUAVA_LAUNCH_BWD2(MK, TM, 0); } while (0)
     if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_BWD(0, 1); else GUAVA_LAUNCH_BWD(0, 0); }

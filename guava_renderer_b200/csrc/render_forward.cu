@@ -47,9 +47,8 @@ struct __align__(128) FwdStage {
 };
 
 // MASKS = 1 (option "taken_masks"): every list entry this block got nothing from -- rejected by the footprint test, or
-// a survivor that no pixel took -- is marked in bit 24 + sub of its point_list word (one coalesced RED.OR per 32-entry
-// chunk), for the backward compositor to skip; the ids this kernel reads are masked to their low 24 bits because the
-// other seven blocks of the tile are marking the same words.
+// a survivor that no pixel took -- is marked in this block's byte of BinningPtrs::taken_marks (one byte store per lane
+// and 32-entry chunk, no atomics), for the backward compositor to skip.
 // TMA = 1 (option "tma_staging"): the survivors' 128-byte feature rows are fetched by the TMA unit -- one elected
 // lane issues cp.async.bulk.tensor...tile::gather4 over a [rows, 32] tensor map of colors_precomp, four survivor rows
 // per instruction, completion on a per-stage mbarrier -- instead of eight 16-byte LDGSTS per survivor lane.
@@ -57,7 +56,7 @@ template <int MASKS, int TMA>
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
-                      uint32_t* __restrict__ point_list, uint32_t* __restrict__ num_rendered,
+                      const uint32_t* __restrict__ point_list, uint8_t* __restrict__ taken_marks, uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
@@ -123,7 +122,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     // rows are requested at the top of the next iteration.
     auto load_id = [&](int c) -> uint32_t {
         const int k = (c << 5) + lane;
-        return k < len ? (MASKS ? (point_list[range.x + k] & BLOCK_MASK_ID) : point_list[range.x + k]) : NO_ID;
+        return k < len ? point_list[range.x + k] : NO_ID;
     };
     // Unconditional (lanes past the end of the list re-read record 0 and are masked by `keep`): a predicated
     // load into loop-carried registers is compiled as load-to-temporary + predicated moves, and the first of
@@ -140,11 +139,13 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     // MASKS: bit = lane of the entries of the chunk being blended / being staged that the footprint test rejected;
     // `untaken`: bit = slot of the chunk's survivors that no pixel of the block took (filled by the blend loop)
     uint32_t marks_cur = 0u, marks_next = 0u;
-    auto flush_marks = [&](int c, uint32_t culled, uint32_t survivors, uint32_t untaken) {   // one RED.OR over the chunk's 32 consecutive words
+    auto flush_marks = [&](int c, uint32_t culled, uint32_t survivors, uint32_t untaken) {   // one byte store per lane
         if (!MASKS) return;
+        const int k = (c << 5) + lane;
+        if (k >= len) return;
         const int slot = __popc(survivors & lt_mask);
         const bool mine = ((culled >> lane) & 1u) || ((((survivors >> lane) & 1u) != 0u) && (((untaken >> slot) & 1u) != 0u));
-        if (mine) atomicOr(&point_list[range.x + (uint32_t)(c << 5) + (uint32_t)lane], 1u << (BLOCK_MASK_SHIFT + sub));
+        taken_marks[((size_t)range.x + (size_t)k) * 8 + sub] = mine ? 1 : 0;
     };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
         const bool keep = id != NO_ID &&
@@ -436,7 +437,8 @@ void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs&
     const unsigned grid = (unsigned)(total < full ? total : full);
 #define GUAVA_LAUNCH_FWD(MK, TM)                                                                                        \
     render_forward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,             \
-                                                      img.num_rendered, img.final_T, img.n_contrib, out_color, out_invdepth)
+                                                      b.taken_marks, img.num_rendered, img.final_T, img.n_contrib, out_color, \
+                                                      out_invdepth)
     if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_FWD(1, 1); else GUAVA_LAUNCH_FWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_FWD(0, 1); else GUAVA_LAUNCH_FWD(0, 0); }
 #undef GUAVA_LAUNCH_FWD

@@ -277,6 +277,9 @@ typedef struct guava_layout {
                               (GeometryState::point_offsets, rasterizer_impl.cu:280) */
     size_t os_vals_alt;    /* binning buffer: uint32 per instance, alternate value buffer of the sort */
     size_t os_scratch;     /* binning buffer: tickets, scan state, digit histograms, look-back state */
+    /* only with option "taken_masks" (default), else zero-sized */
+    size_t taken_marks;    /* binning buffer, right behind point_list: uint8[8] per instance -- byte b != 0: 8x4 pixel
+                              block b of the instance's tile got nothing from it in the forward (backward skips it) */
 } guava_layout;
 
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout *out);
@@ -307,11 +310,11 @@ int guava_buffer_layout_of_call(const char *image_buffer, int V, int P, int widt
  * same results; needs colors_view_stride % 32 == 0),
  * "os_identify_ranges" (0/1, default 0: sort mode 1 re-derives the tile ranges from the sorted keys --
  * identifyTileRanges, rasterizer_impl.cu:116-138, restated -- although the tile scan has already written them),
- * "taken_masks" (0/1, default 1: the forward compositor marks, in bit 24 + b of a point_list entry, that 8x4 pixel block b of
- * the tile got nothing from that entry -- rejected by the footprint test or taken by no pixel -- and the backward
- * compositor walks only the unmarked entries; point_list entries then are not plain indices (index = low 24 bits);
- * applies when P < 2^24; 0 = the compositors of round 1, kept for A/B; the backward reads indices through the
- * 24-bit mask either way, so changing the option between a forward call and its backward call costs speed, not correctness).
+ * "taken_masks" (0/1, default 1: the forward compositor records, one byte per (list entry, 8x4 pixel block of
+ * its tile), which entries the block got nothing from -- rejected by the footprint test or taken by no pixel --
+ * and the backward compositor walks only the others; 0 = the compositors of round 1, kept for A/B.  The forward
+ * notes in the call's header whether it marked, so changing the option between a forward call and its backward
+ * call costs speed, not correctness).
  * Returns GUAVA_OK or GUAVA_ERR_INVALID_ARGUMENT. */
 int guava_set_option(const char *name, long long value);
 long long guava_get_option(const char *name);

@@ -172,8 +172,8 @@ def test_backward_vs_reference_build(ref, case, with_invdepth):
                          ids=["taken_masks", "tma_staging", "taken_masks+tma_staging"])
 @pytest.mark.parametrize("case", GRAD_CASES, ids=lambda c: f"P{c['P']}_{c['H']}x{c['W']}")
 def test_compositor_options_give_the_same_results(case, opts, sort_mode):
-    """Options of the compositors that must not change a result.  taken_masks: the forward marks, in bits 24..31 of
-    point_list, the entries each 8x4 block got nothing from, and the backward skips them.  tma_staging: the
+    """Options of the compositors that must not change a result.  taken_masks: the forward marks, one byte per (list
+    entry, 8x4 block), the entries each block got nothing from, and the backward skips them.  tma_staging: the
     survivors' feature rows are staged by cp.async.bulk.tensor gather4 instead of LDGSTS (same bytes).  Image
     bit-identical, gradients equal to reduction order, in both binning modes."""
     inp = util.inputs_for(**case)
@@ -199,7 +199,7 @@ def test_compositor_options_give_the_same_results(case, opts, sort_mode):
         assert np.array_equal(o0[k], o1[k]), k
     assert np.array_equal(_bits(o0["final_T"]), _bits(o1["final_T"]))
     if opts.get("taken_masks"):
-        assert o1["block_masks"] == 1 and o1["point_list_masks"].any()
+        assert o1["block_masks"] == 1 and "taken_marks" in o1 and "taken_marks" not in o0
     for k in g0:     # two runs differ by the order of their floating-point reductions
         assert util.rel_err(g1[k], g0[k]) <= 5e-5, (k, util.rel_err(g1[k], g0[k]))
 
@@ -881,3 +881,32 @@ def test_compiled_and_ctypes_bindings_agree(tmp_path):
             assert util.rel_err(a[k], c[k]) <= 1e-5, k
     for k in ("xyz", "features", "opacity", "scaling", "rotation"):     # shared cloud: the two views' gradients are summed
         assert util.rel_err(a["b_" + k], 2.0 * a["g_" + k]) <= 1e-5, k
+
+
+@pytest.mark.parametrize("fwd_opt,bwd_opt", [(0, 1), (1, 0)])
+def test_taken_masks_option_may_change_between_forward_and_backward(fwd_opt, bwd_opt):
+    """The forward notes in the call's header whether it marked; a backward that expects marks after a forward that
+    wrote none walks every entry, a backward that ignores them runs its own footprint test: same gradients."""
+    case = CASES[1]
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(9)
+    dL = torch.randn(32, case["H"], case["W"], generator=g)
+    _, want = _run_autograd(ours, inp, dL, None)
+    leaf = {k: inp[k].to(DEV).clone().requires_grad_(True) for k in ("xyz", "features", "opacity", "scaling", "rotation")}
+    m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+    base = grb.get_option("taken_masks")
+    try:
+        grb.set_option("taken_masks", fwd_opt)
+        rast = ours.GaussianRasterizer_32(raster_settings=util.settings_for(ours, inp, DEV))
+        color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                                  opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"], cov3D_precomp=None)
+        loss = (color * dL.to(DEV)).sum()
+        torch.cuda.synchronize()
+        grb.set_option("taken_masks", bwd_opt)
+        loss.backward()
+        torch.cuda.synchronize()
+    finally:
+        grb.set_option("taken_masks", base)
+    for k, v in leaf.items():
+        assert util.rel_err(v.grad.cpu().numpy(), want[k]) <= 5e-5, k

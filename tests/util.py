@@ -79,11 +79,9 @@ def decode_ours(geom, binning, img, V, P, W, H, capacity=None):
     R = out["num_rendered"]
     hdr = i[L.num_rendered:L.num_rendered + 32].view(np.uint32)
     out["sort_mode"], out["block_masks"], out["capacity"] = mode, masks, cap
-    plist = b[L.point_list:L.point_list + R * 4].view(np.uint32).copy()
-    if masks:   # bits 24..31 of an entry: the tile's 8x4 pixel blocks the splat provably cannot touch
-        out["point_list_masks"] = plist >> 24
-        plist &= 0xFFFFFF
-    out["point_list"] = plist
+    out["point_list"] = b[L.point_list:L.point_list + R * 4].view(np.uint32).copy()
+    if masks:   # one byte per (list entry, 8x4 block of its tile): != 0 where the block got nothing from the entry
+        out["taken_marks"] = b[L.taken_marks:L.taken_marks + R * 8].reshape(R, 8).copy()
     if mode == 1:
         out["point_offsets"] = g[L.point_offsets:L.point_offsets + n * 4].view(np.uint32).copy()
     if mode == 1 or ((hdr[5] >> 16) & 1):
