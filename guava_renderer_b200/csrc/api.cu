@@ -151,7 +151,7 @@ static void compute_layout(int V, int P, int W, int H, size_t capacity, bool emi
     L->image_bytes = o;
     o = 0;
     L->point_list = o;    o = align_up(o + capacity * 4);
-    L->taken_marks = o;   o = align_up(o + (taken_masks ? capacity * 8 : 0));   // right behind point_list: the backward finds it from the capacity in the call's header
+    L->taken_marks = o;   o = align_up(o + (taken_masks ? align_up(capacity) * 8 : 0));   // right behind point_list: the backward finds it from the capacity in the call's header
     L->keys_unsorted = o; o = align_up(o + capacity * 8);
     L->keys_sorted = o;   o = align_up(o + ((emit_keys || sort_mode == 1) ? capacity * 8 : 0));
     L->os_vals_alt = o;   o = align_up(o + (sort_mode == 1 ? capacity * 4 : 0));

@@ -105,9 +105,11 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     // MASKS: the forward's marks lie behind point_list (api.cu compute_layout), whose length is in the call's header;
     // a forward that ran without marking says so there, and every entry is then walked (slow, correct)
     const uint8_t* marks = nullptr;
+    size_t marks_plane = 0;
     if (MASKS && ((num_rendered[5] >> 8) & 1u) != 0u) {
         const size_t cap = (size_t)num_rendered[6] | ((size_t)num_rendered[7] << 32);
         marks = reinterpret_cast<const uint8_t*>(point_list) + ((cap * 4 + 255) / 256) * 256;
+        marks_plane = (cap + 255) / 256 * 256;
     }
     (void)taken_marks;
     const int lane = threadIdx.x;
@@ -206,7 +208,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
         const uint32_t p = range.x + (uint32_t)(total - 1 - k);
         const uint32_t id = point_list[p];
         // MASKS: an entry the forward marked for this block is no entry at all (both loads are in flight together)
-        if (MASKS && marks != nullptr) return marks[(size_t)p * 8 + sub] != 0 ? NO_ID : id;
+        if (MASKS && marks != nullptr) return marks[(size_t)sub * marks_plane + p] != 0 ? NO_ID : id;
         return id;
     };
     // Unconditional (lanes past the end of the list re-read record 0 and are masked by `keep`): a predicated

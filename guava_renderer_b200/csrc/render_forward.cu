@@ -47,8 +47,8 @@ struct __align__(128) FwdStage {
 };
 
 // MASKS = 1 (option "taken_masks"): every list entry this block got nothing from -- rejected by the footprint test, or
-// a survivor that no pixel took -- is marked in this block's byte of BinningPtrs::taken_marks (one byte store per lane
-// and 32-entry chunk, no atomics), for the backward compositor to skip.
+// a survivor that no pixel took -- is marked in this block's plane of BinningPtrs::taken_marks (one byte store per lane
+// and 32-entry chunk -- 32 consecutive bytes -- no atomics), for the backward compositor to skip.
 // TMA = 1 (option "tma_staging"): the survivors' 128-byte feature rows are fetched by the TMA unit -- one elected
 // lane issues cp.async.bulk.tensor...tile::gather4 over a [rows, 32] tensor map of colors_precomp, four survivor rows
 // per instruction, completion on a per-stage mbarrier -- instead of eight 16-byte LDGSTS per survivor lane.
@@ -56,7 +56,8 @@ template <int MASKS, int TMA>
 __global__ void __launch_bounds__(32, 16)
 render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                       const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
-                      const uint32_t* __restrict__ point_list, uint8_t* __restrict__ taken_marks, uint32_t* __restrict__ num_rendered,
+                      const uint32_t* __restrict__ point_list, uint8_t* __restrict__ taken_marks, size_t marks_plane,
+                      uint32_t* __restrict__ num_rendered,
                       float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_invdepth)
 {
@@ -145,7 +146,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
         if (k >= len) return;
         const int slot = __popc(survivors & lt_mask);
         const bool mine = ((culled >> lane) & 1u) || ((((survivors >> lane) & 1u) != 0u) && (((untaken >> slot) & 1u) != 0u));
-        taken_marks[((size_t)range.x + (size_t)k) * 8 + sub] = mine ? 1 : 0;
+        taken_marks[(size_t)sub * marks_plane + (size_t)range.x + (size_t)k] = mine ? 1 : 0;   // 32 consecutive bytes per chunk
     };
     auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
         const bool keep = id != NO_ID &&
@@ -437,8 +438,8 @@ void launch_render_forward(const Inputs& in, const GeomPtrs& g, const ImagePtrs&
     const unsigned grid = (unsigned)(total < full ? total : full);
 #define GUAVA_LAUNCH_FWD(MK, TM)                                                                                        \
     render_forward_kernel<MK, TM><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,             \
-                                                      b.taken_marks, img.num_rendered, img.final_T, img.n_contrib, out_color, \
-                                                      out_invdepth)
+                                                      b.taken_marks, (b.capacity + 255) / 256 * 256, img.num_rendered,        \
+                                                      img.final_T, img.n_contrib, out_color, out_invdepth)
     if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_FWD(1, 1); else GUAVA_LAUNCH_FWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_FWD(0, 1); else GUAVA_LAUNCH_FWD(0, 0); }
 #undef GUAVA_LAUNCH_FWD

@@ -278,8 +278,9 @@ typedef struct guava_layout {
     size_t os_vals_alt;    /* binning buffer: uint32 per instance, alternate value buffer of the sort */
     size_t os_scratch;     /* binning buffer: tickets, scan state, digit histograms, look-back state */
     /* only with option "taken_masks" (default), else zero-sized */
-    size_t taken_marks;    /* binning buffer, right behind point_list: uint8[8] per instance -- byte b != 0: 8x4 pixel
-                              block b of the instance's tile got nothing from it in the forward (backward skips it) */
+    size_t taken_marks;    /* binning buffer, right behind point_list: 8 planes of (capacity rounded up to 256) bytes --
+                              plane b, byte i != 0: 8x4 pixel block b of the tile of instance i got nothing from it in
+                              the forward (the backward skips it) */
 } guava_layout;
 
 int guava_buffer_layout(int V, int P, int width, int height, size_t capacity, guava_layout *out);

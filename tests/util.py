@@ -81,7 +81,8 @@ def decode_ours(geom, binning, img, V, P, W, H, capacity=None):
     out["sort_mode"], out["block_masks"], out["capacity"] = mode, masks, cap
     out["point_list"] = b[L.point_list:L.point_list + R * 4].view(np.uint32).copy()
     if masks:   # one byte per (list entry, 8x4 block of its tile): != 0 where the block got nothing from the entry
-        out["taken_marks"] = b[L.taken_marks:L.taken_marks + R * 8].reshape(R, 8).copy()
+        plane = (cap + 255) // 256 * 256
+        out["taken_marks"] = b[L.taken_marks:L.taken_marks + 8 * plane].reshape(8, plane)[:, :R].copy()
     if mode == 1:
         out["point_offsets"] = g[L.point_offsets:L.point_offsets + n * 4].view(np.uint32).copy()
     if mode == 1 or ((hdr[5] >> 16) & 1):
