@@ -1,7 +1,7 @@
 # One GPU-box session: full GPU test suite, A/B of the compositor options, both bench arms, other workloads,
 # sort micro-benchmark, then the profiler passes on the default configuration.  Outputs under gpurun_out/$TAG.
 set -x
-TAG=${TAG:-r02_v4}
+TAG=${TAG:-r02_v6}
 O=gpurun_out/$TAG; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm --format=csv > $O/gpu.txt
 rm -f gpurun_out/grad_parity_stats.jsonl
