@@ -130,19 +130,14 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     // persistent warps pulling 8x4 pixel blocks from a work counter (see render_forward.cu)
     const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
     const uint32_t total_work = blocks_per_view * (uint32_t)in.V;
-    auto fetch_work = [&]() -> uint32_t {
-        uint32_t wk = 0;
-        if (lane == 0) wk = atomicAdd(work_counter, 1u);
-        return __shfl_sync(0xffffffffu, wk, 0);
-    };
+    auto claim_work = [&]() -> uint32_t { return lane == 0 ? atomicAdd(work_counter, 1u) : 0u; };
 
-  uint32_t work = fetch_work();
-  while (work < total_work) {
-    const uint32_t work_next = fetch_work();
+  uint32_t claimed = claim_work();
+  for (uint32_t work = __shfl_sync(0xffffffffu, claimed, 0); work < total_work; work = __shfl_sync(0xffffffffu, claimed, 0)) {
+    claimed = claim_work();   // the next block's claim: broadcast when that block begins (see render_forward.cu)
     const uint4 item = tile_order[work >> 3];   // longest lists first: (tile, range.x, range.y)
     const uint32_t gtile = item.x;
     const int sub = (int)(work & 7u);
-    work = work_next;
     const int v = (int)(gtile / (uint32_t)in.tiles);
     const int tile = (int)(gtile - (uint32_t)v * (uint32_t)in.tiles);
     const int tile_x = tile % in.gx, tile_y = tile / in.gx;

@@ -83,22 +83,25 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
     // scan), so SM slots never idle between blocks and empty tiles cost one atomic.
     const uint32_t blocks_per_view = (uint32_t)in.tiles * 8u;
     const uint32_t total_work = blocks_per_view * (uint32_t)in.V;
-    auto fetch_work = [&]() -> uint32_t {
-        uint32_t wk = 0;
-        if (lane == 0) wk = atomicAdd(&num_rendered[2], 1u);
-        return __shfl_sync(0xffffffffu, wk, 0);
-    };
+    // lane 0 claims; the claim is broadcast only when the block it is for begins (the loop's increment), so the
+    // atomic's round trip to the L2 lies under the block before (the shuffle right behind the atomic held 2.5 % of
+    // this kernel's stall samples, profiles/r02_v6)
+    auto claim_work = [&]() -> uint32_t { return lane == 0 ? atomicAdd(&num_rendered[2], 1u) : 0u; };
+    // backgrounds of the first views in shared memory: the epilogue's 32 FFMAs otherwise each wait for a global load
+    constexpr int BG_VIEWS = 8;
+    __shared__ float s_bg[BG_VIEWS][NUM_CHANNELS];
+    for (int vv = 0; vv < min(in.V, BG_VIEWS); vv++) s_bg[vv][lane] = in.background[(size_t)vv * NUM_CHANNELS + lane];
+    __syncwarp();
 
-  uint32_t work = fetch_work();
-  while (work < total_work) {
-    const uint32_t work_next = fetch_work();   // in flight while this block is blended
+  uint32_t claimed = claim_work();
+  for (uint32_t work = __shfl_sync(0xffffffffu, claimed, 0); work < total_work; work = __shfl_sync(0xffffffffu, claimed, 0)) {
+    claimed = claim_work();   // the next block's claim, in flight while this block is blended
     // one 16-byte work item (tile, list range) instead of two dependent loads (tile order -> range); claiming
     // two blocks ahead to hide this load as well measured 10 % slower (coarser dynamic balancing)
     const uint4 item = tile_order[work >> 3];   // longest lists first
     const uint32_t gtile = item.x;
     const uint2 range = make_uint2(item.y, item.z);
     const int sub = (int)(work & 7u);
-    work = work_next;
     const int v = (int)(gtile / (uint32_t)in.tiles);
     const int tile = (int)(gtile - (uint32_t)v * (uint32_t)in.tiles);
     const int tile_x = tile % in.gx, tile_y = tile / in.gx;
@@ -326,7 +329,7 @@ render_forward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap,
         const size_t pix = (size_t)py * in.W + px;
         final_T[(size_t)v * HW + pix] = T;
         n_contrib[(size_t)v * HW + pix] = last_contributor;
-        const float* __restrict__ bg = in.background + (size_t)v * NUM_CHANNELS;
+        const float* bg = v < BG_VIEWS ? &s_bg[v][0] : in.background + (size_t)v * NUM_CHANNELS;
         float* __restrict__ oc = out_color + (size_t)v * NUM_CHANNELS * HW + pix;
 #pragma unroll
         for (int ch = 0; ch < NUM_CHANNELS / 2; ch++) {
