@@ -83,7 +83,10 @@ __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&
 // TMA = 1 (option "tma_staging"): feature rows staged by cp.async.bulk.tensor gather4.
 // INV = 0: no upstream gradient for the inverse depth (GUAVA's losses never read the depth output,
 // utils/loss_utils.py:89-138): the per-splat 1/depth operand, its term of the dot product and the seventh moment drop out.
-template <int MASKS, int TMA, int INV>
+// NST: number of staging buffers.  2 = chunk c+1 is staged while chunk c is blended; 3 = chunk c+2 is (a chunk with
+// one or two survivors is blended in a few hundred cycles, less than the L2 round trip of the next chunk's rows: the
+// wait behind cp.async.wait_group held 7 % of the NST = 2 kernel's stall samples, profiles/r02_v6).
+template <int MASKS, int TMA, int INV, int NST>
 __global__ void __launch_bounds__(32, 12)
 render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
@@ -92,10 +95,10 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                        float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ num_rendered)
 {
-    __shared__ BwdStage stage[2];
+    __shared__ BwdStage stage[NST];
     __shared__ __align__(16) float ex[4][32];   // blending weights of a survivor, one per pixel: two pairs in flight
-    __shared__ __align__(16) uint32_t srows[2][32];   // TMA: tensor-map row of the survivor in each slot
-    __shared__ __align__(8) uint64_t bars[2];         // TMA: one transaction barrier per stage
+    __shared__ __align__(16) uint32_t srows[NST][32];   // TMA: tensor-map row of the survivor in each slot
+    __shared__ __align__(8) uint64_t bars[NST];         // TMA: one transaction barrier per stage
 
     // The forward's binning overflowed (a replayed capture whose capacity was outgrown): its instance kernels
     // skipped themselves, the lists this kernel would walk were never written.  Gradients stay zero; the caller
@@ -120,8 +123,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     uint32_t phase = 0;    // TMA: bit s = parity the next wait on bars[s] uses
     if (TMA) {
         if (lane == 0) {
-            tma::mbar_init(&bars[0], 1);
-            tma::mbar_init(&bars[1], 1);
+            for (int q = 0; q < NST; q++) tma::mbar_init(&bars[q], 1);
             tma::fence_mbar_init();
         }
         __syncwarp();
@@ -216,12 +218,12 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
         c0 = rp[0];
         c1 = rp[1];
     };
-    auto stage_chunk = [&](int c, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {
+    auto stage_chunk = [&](int sq, uint32_t id, const float4& c0, const float4& c1) -> uint32_t {   // sq: staging buffer
         const bool keep = id != NO_ID &&
                           (MASKS || splat_may_touch(c0.x, c0.y, c0.z, c0.w, c1.x, c1.w, wx0, wx0 + 7.0f, wy0, wy0 + 3.0f));
         const uint32_t mask = __ballot_sync(0xffffffffu, keep);
         if (mask != 0u) {
-            BwdStage& st = stage[c & 1];
+            BwdStage& st = stage[sq];
             if (keep) {
                 const int slot = __popc(mask & lt_mask);
                 const int o = (slot >> 1) * 4 + (slot & 1);
@@ -231,7 +233,7 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 q = &st.cop[0].x + o;  q[0] = c1.x; q[2] = c1.y;
                 if (INV) (&st.rd[0].x)[slot] = c1.z;
                 if (TMA) {
-                    srows[c & 1][slot] = vrow0 + id;
+                    srows[sq][slot] = vrow0 + id;
                 } else {
                     // the lane's own 128-byte feature row as eight 16-byte asynchronous copies, piece order rotated by
                     // the slot so that the lanes of one instruction fall on distinct bank groups (render_forward.cu)
@@ -248,13 +250,13 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const int nsurv = __popc(mask);
                 const int ngroups = (nsurv + 3) >> 2;
                 const uint32_t first_row = vrow0 + __shfl_sync(0xffffffffu, id, __ffs(mask) - 1);
-                if (lane < 3 && nsurv + lane < 4 * ngroups) srows[c & 1][nsurv + lane] = first_row;
+                if (lane < 3 && nsurv + lane < 4 * ngroups) srows[sq][nsurv + lane] = first_row;
                 __syncwarp();
                 if (lane == 0) {
-                    tma::mbar_arrive_expect_tx(&bars[c & 1], (uint32_t)ngroups * 512u);
+                    tma::mbar_arrive_expect_tx(&bars[sq], (uint32_t)ngroups * 512u);
                     for (int gq = 0; gq < ngroups; gq++) {
-                        const uint4 r = *reinterpret_cast<const uint4*>(&srows[c & 1][4 * gq]);
-                        tma::tensor_gather4_g2s(&st.feat[4 * gq][0], &fmap, 0, (int)r.x, (int)r.y, (int)r.z, (int)r.w, &bars[c & 1]);
+                        const uint4 r = *reinterpret_cast<const uint4*>(&srows[sq][4 * gq]);
+                        tma::tensor_gather4_g2s(&st.feat[4 * gq][0], &fmap, 0, (int)r.x, (int)r.y, (int)r.z, (int)r.w, &bars[sq]);
                     }
                 }
             }
@@ -267,29 +269,37 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     float A = 0.0f, last_alpha = 0.0f, last_d = 0.0f;
     const size_t gbase = (size_t)v * in.P;
 
+    // Software pipeline, AHEAD = NST - 1 chunks deep: while chunk c is blended, chunks c+1 .. c+AHEAD are staged (rows in
+    // flight), the records of chunk c+AHEAD+1 are in flight into a0/a1 and the ids of chunk c+AHEAD+2 into id_q[AHEAD+2].
+    // id_q[k]: ids of chunk c+k (id_q[0] gives the gradient addresses of the chunk being blended).
+    constexpr int AHEAD = NST - 1;
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
-    uint32_t id_cur = load_id(0);
-    uint32_t id_next = load_id(1);
-    load_rec(id_cur, a0, a1);
-    uint32_t mask_cur = stage_chunk(0, id_cur, a0, a1);
-    load_rec(id_next, a0, a1);
-    uint32_t id_nn = load_id(2);
+    uint32_t id_q[AHEAD + 3], mask_q[AHEAD + 1];
+#pragma unroll
+    for (int k = 0; k < AHEAD + 2; k++) id_q[k] = load_id(k);
+#pragma unroll
+    for (int k = 0; k < AHEAD; k++) {   // chunks 0 .. AHEAD-1 staged before the loop
+        load_rec(id_q[k], a0, a1);
+        if (k < nchunks) mask_q[k] = stage_chunk(k, id_q[k], a0, a1);
+        else { mask_q[k] = 0u; if (!TMA) tma::cp_async_commit(); }
+    }
+    load_rec(id_q[AHEAD], a0, a1);
+    int s = 0;   // c % NST
     for (int c = 0; c < nchunks; c++) {
-        // id_cur: ids of chunk c (for the gradient addresses); id_next / a0,a1: chunk c+1
-        uint32_t mask_next = 0u;
-        if (c + 1 < nchunks) mask_next = stage_chunk(c + 1, id_next, a0, a1);
+        int sq = s + AHEAD; if (sq >= NST) sq -= NST;   // (c + AHEAD) % NST
+        mask_q[AHEAD] = 0u;
+        if (c + AHEAD < nchunks) mask_q[AHEAD] = stage_chunk(sq, id_q[AHEAD], a0, a1);
         else if (!TMA) tma::cp_async_commit();
-        const uint32_t id_after = id_next;
-        id_next = id_nn;
-        load_rec(id_next, a0, a1);
-        id_nn = load_id(c + 3);
-        const int s = c & 1;
+        load_rec(id_q[AHEAD + 1], a0, a1);
+        id_q[AHEAD + 2] = load_id(c + AHEAD + 2);
+        const uint32_t mask_cur = mask_q[0];
+        const uint32_t id_cur = id_q[0];
         if (mask_cur != 0u) {
             if (TMA) {
                 tma::mbar_wait(&bars[s], (phase >> s) & 1u);
                 phase ^= 1u << s;
             } else {
-                tma::cp_async_wait<1>();   // everything but the newest group (chunk c+1) has landed
+                tma::cp_async_wait<AHEAD>();   // everything but the newest AHEAD groups has landed
             }
             __syncwarp();
             const BwdStage& stg = stage[s];
@@ -419,9 +429,12 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
             }
         }
-        mask_cur = mask_next;
-        id_cur = id_after;
-        __syncwarp();   // every lane is done reading stage[s] before chunk c+2 overwrites it
+#pragma unroll
+        for (int k = 0; k < AHEAD; k++) mask_q[k] = mask_q[k + 1];
+#pragma unroll
+        for (int k = 0; k < AHEAD + 2; k++) id_q[k] = id_q[k + 1];
+        if (++s == NST) s = 0;
+        __syncwarp();   // every lane is done reading this stage before a later chunk overwrites it
     }
     if (!TMA) tma::cp_async_wait<0>();
     __syncwarp();   // nothing in flight when the next block reuses the stages
@@ -443,12 +456,15 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
-#define GUAVA_LAUNCH_BWD2(MK, TM, IV)                                                                                     \
-    render_backward_kernel<MK, TM, IV><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,      \
-                                                           b.taken_marks, img.final_T, img.n_contrib, dL_dpix,            \
-                                                           dL_dinvdepth_pix, dL_dcolor, g.grad_geo, img.num_rendered)
-#define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1); else GUAVA_LAUNCH_BWD2(MK, TM, 0); } while (0)
-    if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
+    static const int stages = [] { const char* e = getenv("GUAVA_BWD_STAGES"); return e ? atoi(e) : 2; }();   // tuning knob
+#define GUAVA_LAUNCH_BWD2(MK, TM, IV, NS)                                                                                 \
+    render_backward_kernel<MK, TM, IV, NS><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,  \
+                                                               b.taken_marks, img.final_T, img.n_contrib, dL_dpix,        \
+                                                               dL_dinvdepth_pix, dL_dcolor, g.grad_geo, img.num_rendered)
+#define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1, 2); else GUAVA_LAUNCH_BWD2(MK, TM, 0, 2); } while (0)
+    if (taken_masks && !tma_staging && stages == 3) {   // the deeper pipeline exists for the default variant only
+        if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(1, 0, 1, 3); else GUAVA_LAUNCH_BWD2(1, 0, 0, 3);
+    } else if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_BWD(0, 1); else GUAVA_LAUNCH_BWD(0, 0); }
 #undef GUAVA_LAUNCH_BWD
 #undef GUAVA_LAUNCH_BWD2
