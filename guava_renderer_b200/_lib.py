@@ -26,6 +26,7 @@ EXPORTS = (
     "guava_selftest_cull",
     "guava_deform_gaussians_forward",
     "guava_deform_gaussians_backward",
+    "guava_deform_gaussians_forward_static",
     "guava_buffer_layout",
     "guava_buffer_layout_of_call",
     "guava_set_option",
@@ -115,6 +116,8 @@ def load() -> ctypes.CDLL:
     lib.guava_image_dot.argtypes = [P, P, c_size_t, P, P]
     lib.guava_deform_gaussians_forward.restype = c_int
     lib.guava_deform_gaussians_forward.argtypes = [c_int] * 4 + [P] * 21
+    lib.guava_deform_gaussians_forward_static.restype = c_int
+    lib.guava_deform_gaussians_forward_static.argtypes = [c_int] * 4 + [P] * 20
     lib.guava_deform_gaussians_backward.restype = c_int
     lib.guava_deform_gaussians_backward.argtypes = [c_int] * 4 + [P] * 12
     lib.guava_buffer_layout.restype = c_int

@@ -56,6 +56,8 @@ static int fail(int code, const std::string& msg)
     return code;
 }
 
+int report_error(int code, const char* msg) { return fail(code, msg ? msg : ""); }
+
 #define GUAVA_CUDA(expr)                                                                        \
     do {                                                                                        \
         cudaError_t e__ = (expr);                                                               \

@@ -20,6 +20,10 @@
 // Gradients are produced for the per-Gaussian attributes (uv_local_xyz, uv_rotation, uv_scaling,
 // smplx_rotation); the mesh (vertices, vertex transforms) is an input without gradient.
 #include "internal.cuh"
+#include "../../include/guava_rasterizer.h"
+
+#include <atomic>
+#include <string>
 
 namespace guava {
 
@@ -287,11 +291,78 @@ void launch_deform_backward(const DeformArgs& a, const float* g_xyz, const float
     count_launch();
 }
 
+// ------------------------------------------------------------------------------------ no-allocation variant
+// Scratch of guava_deform_gaussians_forward_static: the per-(batch, face) frames (4 x float4 each) that the regular
+// entry point takes from its caller.  File-scope device memory: every GPU that loads the library holds these 4 MiB
+// until the process exits.  In HOST code `g_static_frames` is only a stand-in for the symbol, not a device address:
+// the address a kernel may be given comes from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) float4 g_static_frames[(size_t)GUAVA_DEFORM_STATIC_MAX_FACE_FRAMES * 4];
+
+static cudaError_t static_frames_address(float4** out)
+{
+    static std::atomic<float4*> cached[64];   // per device ordinal
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    float4* p = (dev >= 0 && dev < 64) ? cached[dev].load(std::memory_order_acquire) : nullptr;
+    if (p == nullptr) {
+        void* addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_static_frames);   // the current device's instance of the array
+        if (e != cudaSuccess) return e;
+        if (addr == nullptr) return cudaErrorInvalidSymbol;
+        p = static_cast<float4*>(addr);
+        if (dev >= 0 && dev < 64) cached[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
 }  // namespace guava
 
 using namespace guava;
 
 extern "C" {
+
+int guava_deform_gaussians_forward_static(int B, int Nv, int N, int F, const float* vertices, const float* ver_transform,
+                                          const int* faces, const int* uv_binding_face, const float* uv_face_bary,
+                                          const float* smplx_rotation, const float* smplx_scaling,
+                                          const float* smplx_opacity, const float* smplx_features,
+                                          const float* uv_local_xyz, const float* uv_rotation, const float* uv_scaling,
+                                          const float* uv_opacity, const float* uv_features, float* out_xyz,
+                                          float* out_rotation, float* out_scaling, float* out_opacity,
+                                          float* out_features, void* stream)
+{
+    if (B < 0 || Nv < 0 || N < 0 || F < 0) return report_error(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if ((size_t)B * ((size_t)Nv + N) == 0) return GUAVA_OK;
+    if (N != 0 && (size_t)B * (size_t)F > (size_t)GUAVA_DEFORM_STATIC_MAX_FACE_FRAMES) {
+        const std::string msg = "guava_deform_gaussians_forward_static: B*F = " + std::to_string((size_t)B * (size_t)F) +
+                                " face frames exceed the static scratch (maximum " +
+                                std::to_string((size_t)GUAVA_DEFORM_STATIC_MAX_FACE_FRAMES) +
+                                "); use guava_deform_gaussians_forward with caller-provided face_frames";
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, msg.c_str());
+    }
+    if (!vertices || !out_xyz || !out_rotation || !out_scaling || !out_opacity)
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (Nv && (!ver_transform || !smplx_rotation || !smplx_scaling || !smplx_opacity))
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (N && (!faces || !uv_binding_face || !uv_face_bary || !uv_local_xyz || !uv_rotation || !uv_scaling || !uv_opacity))
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (out_features && ((Nv && !smplx_features) || (N && !uv_features)))
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    float4* frames = nullptr;
+    const cudaError_t e = static_frames_address(&frames);
+    if (e != cudaSuccess)
+        return report_error(GUAVA_ERR_CUDA, (std::string("cudaGetSymbolAddress(g_static_frames): ") + cudaGetErrorString(e)).c_str());
+    // Nothing of the scratch has to start at zero: face_frames_kernel writes all B*F frames of this call before
+    // deform_forward_kernel (same stream) reads any; what an earlier call left beyond them is never read.
+    DeformArgs a{B, Nv, N, N ? F : 0, vertices, ver_transform, faces, uv_binding_face, uv_face_bary, smplx_rotation,
+                 smplx_scaling, smplx_opacity, uv_local_xyz, uv_rotation, uv_scaling, uv_opacity, frames};
+    launch_deform_forward(a, smplx_features, uv_features, out_xyz, out_rotation, out_scaling, out_opacity, out_features,
+                          (cudaStream_t)stream);
+    const cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) return report_error(GUAVA_ERR_CUDA, cudaGetErrorString(le));
+    return GUAVA_OK;
+}
 
 int guava_deform_gaussians_forward(int B, int Nv, int N, int F, const float* vertices, const float* ver_transform,
                                    const int* faces, const int* uv_binding_face, const float* uv_face_bary,

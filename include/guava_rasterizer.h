@@ -375,6 +375,30 @@ int guava_deform_gaussians_backward(
     float *dL_dsmplx_rotation /* [B,Nv,4] */, float *dL_duv_local_xyz /* [B,N,3] */,
     float *dL_duv_rotation /* [B,N,4] */, float *dL_duv_scaling /* [B,N,3] */, void *stream);
 
+/* No-allocation variant of guava_deform_gaussians_forward.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same inputs, same outputs, same arithmetic as
+ * guava_deform_gaussians_forward, but the `face_frames` scratch is not an argument: it lives in a file-scope
+ * `static __device__ __align__(256)` array of the library (csrc/deform.cu), whose device address the library obtains
+ * with cudaGetSymbolAddress once per device.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine): it validates, looks the address up and enqueues the same kernels on `stream`.
+ * Limit: B * F <= GUAVA_DEFORM_STATIC_MAX_FACE_FRAMES (65536 face frames = 4 MiB, held by every GPU that loads the
+ * library until the process exits; the SMPLX mesh has F = 20908, so B <= 3); beyond it the call returns
+ * GUAVA_ERR_INVALID_ARGUMENT with the numbers in guava_last_error().
+ * The array is shared by every call on the device and keeps the last call's contents: nothing in it has to start at
+ * zero (each call writes all of its B*F frames before reading any), but two calls that overlap on the GPU --
+ * different streams, or concurrent host threads -- RACE on it; serialise them (one stream, or events).  The frames
+ * do not survive the next call, so there is no backward for this variant: training uses the regular entry point. */
+#define GUAVA_DEFORM_STATIC_MAX_FACE_FRAMES 65536
+int guava_deform_gaussians_forward_static(
+    int B, int Nv, int N, int F,
+    const float *vertices /* [B,Nv,3] */, const float *ver_transform /* [B,Nv,4,4] */,
+    const int *faces /* [F,3] */, const int *uv_binding_face /* [N] */, const float *uv_face_bary /* [N,3] */,
+    const float *smplx_rotation, const float *smplx_scaling, const float *smplx_opacity, const float *smplx_features,
+    const float *uv_local_xyz, const float *uv_rotation, const float *uv_scaling, const float *uv_opacity,
+    const float *uv_features,
+    float *out_xyz, float *out_rotation, float *out_scaling, float *out_opacity, float *out_features, void *stream);
+
 const char *guava_last_error(void);
 const char *guava_version(void);
 
