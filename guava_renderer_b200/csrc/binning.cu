@@ -377,7 +377,7 @@ tile_sort_small_kernel(const uint4* __restrict__ tile_order, const uint32_t* __r
 // memory up to SORT_LARGE keys, beyond that with the same network in place in global
 // memory (L2-resident).  When there is nothing to do the launch costs a few microseconds.
 static constexpr uint32_t SORT_SMALL = 2048;    // 16 KB of keys, 256 threads
-static constexpr uint32_t SORT_MID = 4096;      // 1024 threads x 4 keys in registers (the real GUAVA training size, P = 202 k, has lists of 2-3 k)
+static constexpr uint32_t SORT_MID = 4096;      // 512 threads x 8 keys in registers (the real GUAVA training size, P = 202 k, has lists of 2-3 k)
 static constexpr uint32_t SORT_LARGE = 16384;   // 128 KB of keys, 1024 threads
 
 __global__ void __launch_bounds__(1024)
@@ -386,19 +386,15 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                        uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
 {
     extern __shared__ uint64_t skeys[];
-    if (num_rendered[1] || num_rendered[4] <= SORT_SMALL) return;
+    if (num_rendered[1] || num_rendered[4] <= SORT_MID) return;
     const int tid = threadIdx.x;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const uint2 r = ranges[tile];
         const uint32_t n = r.y - r.x;
         if (n <= SORT_SMALL) continue;   // block-uniform
         const uint64_t tile_hi = (uint64_t)(tile % tiles_per_view) << 32;
-        if (n <= SORT_MID) {
-            // same register-resident network as the small buckets, 1024 threads x 4 keys: 15 of its 78 steps go through
-            // shared memory, where the network below synchronises the block after every step
-            tile_sort_registers<4, 1024>(keys + r.x, n, skeys, point_list + r.x, keys_sorted != nullptr ? keys_sorted + r.x : nullptr,
-                                         tile_hi, tid);
-        } else if (n <= SORT_LARGE) {
+        if (n <= SORT_MID) continue;   // block-uniform: tile_sort_mid_kernel's lists
+        if (n <= SORT_LARGE) {
             for (uint32_t k = tid; k < n; k += 1024) skeys[k] = keys[r.x + k];
             bitonic_sort_ascending(skeys, n, next_pow2(n), tid, 1024);
             for (uint32_t k = tid; k < n; k += 1024) {
@@ -415,6 +411,33 @@ tile_sort_large_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                 if (keys_sorted != nullptr) keys_sorted[r.x + k] = tile_hi | (key >> 32);
             }
         }
+        __syncthreads();   // skeys is reused by the next tile
+    }
+}
+
+// Buckets of SORT_SMALL + 1 .. SORT_MID keys -- the real GUAVA training size (P = 202 k) has lists of 2-3 k: the same
+// register-resident network as the small buckets, 512 threads x 8 keys (the steps at distance >= 256 go through shared
+// memory).  A kernel of its own with 32 KB of static shared memory and 48 registers, so that two to three CTAs fit an
+// SM: inside the long-bucket kernel (128 KB of dynamic shared memory, one 1024-thread CTA per SM) these sorts took
+// 0.040 ms of the P = 202 k step.  The tile
+// order lists the tiles longest first in bins of 8 keys, every list of 2040 keys or more in the first bin: the CTAs
+// stride over that head of the order and stop at the first shorter list.
+__global__ void __launch_bounds__(512)
+tile_sort_mid_kernel(const uint4* __restrict__ tile_order, const uint32_t* __restrict__ num_rendered,
+                     const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                     uint64_t* __restrict__ keys_sorted, int tiles_per_view, int total_tiles)
+{
+    __shared__ uint64_t skeys[SORT_MID];
+    if (num_rendered[1] || num_rendered[4] <= SORT_SMALL) return;
+    const int tid = threadIdx.x;
+    for (int w = blockIdx.x; w < total_tiles; w += gridDim.x) {
+        const uint4 item = tile_order[w];
+        const uint32_t n = item.z - item.y;
+        if (n < 2040u) break;                          // block-uniform: the rest of the order is shorter
+        if (n <= SORT_SMALL || n > SORT_MID) continue;   // block-uniform: the small / long-bucket kernels' lists
+        const uint64_t tile_hi = (uint64_t)(item.x % (uint32_t)tiles_per_view) << 32;
+        tile_sort_registers<8, 512>(keys + item.y, n, skeys, point_list + item.y,
+                                     keys_sorted != nullptr ? keys_sorted + item.y : nullptr, tile_hi, tid);
         __syncthreads();   // skeys is reused by the next tile
     }
 }
@@ -439,6 +462,10 @@ void launch_tile_sort(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img,
                                                        b.keys_sorted, in.tiles);
     count_launch();
     if (!with_large) return;
+    const int mid_grid = total_tiles < 3 * sm_count() ? total_tiles : 3 * sm_count();
+    tile_sort_mid_kernel<<<mid_grid, 512, 0, s>>>(img.tile_order, img.num_rendered, b.keys_unsorted, b.point_list,
+                                                   b.keys_sorted, in.tiles, total_tiles);
+    count_launch();
     const int big_grid = total_tiles < sm_count() ? total_tiles : sm_count();
     tile_sort_large_kernel<<<big_grid, 1024, SORT_LARGE * sizeof(uint64_t), s>>>(
         img.ranges, img.num_rendered, b.keys_unsorted, b.point_list, b.keys_sorted, in.tiles, total_tiles);
