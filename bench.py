@@ -12,6 +12,11 @@ Workloads (config.workload), all synthetic (guava_renderer_b200/synthetic.py, SU
       N > 1 by one NCCL all-reduce(sum) of the packed per-Gaussian gradients [P,43] fp32.
   C2  -- inference shape: 8 views x 100k Gaussians, 512x512, forward only, one launch chain (N = 1;
       for N > 1 every rank renders its own 8 views: weak).
+  C3pose -- the C3 step driven the way GUAVA drives it (N = 1 only; a second, clearly labelled end-to-end line, the
+      headline stays C3): the avatar's per-Gaussian attributes are resident, what reaches the device every step is the
+      POSE -- deformed mesh vertices [V,Nv,3] and per-vertex transforms [V,Nv,4,4], 1.6 MB -- and the step is
+      deformation (models/UbodyAvatar/ubody_gaussian.py:245-289) -> rasterizer forward -> loss -> rasterizer
+      backward -> deformation backward, gradients landing on the avatar attributes.
   C4  -- cross-reenactment video: 300k Gaussians, 1024x1024, 240 frames, forward only, frames split
       contiguously over the N ranks (strong scaling: the job is the 240 frames); the cloud is resident,
       each frame has its own positions (base + 0.02 sin(2 pi f/240 + phi_i)); no cross-GPU traffic.
@@ -50,6 +55,7 @@ WORKLOADS = {
     "C3": dict(P=100_000, H=512, W=512, views=2, backward=True, scaling="weak", config_id=3),
     "C2": dict(P=100_000, H=512, W=512, views=8, backward=False, scaling="weak", config_id=2),
     "C4": dict(P=300_000, H=1024, W=1024, views=240, backward=False, scaling="strong", config_id=4),
+    "C3pose": dict(P=100_000, H=512, W=512, views=2, backward=True, scaling="weak", config_id=3),
 }
 C4_CHUNK = 8      # frames per launch chain
 
@@ -204,6 +210,10 @@ def workload_name(args):
     if args.workload == "C3":
         return (f"C3 GUAVA training step: {args.P // 1000}k-Gaussian 32-ch avatar, {args.H}x{args.W}, fwd+bwd, "
                 f"{args.views_per_gpu} views/GPU/step (16 views over 8 GPUs), NCCL all-reduce of [P,43] grads for N>1")
+    if args.workload == "C3pose":
+        return (f"C3pose GUAVA training step from the pose: {args.P // 1000}k-Gaussian avatar resident (10458 vertex + "
+                f"{args.P - 10458} face-bound Gaussians), per step {args.views_per_gpu} posed meshes host->device, deformation + "
+                f"rasterizer fwd+bwd + deformation bwd, {args.H}x{args.W}")
     if args.workload == "C2":
         return (f"C2 GUAVA inference: {args.P // 1000}k-Gaussian 32-ch avatar, {args.H}x{args.W}, forward only, "
                 f"{args.views_per_gpu} views batched per GPU and step")
@@ -239,6 +249,8 @@ def run_own(args, rank, world, device):
     from guava_renderer_b200 import sharding
     import torch.distributed as dist
 
+    if args.workload == "C3pose":
+        return run_own_pose(args, rank, world, device)
     if args.workload != "C3":
         return run_own_forward_only(args, rank, world, device)
 
@@ -492,6 +504,143 @@ def run_own(args, rank, world, device):
                 h2d=h2d_bytes, d2h=d2h_bytes, wall_ms_e2e=t_wall, enqueue_ms_e2e=t_enq, ms_h2d_alone=ms_h2d_alone,
                 ms_h2d_loaded=ms_h2d_loaded,
                 step_call="eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)")
+
+
+ATTR_KEYS = ("smplx_rotation", "smplx_scaling", "smplx_opacity", "smplx_features_color",
+             "uv_local_xyz", "uv_rotation", "uv_scaling", "uv_opacity", "uv_features_color")
+POSE_SETS = 4
+
+
+def build_pose_inputs(P, V, H, W, pin):
+    """The resident avatar, POSE_SETS posed meshes (one packed block each: vertices [V,Nv,3] then transforms
+    [V,Nv,16]) and the V cameras of the C3 orbit."""
+    synthetic = load_synthetic()
+    av = synthetic.pose_avatar(P, V, seed=3100)
+    Nv = av["vertices"].shape[0]
+    poses = []
+    for i in range(POSE_SETS):
+        pv, pt = synthetic.pose_of(av["vertices"], i, V)
+        blk = torch.cat([pv.reshape(-1), pt.reshape(-1)])
+        poses.append(blk.pin_memory() if pin else blk)
+    cams = [synthetic.camera(v, 16, 1.0 / 24 * W / H, 1.0 / 24) for v in range(V)]
+    return av, Nv, poses, cams
+
+
+def run_own_pose(args, rank, world, device):
+    """C3pose: pose in, gradients on the avatar attributes out.  The whole step -- deform_gaussians, rasterizer
+    forward, loss, rasterizer backward, deformation backward, gradient packing -- is one captured CUDA graph per
+    staging buffer (GraphedRenderStep with a producer)."""
+    import guava_renderer_b200 as grb
+    if world != 1:
+        raise SystemExit("--workload C3pose is a single-GPU line")
+    P, H, W, V = args.P, args.H, args.W, args.views_per_gpu
+    clocks = ClockSampler(smi_index(device.index))
+    av, Nv, poses_host, cams = build_pose_inputs(P, V, H, W, pin=True)
+    N = P - Nv
+    dL = upstream(V, H, W, device)
+    tanfov = torch.tensor([[cams[0]["tanfovx"], cams[0]["tanfovy"]]] * V, device=device)
+    bg = torch.zeros(V, 32, device=device)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, bg, 1.0, torch.stack([c["viewmatrix"] for c in cams]).to(device),
+                                        torch.stack([c["projmatrix"] for c in cams]).to(device))
+    mesh = {k: av[k].to(device) for k in ("faces", "uv_binding_face", "uv_face_bary")}
+    attrs = {k: av[k].to(device) for k in ATTR_KEYS}
+
+    class Producer:
+        """deform_gaussians on the posed mesh in `buf`; fresh attribute leaves per call (see GraphedRenderStep)."""
+        def __init__(self, buf):
+            self.vertices = buf[:V * Nv * 3].view(V, Nv, 3)
+            self.transforms = buf[V * Nv * 3:].view(V, Nv, 4, 4)
+            self.leaves = {}
+
+        def __call__(self):
+            self.leaves = {k: t.detach().requires_grad_(torch.is_grad_enabled()) for k, t in attrs.items()}
+            out = grb.deform_gaussians(self.vertices, self.transforms, mesh["faces"], mesh["uv_binding_face"],
+                                       mesh["uv_face_bary"], **self.leaves)
+            return dict(xyz=out["xyz"], features=out["features_color"], opacity=out["opacity"], scaling=out["scaling"],
+                        rotation=out["rotation"])
+
+    NSTAGE = 3
+    stage = []
+    for i in range(NSTAGE):
+        buf = torch.empty(V * Nv * 19, device=device)
+        buf.copy_(poses_host[i % POSE_SETS])
+        prod = Producer(buf)
+        stage.append(dict(buf=buf, prod=prod, ev=torch.cuda.Event(), done=torch.cuda.Event(), fin=torch.cuda.Event(),
+                          step=grb.GraphedRenderStep(None, None, None, None, None, st, dL_dcolor=dL, producer=prod)))
+    copy_stream = torch.cuda.Stream(device=device)
+    result_stream = torch.cuda.Stream(device=device)     # the step's result is reduced and read back beside the next step
+    result_host = torch.empty(3, dtype=torch.float32).pin_memory()
+    h2d_bytes, d2h_bytes = V * Nv * 19 * 4, 12
+
+    def prefetch(i):
+        b = stage[i % NSTAGE]
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_stream(torch.cuda.current_stream(device))
+            b["buf"].copy_(poses_host[i % POSE_SETS], non_blocking=True)
+            b["ev"].record(copy_stream)
+
+    def step(i, host_inputs):
+        b = stage[i % NSTAGE]
+        if host_inputs:
+            torch.cuda.current_stream(device).wait_event(b["ev"])
+        g = b["step"]
+        compute = torch.cuda.current_stream(device)
+        if host_inputs:
+            compute.wait_event(b["fin"])      # the result of the step that last used these buffers has been read
+        g.replay()
+        if host_inputs:   # the step's result: loss, |d/d(rasterizer inputs)|_1, |d/d(uv_local_xyz)|_1 -> pinned host memory
+            b["done"].record(compute)
+            with torch.cuda.stream(result_stream):
+                result_stream.wait_event(b["done"])
+                res = torch.stack([g.loss, torch.linalg.vector_norm(g.packed.view(-1), 1),
+                                   torch.linalg.vector_norm(b["prod"].leaves["uv_local_xyz"].grad.view(-1), 1)])
+                result_host.copy_(res, non_blocking=True)
+                b["fin"].record(result_stream)
+
+    out = {}
+    for name, host_inputs in (("res", False), ("e2e", True)):
+        if host_inputs:
+            prefetch(0); prefetch(1)
+        for i in range(args.warmup):
+            if host_inputs:
+                prefetch(i + 2)
+            step(i, host_inputs)
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks.begin()
+        e0.record()
+        for i in range(args.steps):
+            if host_inputs:
+                prefetch(args.warmup + i + 2)
+            step(args.warmup + i, host_inputs)
+        torch.cuda.current_stream(device).wait_stream(result_stream)   # the last result has reached the host
+        e1.record()
+        torch.cuda.synchronize(device)
+        clocks.end()
+        out[name] = e0.elapsed_time(e1)
+    vals = [float(x) for x in result_host]
+    for b in stage:
+        b["step"].check()
+    assert all(np.isfinite(vals)) and vals[1] > 0 and vals[2] > 0, vals
+    # roofline object: the rasterizer's kernels on one deformed input set (eager, per-stage events)
+    with torch.no_grad():
+        d = stage[0]["prod"]()
+    prof = dict(xyz=d["xyz"], feat=d["features"], op=d["opacity"], sc=d["scaling"], rot=d["rotation"], vm=st.viewmatrix,
+                pm=st.projmatrix)
+    grb.set_option("profile_stages", 1)
+    grb._lib_mod.stage_times_reset()
+    for _ in range(3):
+        leaves = [prof[k].detach().requires_grad_(True) for k in ("xyz", "feat", "op", "sc", "rot")]
+        m2 = torch.zeros(V, P, 3, device=device, requires_grad=True)
+        color, _, _ = grb.rasterize_gaussians_batch(leaves[0], m2, leaves[1], leaves[2], leaves[3], leaves[4], st)
+        color.backward(dL)
+    torch.cuda.synchronize(device)
+    grb.set_option("profile_stages", 0)
+    roof = roofline_object(grb._lib_mod.stage_times(), prof, tanfov, bg, P, H, W, V, device, backward=True)
+    return dict(ms_res=out["res"], ms_e2e=out["e2e"], pix=V * H * W * args.steps,
+                launches=int(stage[0]["step"].launches_per_replay * args.steps), clocks=clocks.result(), roofline=roof,
+                h2d=h2d_bytes, d2h=d2h_bytes,
+                step_call="guava_renderer_b200.GraphedRenderStep with producer=deform_gaussians (CUDA graph replay)")
 
 
 def run_own_forward_only(args, rank, world, device):
@@ -816,6 +965,49 @@ def run_reference(args, rank, world, local_rank):
                             acc.add_(img.view(-1)[::4099].sum())
             if host_inputs:
                 result_host[:1].copy_(acc, non_blocking=True)
+    elif args.workload == "C3pose":
+        # the reference's own path for this step: Ubody_Gaussian.forward (ubody_gaussian.py:245-289) as eager torch ops
+        # on the GPU -- its line-by-line restatement oracle/deform_oracle.py, the module itself needs pytorch3d / roma --
+        # then the per-view loop over the unmodified rasterizer build, backward through both
+        if world != 1:
+            raise SystemExit("--workload C3pose is a single-GPU line")
+        from oracle import deform_oracle
+        V = args.views_per_gpu
+        av, Nv, poses_host, cams = build_pose_inputs(P, V, H, W, pin=True)
+        dL = upstream(V, H, W, device)
+        mesh = {k: av[k].to(device) for k in ("faces", "uv_binding_face", "uv_face_bary")}
+        attrs = {k: av[k].to(device) for k in ATTR_KEYS}
+        pose_dev = [poses_host[i % POSE_SETS].to(device) for i in range(2)]
+        cam_dev = [{k: (c[k].to(device) if torch.is_tensor(c[k]) else c[k]) for k in c} for c in cams]
+        result_host = torch.empty(3, dtype=torch.float32).pin_memory()
+        h2d, d2h = V * Nv * 19 * 4, 12
+
+        def step(i, host_inputs):
+            buf = pose_dev[i % 2]
+            if host_inputs:
+                buf.copy_(poses_host[i % POSE_SETS], non_blocking=True)
+            leaves = {k: t.detach().requires_grad_(True) for k, t in attrs.items()}
+            d = deform_oracle.deform(buf[:V * Nv * 3].view(V, Nv, 3), buf[V * Nv * 3:].view(V, Nv, 4, 4), mesh["faces"],
+                                     mesh["uv_binding_face"], mesh["uv_face_bary"], **leaves)
+            mean_2d = torch.zeros(V, P, 3, device=device, requires_grad=True)
+            imgs = []
+            for bi in range(V):          # gaussian_render.py:37-67
+                c = cam_dev[bi]
+                rs = ref.GaussianRasterizationSettings(
+                    image_height=H, image_width=W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=bgv, scale_modifier=1.0,
+                    viewmatrix=c["viewmatrix"], projmatrix=c["projmatrix"], sh_degree=0, campos=c["campos"],
+                    prefiltered=False, debug=False, antialiasing=False)
+                img, radii, depth = ref.GaussianRasterizer_32(raster_settings=rs)(
+                    means3D=d["xyz"][bi], means2D=mean_2d[bi], shs=None, colors_precomp=d["features_color"][bi],
+                    opacities=d["opacity"][bi], scales=d["scaling"][bi], rotations=d["rotation"][bi], cov3D_precomp=None)
+                imgs.append(img)
+            color = torch.stack(imgs, 0)
+            loss = torch.dot(color.detach().view(-1), dL.view(-1))
+            color.backward(dL)
+            if host_inputs:
+                res = torch.stack([loss, sum(torch.linalg.vector_norm(leaves[k].grad.view(-1), 1) for k in ATTR_KEYS),
+                                   torch.linalg.vector_norm(leaves["uv_local_xyz"].grad.view(-1), 1)])
+                result_host.copy_(res, non_blocking=True)
     else:
         V = args.views_per_gpu
         views = shard_views(V * world, rank, world)
@@ -869,7 +1061,7 @@ def run_reference(args, rank, world, local_rank):
 
     out = {}
     for name, host_inputs in (("resident", False), ("e2e", True)):
-        if args.workload != "C4":
+        if args.workload not in ("C4", "C3pose"):
             for i in range(2):   # both staging buffers hold data for the resident pass
                 for k in TENSOR_KEYS + ("cams",):
                     stage[i][k].copy_(sets_host[i % len(sets_host)][k])

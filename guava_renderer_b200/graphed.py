@@ -53,15 +53,26 @@ class GraphedRenderStep:
         .loss                            scalar tensor (training mode)
         .grads                           dict xyz / scaling / rotation / opacity / features (per view)
         .packed                          [P,43] sum over views, the all-reduce payload (sharding.py)
+    `producer` (instead of the five tensors, pass None for them): a callable that computes the rasterizer's inputs
+    inside the captured step from its own static tensors -- e.g. `deform_gaussians` on a posed mesh (the step before
+    the rasterizer in GUAVA, ubody_gaussian.py:245-289) -- and returns them as a dict xyz / features / opacity /
+    scaling / rotation.  In training mode the backward then runs on through the producer's autograd graph into ITS
+    leaves, which it must create afresh on every call (`t.detach().requires_grad_(True)`: a captured backward assigns
+    `.grad`, it must not accumulate into a tensor left over from the warm-up runs).
     """
 
     def __init__(self, means3D, colors_precomp, opacities, scales, rotations, settings: BatchRasterizationSettings,
                  dL_dcolor: Optional[torch.Tensor] = None,
                  loss_fn: Optional[Callable[[torch.Tensor, torch.Tensor], torch.Tensor]] = None,
-                 packed_out: Optional[torch.Tensor] = None, warmup: int = 2):
+                 packed_out: Optional[torch.Tensor] = None, warmup: int = 2,
+                 producer: Optional[Callable[[], Dict[str, torch.Tensor]]] = None):
+        self.producer = producer
+        if producer is not None:
+            means3D = settings.viewmatrix       # device only
         if not means3D.is_cuda:
             raise RuntimeError("GraphedRenderStep needs CUDA tensors (there is no CPU path)")
-        self.inputs = dict(xyz=means3D, features=colors_precomp, opacity=opacities, scaling=scales, rotation=rotations)
+        self.inputs = None if producer is not None else dict(xyz=means3D, features=colors_precomp, opacity=opacities,
+                                                             scaling=scales, rotation=rotations)
         self.settings = settings
         self.dL_dcolor = dL_dcolor
         self.loss_fn = loss_fn
@@ -73,10 +84,7 @@ class GraphedRenderStep:
         # (num_rendered, longest list | overflow << 31) of the latest replay: the tile scan stores them
         # straight into these pinned words (guava_call_options::status_words) -- no copy node in the graph
         self._status = torch.zeros(2, dtype=torch.int32).pin_memory()
-        V = int(settings.viewmatrix.shape[0])
-        P = int(means3D.shape[-2])
         # means2D is a gradient sink whose values no kernel reads (gaussian_render.py:30-33): never filled
-        self._m2_shape = (V, P, 3)
         self._side = torch.cuda.Stream(device=self.device)
         self._loss_buf = torch.zeros(64, device=self.device)      # guava_image_dot: [0] value, rest scratch
         self.graph = torch.cuda.CUDAGraph()
@@ -98,14 +106,20 @@ class GraphedRenderStep:
 
     # one step, eager or under capture
     def _step(self, no_host_wait: bool = False):
-        i = self.inputs
         V = int(self.settings.viewmatrix.shape[0])
-        P = int(i["xyz"].shape[-2])
-        if self.training:
-            leaf = {k: v.detach().requires_grad_(True) for k, v in i.items()}
+        if self.producer is not None:
+            with torch.set_grad_enabled(self.training):
+                leaf = self.producer()
+            if self.training:
+                for v in leaf.values():
+                    if v.requires_grad and not v.is_leaf:
+                        v.retain_grad()      # the rasterizer-input gradients feed .grads / .packed
+        elif self.training:
+            leaf = {k: v.detach().requires_grad_(True) for k, v in self.inputs.items()}
         else:
-            leaf = i
-        m2 = torch.empty(self._m2_shape, device=self.device, requires_grad=self.training)
+            leaf = self.inputs
+        P = int(leaf["xyz"].shape[-2])
+        m2 = torch.empty((V, P, 3), device=self.device, requires_grad=self.training)
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
                                                            leaf["scaling"], leaf["rotation"], self.settings,

@@ -127,3 +127,74 @@ def make_views(config_id: int, P: int, H: int, W: int, views: List[int], num_vie
     out["tanfovy"] = tanfovy
     out["H"], out["W"] = H, W
     return out
+
+
+# ----------------------------------------------------------------------------- pose-driven avatar
+def pose_avatar(P: int, V: int, seed: int, rows: int = 83, cols: int = 126) -> Dict[str, torch.Tensor]:
+    """A GUAVA-shaped avatar for the pose-driven workload (what models/UbodyAvatar/ubody_gaussian.py:245-289 takes):
+    a lat-long triangle mesh of the cloud's ellipsoid shell -- rows*cols = 10 458 vertices and 2*(rows-1)*cols =
+    20 664 faces with the defaults, SMPL-X has 10 475 / 20 908 -- one Gaussian per vertex and N = P - Nv Gaussians bound
+    to random faces with barycentric coordinates and a local offset, per-view attribute sets [V, ...] (the reference's
+    batch dimension).  World-space sizes follow guava_cloud (s0 = 0.0054 sqrt(1e5 / P))."""
+    g = torch.Generator().manual_seed(int(seed))
+    Nv = rows * cols
+    N = P - Nv
+    if N < 0:
+        raise ValueError("P must be at least rows * cols")
+    th = torch.linspace(0.04, math.pi - 0.04, rows)[:, None].expand(rows, cols)
+    ph = (torch.arange(cols, dtype=torch.float32) * (2.0 * math.pi / cols))[None, :].expand(rows, cols)
+    radii = torch.tensor([0.55, 0.75, 0.25])
+    verts = torch.stack([torch.sin(th) * torch.cos(ph), torch.cos(th), torch.sin(th) * torch.sin(ph)], -1).reshape(Nv, 3) * radii
+    r = torch.arange(rows - 1)[:, None]
+    c = torch.arange(cols)[None, :]
+    v00, v10 = r * cols + c, (r + 1) * cols + c
+    v01, v11 = r * cols + (c + 1) % cols, (r + 1) * cols + (c + 1) % cols
+    faces = torch.cat([torch.stack([v00, v10, v01], -1).reshape(-1, 3), torch.stack([v01, v10, v11], -1).reshape(-1, 3)], 0)
+    F = faces.shape[0]
+    face_size = 0.5 * (2.0 * math.pi * 0.55 / cols + math.pi * 0.75 / rows)      # typical (edge + height) / 2 of a face
+    s0 = 0.0054 * math.sqrt(1e5 / P)
+    rn = lambda *s: torch.randn(*s, generator=g)
+    unit = lambda x: x / x.norm(dim=-1, keepdim=True).clamp_min(1e-12)
+    bary = torch.rand(N, 3, generator=g)
+    bary = bary / bary.sum(-1, keepdim=True)
+    # faces shrink towards the poles: bind in proportion to face area (uniform over the surface) and size the bound
+    # Gaussians by their face's own scale (utils/graphics_utils.py:61-80: s = (|e0| + |a2 . e1|) / 2), so that world
+    # sizes and tile-list lengths are those of guava_cloud
+    e0, e1 = verts[faces[:, 1]] - verts[faces[:, 0]], verts[faces[:, 2]] - verts[faces[:, 0]]
+    a0 = unit(e0)
+    a1 = unit(torch.linalg.cross(a0, e1))
+    a2 = -unit(torch.linalg.cross(a1, a0))
+    s_face = 0.5 * (e0.norm(dim=-1) + (a2 * e1).sum(-1).abs())
+    area = 0.5 * torch.linalg.cross(e0, e1).norm(dim=-1)
+    binding = torch.multinomial(area / area.sum(), N, replacement=True, generator=g) if N else torch.zeros(0, dtype=torch.long)
+    inv_s = (1.0 / s_face[binding].clamp_min(1e-4))[None, :, None]
+
+    def feats(n):
+        f = rn(V, n, NUM_CHANNELS)
+        f[..., :3] = torch.sigmoid(f[..., :3])
+        return f
+
+    opac = lambda n: torch.sigmoid(1.0 + 2.0 * rn(V, n, 1)).clamp(0.002, 0.999)
+    return dict(
+        vertices=verts.float().contiguous(), faces=faces.int().contiguous(),
+        uv_binding_face=binding.int().contiguous(), uv_face_bary=bary.float().contiguous(),
+        smplx_rotation=unit(rn(V, Nv, 4)), smplx_scaling=s0 * torch.exp(0.4 * rn(V, Nv, 3)), smplx_opacity=opac(Nv),
+        smplx_features_color=feats(Nv), uv_local_xyz=(0.3 * face_size) * rn(V, N, 3) * inv_s, uv_rotation=unit(rn(V, N, 4)),
+        uv_scaling=s0 * torch.exp(0.4 * rn(V, N, 3)) * inv_s, uv_opacity=opac(N), uv_features_color=feats(N))
+
+
+def pose_of(vertices: torch.Tensor, step: int, V: int):
+    """Posed mesh of `step` for V views: a rigid sway of the rest mesh (rotation about y, small translation) -- the
+    per-step data GUAVA moves to the device: vertices [V,Nv,3] and per-vertex transforms [V,Nv,4,4]."""
+    Nv = vertices.shape[0]
+    outv, outt = [], []
+    for v in range(V):
+        a = 0.2 * math.sin(0.37 * step + 1.3 * v)
+        R = torch.tensor([[math.cos(a), 0.0, math.sin(a)], [0.0, 1.0, 0.0], [-math.sin(a), 0.0, math.cos(a)]])
+        t = torch.tensor([0.02 * math.sin(0.11 * step + v), 0.015 * math.cos(0.23 * step), 0.0])
+        T = torch.eye(4)
+        T[:3, :3] = R
+        T[:3, 3] = t
+        outv.append(vertices @ R.T + t)
+        outt.append(T[None].expand(Nv, 4, 4))
+    return torch.stack(outv, 0).float().contiguous(), torch.stack(outt, 0).float().contiguous()

@@ -43,11 +43,11 @@ def rotmat_to_unitquat(R):
     shape = R.shape[:-2]
     m = R.reshape(-1, 3, 3)
     n = m.shape[0]
-    dec = torch.empty((n, 4), dtype=m.dtype)
+    dec = torch.empty((n, 4), dtype=m.dtype, device=m.device)
     dec[:, :3] = m.diagonal(dim1=1, dim2=2)
     dec[:, 3] = dec[:, :3].sum(dim=1)
     choices = dec.argmax(dim=1)
-    quat = torch.empty((n, 4), dtype=m.dtype)
+    quat = torch.empty((n, 4), dtype=m.dtype, device=m.device)
     ind = torch.nonzero(choices != 3, as_tuple=True)[0]
     i = choices[ind]
     j = (i + 1) % 3

@@ -89,3 +89,60 @@ def test_deform_kernels_against_golden_from_the_reference_source():
         if k == "rotation":   # q and -q are the same rotation
             o = o * torch.sign((o * r).sum(-1, keepdim=True))
         assert float((o - r).abs().max()) <= 1e-5 * max(1.0, float(r.abs().max())), k
+
+
+def test_graphed_step_with_a_deformation_producer_equals_the_eager_chain():
+    """GraphedRenderStep(producer=...): deform_gaussians -> rasterizer forward -> loss -> rasterizer backward ->
+    deformation backward captured as one graph and replayed == the same chain run eagerly (image bit for bit,
+    gradients on the avatar attributes to atomic-order tolerance); a second replay after the posed mesh changed
+    in place follows the new pose."""
+    import guava_renderer_b200 as grb
+    from guava_renderer_b200 import synthetic
+    from tests import util
+    dev = "cuda:0"
+    V, P, H, W = 2, 14000, 96, 128
+    av = synthetic.pose_avatar(P, V, seed=9, rows=40, cols=60)
+    Nv = av["vertices"].shape[0]
+    mesh = ("faces", "uv_binding_face", "uv_face_bary")
+    g = {k: av[k].to(dev) for k in mesh + LEAVES}
+    cams = [synthetic.camera(v, 16, 1.0 / 24 * W / H, 1.0 / 24) for v in range(V)]
+    tanfov = torch.tensor([[c["tanfovx"], c["tanfovy"]] for c in cams], device=dev)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=dev), 1.0,
+                                        torch.stack([c["viewmatrix"] for c in cams]).to(dev),
+                                        torch.stack([c["projmatrix"] for c in cams]).to(dev))
+    gen = torch.Generator().manual_seed(3)
+    dL = torch.randn(V, 32, H, W, generator=gen).to(dev)
+    pv, pt = synthetic.pose_of(av["vertices"], 0, V)
+    verts, xf = pv.to(dev), pt.to(dev)
+
+    class Producer:
+        def __call__(self):
+            self.leaves = {k: g[k].detach().requires_grad_(torch.is_grad_enabled()) for k in LEAVES}
+            o = grb.deform_gaussians(verts, xf, g["faces"], g["uv_binding_face"], g["uv_face_bary"], **self.leaves)
+            return dict(xyz=o["xyz"], features=o["features_color"], opacity=o["opacity"], scaling=o["scaling"],
+                        rotation=o["rotation"])
+
+    def eager():
+        p = Producer()
+        d = p()
+        m2 = torch.zeros(V, P, 3, device=dev, requires_grad=True)
+        color, radii, invd = grb.rasterize_gaussians_batch(d["xyz"], m2, d["features"], d["opacity"], d["scaling"], d["rotation"], st)
+        color.backward(dL)
+        torch.cuda.synchronize()
+        return color.detach().clone(), {k: v.grad.clone() for k, v in p.leaves.items()}
+
+    prod = Producer()
+    step = grb.GraphedRenderStep(None, None, None, None, None, st, dL_dcolor=dL, producer=prod)
+    for pose in (0, 5):
+        pv, pt = synthetic.pose_of(av["vertices"], pose, V)
+        verts.copy_(pv.to(dev)); xf.copy_(pt.to(dev))
+        step.replay()
+        step.check()
+        want_color, want = eager()
+        assert torch.equal(step.color.detach(), want_color)
+        assert float(want_color.abs().sum()) > 0
+        for k in LEAVES:
+            got = prod.leaves[k].grad
+            assert got is not None, k
+            assert util.rel_err(got.cpu().numpy(), want[k].cpu().numpy()) <= 5e-5, k
+        assert step.packed.shape == (P, 43) and float(step.packed.abs().sum()) > 0

@@ -183,3 +183,29 @@ def test_compiled_torch_binding_is_built_and_exports_the_reference_entry_points(
             assert callable(getattr(grb._C, name)), name
     import diff_gaussian_rasterization_32 as dgr
     assert dgr._C is grb._C
+
+
+def test_pose_avatar_is_well_formed_and_renders_like_the_benchmark_cloud():
+    """synthetic.pose_avatar / pose_of (bench.py --workload C3pose): index ranges, unit quaternions, and -- deformed
+    by the CPU restatement of ubody_gaussian.py:245-289 -- world-space sizes of the benchmark cloud."""
+    from guava_renderer_b200 import synthetic
+    from oracle import deform_oracle as do
+    V, P = 2, 9000
+    av = synthetic.pose_avatar(P, V, seed=4, rows=30, cols=40)
+    Nv, F = av["vertices"].shape[0], av["faces"].shape[0]
+    assert Nv == 1200 and F == 2 * 29 * 40 and av["uv_binding_face"].shape == (P - Nv,)
+    assert int(av["faces"].max()) < Nv and int(av["faces"].min()) >= 0
+    assert int(av["uv_binding_face"].max()) < F and int(av["uv_binding_face"].min()) >= 0
+    assert torch.allclose(av["uv_face_bary"].sum(-1), torch.ones(P - Nv), atol=1e-6)
+    assert torch.allclose(av["uv_rotation"].norm(dim=-1), torch.ones(V, P - Nv), atol=1e-5)
+    pv, pt = synthetic.pose_of(av["vertices"], 3, V)
+    assert pv.shape == (V, Nv, 3) and pt.shape == (V, Nv, 4, 4)
+    R = pt[0, 0, :3, :3]
+    assert torch.allclose(R @ R.T, torch.eye(3), atol=1e-6)
+    out = do.deform(pv, pt, av["faces"], av["uv_binding_face"], av["uv_face_bary"], **{k: av[k] for k in (
+        "smplx_rotation", "smplx_scaling", "smplx_opacity", "smplx_features_color", "uv_local_xyz", "uv_rotation",
+        "uv_scaling", "uv_opacity", "uv_features_color")})
+    assert out["xyz"].shape == (V, P, 3) and torch.isfinite(out["xyz"]).all()
+    s0 = 0.0054 * (1e5 / P) ** 0.5
+    assert 0.8 * s0 < float(out["scaling"][:, Nv:].median()) < 1.25 * s0          # face-bound Gaussians keep the target size
+    assert torch.allclose(out["rotation"].norm(dim=-1), torch.ones(V, P), atol=1e-4)
