@@ -910,3 +910,29 @@ def test_taken_masks_option_may_change_between_forward_and_backward(fwd_opt, bwd
         grb.set_option("taken_masks", base)
     for k, v in leaf.items():
         assert util.rel_err(v.grad.cpu().numpy(), want[k]) <= 5e-5, k
+
+
+@pytest.mark.parametrize("how", ["rerun_after_overflow", "exact_binning"])
+def test_backward_after_the_binning_buffer_was_resized(how):
+    """The backward finds the forward's taken marks behind point_list from the capacity the call's header records:
+    gradients after a forward whose binning buffer was re-sized (estimate too small -> tail re-enqueued with the exact
+    size; or the reference's wait-then-allocate order) equal those of a forward with ample capacity."""
+    case = CASES[1]
+    inp = util.inputs_for(**case)
+    inp["bg"] = torch.linspace(-1, 1, 32)
+    g = torch.Generator().manual_seed(9)
+    dL = torch.randn(32, case["H"], case["W"], generator=g)
+    dLi = torch.randn(1, case["H"], case["W"], generator=g)
+    c0, want = _run_autograd(ours, inp, dL, dLi)
+    try:
+        if how == "exact_binning":
+            grb.set_option("exact_binning", 1)
+        else:
+            grb.set_option("capacity_hint", 512)
+        c1, got = _run_autograd(ours, inp, dL, dLi)
+    finally:
+        grb.set_option("exact_binning", 0)
+        grb.set_option("capacity_hint", CAP)
+    assert np.array_equal(c0, c1)
+    for k in want:
+        assert util.rel_err(got[k], want[k]) <= 5e-5, (k, util.rel_err(got[k], want[k]))

@@ -1,7 +1,7 @@
 # One GPU-box session: full GPU test suite, A/B of the compositor options, both bench arms, other workloads,
 # sort micro-benchmark, then the profiler passes on the default configuration.  Outputs under gpurun_out/$TAG.
 set -x
-TAG=${TAG:-r02_v6}
+TAG=${TAG:-r02_v10}
 O=gpurun_out/$TAG; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm --format=csv > $O/gpu.txt
 rm -f gpurun_out/grad_parity_stats.jsonl
@@ -18,6 +18,10 @@ GUAVA_OPT_TAKEN_MASKS=0 $B --P 202000 > $O/bench_202k_nomasks.json 2> $O/bench_2
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > $O/bench_ref.json 2> $O/bench_ref.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 --P 202000 --no-cpu-baseline > $O/bench_ref_202k.json 2> $O/bench_ref_202k.err
 timeout 200 python bench.py --steps 20 --warmup 5 > $O/bench_own_driverlike.json 2> $O/bench_own_driverlike.err
+timeout 300 python bench.py --workload C3pose --steps 100 --warmup 10 --no-cpu-baseline > $O/bench_pose.json 2> $O/bench_pose.err
+timeout 300 python bench.py --workload C3pose --impl reference --steps 20 --warmup 5 > $O/bench_pose_ref.json 2> $O/bench_pose_ref.err
+timeout 200 python bench.py --workload C2 --steps 20 --warmup 5 --no-cpu-baseline > $O/bench_c2.json 2> $O/bench_c2.err
+timeout 300 python bench.py --workload C4 --steps 3 --warmup 3 --no-cpu-baseline > $O/bench_c4.json 2> $O/bench_c4.err
 timeout 300 python tools/sort_vs_cub.py > $O/sort_vs_cub.jsonl 2> $O/sort_vs_cub.err
 timeout 300 python tools/bench_configs.py > $O/configs.jsonl 2> $O/configs.err
 tail -15 $O/pytest_gpu.log
