@@ -56,10 +56,11 @@ class Layout(Structure):
 class CallOptions(Structure):
     """guava_call_options (include/guava_rasterizer.h): per-call options of the batched entry."""
     _fields_ = [("struct_size", c_size_t), ("refiner_output_nhwc_bf16", c_void_p), ("status_words", c_void_p),
-                ("no_host_wait", c_int)]
+                ("no_host_wait", c_int), ("forward_only", c_int)]
 
-    def __init__(self, refiner_output=0, status_words=0, no_host_wait=False):
-        super().__init__(ctypes.sizeof(CallOptions), refiner_output or None, status_words or None, int(bool(no_host_wait)))
+    def __init__(self, refiner_output=0, status_words=0, no_host_wait=False, forward_only=False):
+        super().__init__(ctypes.sizeof(CallOptions), refiner_output or None, status_words or None, int(bool(no_host_wait)),
+                         int(bool(forward_only)))
 
 
 class GuavaLibraryError(RuntimeError):

@@ -364,7 +364,7 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     if (co != nullptr && co->struct_size != sizeof(guava_call_options))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "guava_call_options::struct_size does not match this library");
     in.aux_nhwc_bf16 = co ? co->refiner_output_nhwc_bf16 : nullptr;
-    const int block_masks = g_opt_taken_masks.load() != 0;
+    const int block_masks = g_opt_taken_masks.load() != 0 && !(co != nullptr && co->forward_only != 0);
     uint32_t* const status_host = co ? (uint32_t*)co->status_words : nullptr;
     if (((uintptr_t)status_host & 7) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");

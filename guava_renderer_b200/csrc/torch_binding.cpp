@@ -184,7 +184,7 @@ RasterizeGaussiansBatchCUDA(const torch::Tensor& background, const torch::Tensor
                             const float scale_modifier, const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
                             const torch::Tensor& tanfov, const int image_height, const int image_width, const bool antialiasing,
                             const bool debug, const c10::optional<torch::Tensor>& refiner_output, const int64_t status_words,
-                            const bool no_host_wait)
+                            const bool no_host_wait, const bool forward_only)
 {
     TORCH_CHECK(means3D.is_cuda(), "guava_renderer_b200: tensors must live on a CUDA device (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
@@ -209,6 +209,7 @@ RasterizeGaussiansBatchCUDA(const torch::Tensor& background, const torch::Tensor
     }
     co.status_words = reinterpret_cast<void*>(status_words);
     co.no_host_wait = no_host_wait ? 1 : 0;
+    co.forward_only = forward_only ? 1 : 0;
     if (V * P == 0) {
         out_color.zero_();
         out_invdepth.zero_();

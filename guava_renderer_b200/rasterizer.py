@@ -402,6 +402,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         aux = call.get("refiner_output")
         status = call.get("status_words")
         no_wait = bool(call.get("no_host_wait", False))
+        fwd_only = not any(ctx.needs_input_grad)      # no gradient can be asked for: inference
         m, c, o = _f32c(means3D), _f32c(colors_precomp), _f32c(opacities)
         s, r = _f32c(scales), _f32c(rotations)
         bg, vm, pm, tf = _f32c(st.bg), _f32c(st.viewmatrix), _f32c(st.projmatrix), _f32c(st.tanfov)
@@ -410,7 +411,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         if BINDING == "compiled":
             rendered, out_color, radii, geom, binning, img, out_invdepth = _C.rasterize_gaussians_batch(
                 bg, m, c, o, s, r, float(st.scale_modifier), vm, pm, tf, H, W, bool(st.antialiasing), bool(st.debug),
-                aux, status.data_ptr() if status is not None else 0, no_wait)
+                aux, status.data_ptr() if status is not None else 0, no_wait, fwd_only)
             bufs = [geom, binning, img]
         else:
             lib = _lib.load()
@@ -431,7 +432,8 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                     if V * P == 0:
                         aux.zero_()
                 copts = _lib.CallOptions(refiner_output=_ptr(aux) if aux is not None else 0,
-                                         status_words=status.data_ptr() if status is not None else 0, no_host_wait=no_wait)
+                                         status_words=status.data_ptr() if status is not None else 0, no_host_wait=no_wait,
+                                         forward_only=fwd_only)
                 rc = lib.guava_rasterizer_forward_batch(
                     _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
                     V, P, _ptr(bg), W, H,

@@ -162,6 +162,10 @@ typedef struct guava_call_options {
      * the sort that was launched) makes every later kernel of the forward AND of the backward skip
      * itself; it is visible in status_words[1] bit 31 / the image buffer's num_rendered[1]. */
     int no_host_wait;
+    /* 1: no backward call will follow this forward (inference): the forward compositor does not record its
+     * "taken" marks (option "taken_masks") and the binning buffer does not hold them -- 2 % of the forward and
+     * 8 bytes per instance saved.  A backward call after such a forward is still correct, only slower. */
+    int forward_only;
 } guava_call_options;
 
 /* Batched multi-view entry (replaces the per-view Python

@@ -936,3 +936,26 @@ def test_backward_after_the_binning_buffer_was_resized(how):
     assert np.array_equal(c0, c1)
     for k in want:
         assert util.rel_err(got[k], want[k]) <= 5e-5, (k, util.rel_err(got[k], want[k]))
+
+
+def test_inference_calls_of_the_batched_entry_record_no_taken_marks():
+    """guava_call_options::forward_only: a batched forward that no backward can follow (no input requires a gradient)
+    skips the marks and their 8 bytes per instance; the image is the same bit for bit."""
+    V, P, H, W = 2, 5000, 96, 112
+    views = [util.inputs_for(P, H, W, seed=700 + v, view=v, num_views=V, scale_mult=1.3) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    tanfov = torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.zeros(V, 32, device=DEV), 1.0, stack("viewmatrix"), stack("projmatrix"))
+    args = lambda rg: (stack("xyz").requires_grad_(rg), torch.zeros(V, P, 3, device=DEV), stack("features"), stack("opacity"),
+                       stack("scaling"), stack("rotation"), st)
+    grb.set_option("capacity_hint", 0)
+    out = {}
+    for rg in (False, True):
+        color, radii, invd = grb.rasterize_gaussians_batch(*args(rg))
+        torch.cuda.synchronize()
+        geom, binning, img = grb.rasterizer._tls.last_buffers
+        o = util.decode_ours(geom, binning, img, V, P, W, H)
+        out[rg] = (color.detach().clone(), o["block_masks"], binning.numel())
+    assert out[False][1] == 0 and out[True][1] == 1
+    assert out[False][2] < out[True][2]
+    assert torch.equal(out[False][0], out[True][0])
