@@ -86,8 +86,9 @@ __device__ __forceinline__ void warp_transpose_reduce8x2(float (&a)[8], float (&
 // NST: number of staging buffers.  2 = chunk c+1 is staged while chunk c is blended; 3 = chunk c+2 is (a chunk with
 // one or two survivors is blended in a few hundred cycles, less than the L2 round trip of the next chunk's rows: the
 // wait behind cp.async.wait_group held 7 % of the NST = 2 kernel's stall samples, profiles/r02_v6).
-template <int MASKS, int TMA, int INV, int NST>
-__global__ void __launch_bounds__(32, 12)
+// MINB: resident one-warp CTAs per SM the kernel is compiled for (register cap 65536 / (32 MINB)).
+template <int MASKS, int TMA, int INV, int NST, int MINB = 12>
+__global__ void __launch_bounds__(32, MINB)
 render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap, const SplatRec* __restrict__ recs,
                        const uint2* __restrict__ ranges, const uint4* __restrict__ tile_order,
                        const uint32_t* __restrict__ point_list, const uint8_t* __restrict__ taken_marks,
@@ -452,7 +453,8 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     memset(&fmap, 0, sizeof(fmap));
     if (tma_staging && !make_feature_tensor_map(in, &fmap)) tma_staging = 0;
     const long long total = (long long)in.tiles * 8 * in.V;
-    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : 12; }();   // tuning knob
+    static const int minb = [] { const char* e = getenv("GUAVA_BWD_MINB"); return e ? atoi(e) : 12; }();          // tuning knob: 12, 14 or 16
+    static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : minb; }();   // tuning knob
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
     // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
@@ -462,12 +464,26 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
                                                                b.taken_marks, img.final_T, img.n_contrib, dL_dpix,        \
                                                                dL_dinvdepth_pix, dL_dcolor, g.grad_geo, img.num_rendered)
 #define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1, 2); else GUAVA_LAUNCH_BWD2(MK, TM, 0, 2); } while (0)
-    if (taken_masks && !tma_staging && stages == 3) {   // the deeper pipeline exists for the default variant only
+#define GUAVA_LAUNCH_BWD_MINB(MB)                                                                                          \
+    do {                                                                                                                  \
+        if (dL_dinvdepth_pix != nullptr)                                                                                  \
+            render_backward_kernel<1, 0, 1, 2, MB><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order,       \
+                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo, \
+                img.num_rendered);                                                                                        \
+        else                                                                                                              \
+            render_backward_kernel<1, 0, 0, 2, MB><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order,       \
+                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo, \
+                img.num_rendered);                                                                                        \
+    } while (0)
+    if (taken_masks && !tma_staging && stages == 2 && minb == 14) GUAVA_LAUNCH_BWD_MINB(14);
+    else if (taken_masks && !tma_staging && stages == 2 && minb == 16) GUAVA_LAUNCH_BWD_MINB(16);
+    else if (taken_masks && !tma_staging && stages == 3) {   // the deeper pipeline exists for the default variant only
         if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(1, 0, 1, 3); else GUAVA_LAUNCH_BWD2(1, 0, 0, 3);
     } else if (taken_masks) { if (tma_staging) GUAVA_LAUNCH_BWD(1, 1); else GUAVA_LAUNCH_BWD(1, 0); }
     else             { if (tma_staging) GUAVA_LAUNCH_BWD(0, 1); else GUAVA_LAUNCH_BWD(0, 0); }
 #undef GUAVA_LAUNCH_BWD
 #undef GUAVA_LAUNCH_BWD2
+#undef GUAVA_LAUNCH_BWD_MINB
     cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();
 }
