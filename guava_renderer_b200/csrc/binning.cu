@@ -20,6 +20,7 @@
 // from 152 B (1 histogram + 6 onesweep passes over 12-byte pairs) to 8 B
 // written by the scatter + 8 B read and 4 B written by the tile sort.
 #include <atomic>
+#include <cstdlib>
 
 #include "internal.cuh"
 
@@ -158,9 +159,105 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     }
 }
 
+// The same results from ONE block when the frame has few tiles (up to 1024 * ITEMS: every GUAVA training shape --
+// 2 views of 512 x 512 are 2048 tiles): thread t owns ITEMS consecutive tiles, so the scan is a serial sum per thread
+// plus one block scan, and the work order is written from registers.  No ticket, no look-back, no "last block" election,
+// no second read of the ranges: one global round trip (the counters) instead of seven, 12 us -> 5 us per step.
+template <int ITEMS>
+__global__ void __launch_bounds__(1024)
+tile_scan_single_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges,
+                        uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
+                        uint32_t list_limit, uint32_t call_flags, uint4* __restrict__ tile_order)
+{
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t bins[256];
+    __shared__ uint32_t bin_base[256];
+    __shared__ uint32_t s_longest;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < 256) bins[tid] = 0u;
+    if (tid == 0) s_longest = 0u;
+    uint32_t c[ITEMS], sum = 0u, mx = 0u;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const int k = tid * ITEMS + i;
+        c[i] = k < n ? cursor[(size_t)k * CURSOR_STRIDE] : 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const int k = tid * ITEMS + i;
+        sum += c[i];
+        mx = max(mx, c[i]);
+        const uint32_t bin = k < n ? 255u - min(c[i] >> 3, 255u) : 256u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        if (lane == __ffs(peers) - 1 && bin < 256u) atomicAdd(&bins[bin], (uint32_t)__popc(peers));
+    }
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0 && wmax != 0u) atomicMax(&s_longest, wmax);
+    uint32_t R;
+    uint32_t run = block_exclusive_scan_1024(sum, warp_sums, tid, R);   // syncs: bins and s_longest complete
+    uint2 rg[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const int k = tid * ITEMS + i;
+        rg[i] = c[i] ? make_uint2(run, run + c[i]) : make_uint2(0u, 0u);   // untouched tiles keep (0,0)
+        if (k < n) {
+            ranges[k] = rg[i];
+            cursor[(size_t)k * CURSOR_STRIDE] = run;
+        }
+        run += c[i];
+    }
+    if (tid == 0) {
+        const uint32_t longest = s_longest;
+        const bool overflow = (unsigned long long)R > capacity || longest > list_limit;
+        num_rendered[0] = R;
+        num_rendered[1] = overflow ? 1u : 0u;
+        num_rendered[2] = 0u;
+        num_rendered[3] = 0u;
+        num_rendered[4] = longest;
+        num_rendered[5] = call_flags;
+        num_rendered[6] = (uint32_t)capacity;
+        num_rendered[7] = (uint32_t)(capacity >> 32);
+        if (host_R != nullptr)
+            *reinterpret_cast<volatile unsigned long long*>(host_R) =
+                (unsigned long long)R | ((unsigned long long)(longest | (overflow ? 0x80000000u : 0u)) << 32);
+    }
+    {
+        uint32_t dummy;
+        const uint32_t mine = tid < 256 ? bins[tid] : 0u;
+        const uint32_t ex = block_exclusive_scan_1024(mine, warp_sums, tid, dummy);   // first sync: every `mine` is read
+        if (tid < 256) { bin_base[tid] = ex; bins[tid] = 0u; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const int k = tid * ITEMS + i;
+        const uint32_t bin = k < n ? 255u - min(c[i] >> 3, 255u) : 256u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        const int leader = __ffs(peers) - 1;
+        uint32_t pos = 0;
+        if (lane == leader && bin < 256u) pos = bin_base[bin] + atomicAdd(&bins[bin], (uint32_t)__popc(peers));
+        pos = __shfl_sync(0xffffffffu, pos, leader);
+        if (bin < 256u) tile_order[pos + __popc(peers & ((1u << lane) - 1u))] = make_uint4((uint32_t)k, rg[i].x, rg[i].y, 0u);
+    }
+}
+
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity,
                       uint32_t list_limit, uint32_t call_flags, cudaStream_t s)
 {
+    static const int single = [] { const char* e = getenv("GUAVA_SCAN_SINGLE"); return e ? atoi(e) : 1; }();   // tuning knob
+    if (single && total_tiles <= 8192) {
+        if (total_tiles <= 2048)
+            tile_scan_single_kernel<2><<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.num_rendered,
+                                                          host_mapped_R, (unsigned long long)capacity, list_limit,
+                                                          call_flags, img.tile_order);
+        else
+            tile_scan_single_kernel<8><<<1, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.num_rendered,
+                                                          host_mapped_R, (unsigned long long)capacity, list_limit,
+                                                          call_flags, img.tile_order);
+        count_launch();
+        return;
+    }
     const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
     tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
