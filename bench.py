@@ -289,8 +289,11 @@ def run_own(args, rank, world, device):
 
     graphed = not args.eager
     if graphed:
+        # summed: the backward adds the views' parameter gradients straight into the step's [P,43] all-reduce buffer
+        # (guava_rasterizer_backward_batch_summed) -- no [V,P,43] intermediates, no packing kernel
         g_res = [grb.GraphedRenderStep(s["xyz"], s["feat"], s["op"], s["sc"], s["rot"], settings_of(s["vm"], s["pm"]),
-                                       dL_dcolor=dL) for s in sets_dev]      # each step owns its [P,43] buffer
+                                       dL_dcolor=dL, summed=not args.per_view_grads)
+                 for s in sets_dev]      # each step owns its [P,43] buffer
 
     # N > 1: the all-reduce of step k is issued asynchronously (NCCL's stream) and joined one step later,
     # so it runs under the binning kernels of step k+1 ("overlap with the next
@@ -345,7 +348,7 @@ def run_own(args, rank, world, device):
             b["packed"].copy_(sets_host[i % len(sets_host)]["packed"])
         g_e2e = [grb.GraphedRenderStep(b["xyz"], b["feat"], b["op"], b["sc"], b["rot"],
                                        settings_of(b["cams"][:, :16].reshape(V, 4, 4), b["cams"][:, 16:].reshape(V, 4, 4)),
-                                       dL_dcolor=dL) for b in stage]
+                                       dL_dcolor=dL, summed=not args.per_view_grads) for b in stage]
 
     # The step's result (loss + checksum of the reduced gradients -> pinned host memory) is produced on its
     # own stream, ordered after the step (N = 1) or after its all-reduce (N > 1), so that it runs under the
@@ -503,7 +506,9 @@ def run_own(args, rank, world, device):
     return dict(ms_res=ms_res, ms_e2e=ms_e2e, pix=pix, launches=int(launches), clocks=clk, roofline=roof,
                 h2d=h2d_bytes, d2h=d2h_bytes, wall_ms_e2e=t_wall, enqueue_ms_e2e=t_enq, ms_h2d_alone=ms_h2d_alone,
                 ms_h2d_loaded=ms_h2d_loaded,
-                step_call="eager op-by-op" if args.eager else "guava_renderer_b200.GraphedRenderStep (CUDA graph replay)")
+                step_call="eager op-by-op" if args.eager else
+                ("guava_renderer_b200.GraphedRenderStep (CUDA graph replay)" if args.per_view_grads else
+                 "guava_renderer_b200.GraphedRenderStep(summed=True) (CUDA graph replay; views summed inside the backward)"))
 
 
 ATTR_KEYS = ("smplx_rotation", "smplx_scaling", "smplx_opacity", "smplx_features_color",
@@ -1119,6 +1124,9 @@ def main():
     ap.add_argument("--trace-e2e", default="", help="write device timestamps of the e2e steps' phases to PATH.rank<r>.json")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to its GPU's NUMA node")
     ap.add_argument("--eager", action="store_true", help="enqueue every step op by op instead of replaying CUDA graphs")
+    ap.add_argument("--per-view-grads", action="store_true",
+                    help="C3: materialise the [V,P,43] per-view gradients and pack them with a kernel, instead of summing "
+                         "over the views inside the backward (GraphedRenderStep(summed=True), the default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     wl = WORKLOADS[args.workload]

@@ -21,6 +21,7 @@ EXPORTS = (
     "guava_rasterizer_mark_visible",
     "guava_rasterizer_forward_batch",
     "guava_rasterizer_backward_batch",
+    "guava_rasterizer_backward_batch_summed",
     "guava_pack_view_gradients",
     "guava_image_dot",
     "guava_selftest_cull",
@@ -110,6 +111,13 @@ def load() -> ctypes.CDLL:
         P, c_size_t, P, c_size_t, P, c_size_t, P, c_size_t, c_float, P, c_size_t,
         P, P, P, P, P, P, P, P, P,
         P, P, P, P, P, P, P, P, P,
+        c_int, c_int, P]
+    lib.guava_rasterizer_backward_batch_summed.restype = c_int
+    lib.guava_rasterizer_backward_batch_summed.argtypes = [
+        c_int, c_int, c_int, P, c_int, c_int,
+        P, c_size_t, P, c_size_t, P, c_size_t, P, c_size_t, c_float, P, c_size_t,
+        P, P, P, P, P, P, P,
+        P, P, P, P, P, P, P, c_size_t,
         c_int, c_int, P]
     lib.guava_pack_view_gradients.restype = c_int
     lib.guava_pack_view_gradients.argtypes = [c_int, c_int, P, P, P, P, P, P, P]

@@ -553,18 +553,20 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
                          const float* dL_dpix, const float* dL_invdepths,
                          float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                          float* dL_dinvdepth, float* dL_dmean3D, float* dL_dcov3D,
-                         float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream)
+                         float* dL_dscale, float* dL_drot, int debug, cudaStream_t stream,
+                         const SummedRows* sum = nullptr)   // non-NULL: outputs are sums over the views, rows of these strides
 {
     if ((size_t)in.V * in.P == 0) return GUAVA_OK;
     const int block_masks = g_opt_taken_masks.load() != 0;   // a backward after a forward that did not mark finds that in the header
-    if (!geom || !bin || !img || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
-        !dL_dmean3D || !dL_dcov3D || !radii)
+    if (!geom || !bin || !img || !dL_dpix || !dL_dopacity || !dL_dcolor || !dL_dmean3D || !radii)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
+    if (sum == nullptr && (!dL_dmean2D || !dL_dconic || !dL_dcov3D))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
     if (in.cov3D_precomp == nullptr && (!dL_dscale || !dL_drot))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "null required pointer");
-    if (dL_invdepths != nullptr && dL_dinvdepth == nullptr)
+    if (sum == nullptr && dL_invdepths != nullptr && dL_dinvdepth == nullptr)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "dL_dinvdepth buffer missing");
-    if (((uintptr_t)dL_drot & 15) != 0)   // written with one 16-byte store per Gaussian
+    if (sum == nullptr && ((uintptr_t)dL_drot & 15) != 0)   // written with one 16-byte store per Gaussian
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "dL_drot must be 16-byte aligned");
     if (((uintptr_t)in.colors & 15) || ((in.colors_vs * sizeof(float)) & 15))
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "colors_precomp must be 16-byte aligned");
@@ -596,12 +598,13 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
     StageTimer timer(stream);
     timer.begin(5);
     GUAVA_CUDA(cudaMemsetAsync(g.grad_geo, 0, (size_t)in.V * in.P * 32, stream));
-    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, block_masks, g_opt_tma_staging.load() != 0, stream);
+    launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, sum ? sum->rs_color : (size_t)NUM_CHANNELS,
+                           sum ? 0 : (size_t)in.P * NUM_CHANNELS, block_masks, g_opt_tma_staging.load() != 0, stream);
     timer.end();
     GUAVA_STAGE("render_backward", debug);
     timer.begin(6);
     launch_preprocess_backward(in, g, im.num_rendered, radii, dL_invdepths != nullptr, dL_dmean2D, dL_dconic, dL_dinvdepth,
-                               dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot, stream);
+                               dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dscale, dL_drot, sum, stream);
     timer.end();
     GUAVA_STAGE("preprocess_backward", debug);
     return GUAVA_OK;
@@ -737,6 +740,43 @@ int guava_rasterizer_backward_batch(
     return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, dL_dmean2D,
                          dL_dconic, dL_dopacity, dL_dcolor, dL_dinvdepth, dL_dmean3D, dL_dcov3D, dL_dscale,
                          dL_drot, debug, (cudaStream_t)stream);
+}
+
+int guava_rasterizer_backward_batch_summed(
+    int V, int P, int R, const float* background, int width, int height, const float* means3D,
+    size_t means3D_view_stride, const float* colors_precomp, size_t colors_view_stride, const float* opacities,
+    size_t opacities_view_stride, const float* scales, size_t scales_view_stride, float scale_modifier,
+    const float* rotations, size_t rotations_view_stride, const float* viewmatrix, const float* projmatrix,
+    const float* tan_fov, const int* radii, char* geom_buffer, char* binning_buffer, char* image_buffer,
+    const float* dL_dpix, const float* dL_invdepths, float* dL_dmean3D, float* dL_dscale, float* dL_drot,
+    float* dL_dopacity, float* dL_dcolor, size_t out_row_stride, int antialiasing, int debug, void* stream)
+{
+    (void)R;
+    if (tan_fov == nullptr) return fail(GUAVA_ERR_INVALID_ARGUMENT, "tan_fov must be a device array [V,2]");
+    if (colors_precomp == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "For non-RGB, provide precomputed Gaussian colors!");
+    if (scales == nullptr || rotations == nullptr)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "the batched entry takes scales and rotations");
+    if (out_row_stride != 0 && out_row_stride < 43)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "out_row_stride is 0 (dense [P,w] outputs) or at least 43 floats");
+    if (out_row_stride > 0xffffffffull) return fail(GUAVA_ERR_INVALID_ARGUMENT, "out_row_stride too large");
+    Inputs in{};
+    in.V = V; in.P = P; in.W = width; in.H = height;
+    in.means3D = means3D; in.means3D_vs = means3D_view_stride;
+    in.colors = colors_precomp; in.colors_vs = colors_view_stride;
+    in.opacities = opacities; in.opacities_vs = opacities_view_stride;
+    in.scales = scales; in.scales_vs = scales_view_stride;
+    in.rotations = rotations; in.rotations_vs = rotations_view_stride;
+    in.cov3D_precomp = nullptr;
+    in.scale_modifier = scale_modifier;
+    in.viewmatrix = viewmatrix; in.projmatrix = projmatrix;
+    in.tan_fov_dev = tan_fov;
+    in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
+    const uint32_t rs = (uint32_t)out_row_stride;
+    const SummedRows sum = rs ? SummedRows{rs, rs, rs, rs, rs} : SummedRows{3u, 3u, 4u, 1u, (uint32_t)NUM_CHANNELS};
+    return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, nullptr, nullptr,
+                         dL_dopacity, dL_dcolor, nullptr, dL_dmean3D, nullptr, dL_dscale, dL_drot, debug,
+                         (cudaStream_t)stream, &sum);
 }
 
 int guava_pack_view_gradients(int V, int P, const float* dL_dmeans3D, const float* dL_dscales,

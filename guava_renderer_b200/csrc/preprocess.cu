@@ -276,6 +276,10 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 // writes dL/dmean3D, dL/dcov3D, dL/dscale, dL/drot.  The 3D covariance is
 // recomputed from scale/rotation (12 FFMA-chains) instead of being stored by
 // the forward pass and re-read here (24 B/Gaussian each way).
+// SUM = 1 (guava_rasterizer_backward_batch_summed): the parameter gradients of Gaussian i are ADDED, over the views, to
+// row i of the four output arrays (row strides in `sum`: the columns of one packed [P,43] row, or dense [P,w] tensors);
+// the per-view outputs the reference's binding keeps (mean2D, conic, cov3D, inverse depth) are not written.
+template <int SUM>
 __global__ void __launch_bounds__(256)
 preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_rendered, const int* __restrict__ radii,
                            const SplatRec* __restrict__ recs,
@@ -283,7 +287,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
                            int has_invdepth, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
                            float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
-                           float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+                           float* __restrict__ dL_dscale, float* __restrict__ dL_drot, const SummedRows sum)
 {
     const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (gid >= (size_t)in.V * in.P) return;
@@ -320,14 +324,16 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
     gg1.z = mo1.z;                                               // dL/dinvdepth
     gg1.w = 0.0f;
     // outputs the reference's binding returns / keeps (rasterize_points.cu:163-172)
-    dL_dmean2D[3 * gid] = gg0.x;
-    dL_dmean2D[3 * gid + 1] = gg0.y;
-    if (dL_dconic != nullptr) {
-        dL_dconic[4 * gid] = gg0.z;
-        dL_dconic[4 * gid + 1] = gg0.w;
-        dL_dconic[4 * gid + 3] = gg1.x;
+    if (!SUM) {
+        dL_dmean2D[3 * gid] = gg0.x;
+        dL_dmean2D[3 * gid + 1] = gg0.y;
+        if (dL_dconic != nullptr) {
+            dL_dconic[4 * gid] = gg0.z;
+            dL_dconic[4 * gid + 1] = gg0.w;
+            dL_dconic[4 * gid + 3] = gg1.x;
+        }
+        if (has_invdepth && dL_dinvdepth != nullptr) dL_dinvdepth[gid] = gg1.z;
     }
-    if (has_invdepth && dL_dinvdepth != nullptr) dL_dinvdepth[gid] = gg1.z;
     const float* __restrict__ V = in.viewmatrix + 16 * v;
     const float* __restrict__ proj = in.projmatrix + 16 * v;
 
@@ -382,11 +388,13 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         const float h_scale = sqrtf(fmaxf(0.000025f, det_cov / det_cov_plus_h_cov));
         const float dL_dop_v = gg1.y;
         const float d_h_scale = dL_dop_v * in.opacities[(size_t)v * in.opacities_vs + i];
-        dL_dopacity[gid] = dL_dop_v * h_scale;
+        if (SUM) atomicAdd(dL_dopacity + (size_t)i * sum.rs_opacity, dL_dop_v * h_scale);
+        else dL_dopacity[gid] = dL_dop_v * h_scale;
         d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f ? 0.0f : d_h_scale / (2 * h_scale);
     } else {
         c_xx += h_var; c_yy += h_var;
-        dL_dopacity[gid] = gg1.y;
+        if (SUM) atomicAdd(dL_dopacity + (size_t)i * sum.rs_opacity, gg1.y);
+        else dL_dopacity[gid] = gg1.y;
     }
     float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
     if (in.antialiasing) {
@@ -414,8 +422,10 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
 #pragma unroll
         for (int k = 0; k < 6; k++) dcov[k] = 0;
     }
+    if (!SUM) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) dL_dcov3D[6 * gid + k] = dcov[k];
+        for (int k = 0; k < 6; k++) dL_dcov3D[6 * gid + k] = dcov[k];
+    }
 
     const float dL_dT00 = 2 * VT0[0] * dL_dc_xx + VT1[0] * dL_dc_xy;
     const float dL_dT01 = 2 * VT0[1] * dL_dc_xx + VT1[1] * dL_dc_xy;
@@ -446,7 +456,12 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
     gmx += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
     gmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
     gmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
-    dL_dmean3D[3 * gid] = gmx; dL_dmean3D[3 * gid + 1] = gmy; dL_dmean3D[3 * gid + 2] = gmz;
+    if (SUM) {
+        float* q = dL_dmean3D + (size_t)i * sum.rs_mean3D;
+        atomicAdd(q, gmx); atomicAdd(q + 1, gmy); atomicAdd(q + 2, gmz);
+    } else {
+        dL_dmean3D[3 * gid] = gmx; dL_dmean3D[3 * gid + 1] = gmy; dL_dmean3D[3 * gid + 2] = gmz;
+    }
 
     if (in.cov3D_precomp == nullptr) {
         const float r = sr[3], x = sr[4], y = sr[5], z = sr[6];
@@ -470,8 +485,11 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
             for (int rr = 0; rr < 3; rr++)
                 dMt[rr][c] = 2.0f * (M[0][rr] * dS[c][0] + M[1][rr] * dS[c][1] + M[2][rr] * dS[c][2]);
 #pragma unroll
-        for (int k = 0; k < 3; k++)
-            dL_dscale[3 * gid + k] = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
+        for (int k = 0; k < 3; k++) {
+            const float ds = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
+            if (SUM) atomicAdd(dL_dscale + (size_t)i * sum.rs_scale + k, ds);
+            else dL_dscale[3 * gid + k] = ds;
+        }
 #pragma unroll
         for (int k = 0; k < 3; k++)
 #pragma unroll
@@ -481,20 +499,31 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
         dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
         dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
-        reinterpret_cast<float4*>(dL_drot)[gid] = dq;
+        if (SUM) {
+            float* q = dL_drot + (size_t)i * sum.rs_rot;
+            atomicAdd(q, dq.x); atomicAdd(q + 1, dq.y); atomicAdd(q + 2, dq.z); atomicAdd(q + 3, dq.w);
+        } else {
+            reinterpret_cast<float4*>(dL_drot)[gid] = dq;
+        }
     }
 }
 
 void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const uint32_t* num_rendered, const int* radii, int has_invdepth,
                                 float* dL_dmean2D, float* dL_dconic, float* dL_dinvdepth,
                                 float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D,
-                                float* dL_dscale, float* dL_drot, cudaStream_t s)
+                                float* dL_dscale, float* dL_drot, const SummedRows* sum, cudaStream_t s)
 {
     const size_t n = (size_t)in.V * in.P;
     if (n == 0) return;
-    preprocess_backward_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
-        in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D, dL_dcov3D,
-        dL_dscale, dL_drot);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (sum != nullptr)
+        preprocess_backward_kernel<1><<<grid, 256, 0, s>>>(
+            in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D,
+            dL_dcov3D, dL_dscale, dL_drot, *sum);
+    else
+        preprocess_backward_kernel<0><<<grid, 256, 0, s>>>(
+            in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D,
+            dL_dcov3D, dL_dscale, dL_drot, SummedRows{});
     count_launch();
 }
 

@@ -94,8 +94,12 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                        const uint32_t* __restrict__ point_list, const uint8_t* __restrict__ taken_marks,
                        const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
-                       float* __restrict__ dL_dcolor, float* __restrict__ grad_geo, uint32_t* __restrict__ num_rendered)
+                       float* __restrict__ dL_dcolor, uint32_t color_rs, size_t color_vs,
+                       float* __restrict__ grad_geo, uint32_t* __restrict__ num_rendered)
 {
+    // dL_dcolor: row `id` of view v starts at dL_dcolor + v * color_vs + id * color_rs (floats).  [V,P,32] is
+    // (32, 32 P); a sum over the views into columns of a packed [P,43] row is (43, 0) -- the reductions are atomic,
+    // so the views add up in place (guava_rasterizer_backward_batch_summed).
     __shared__ BwdStage stage[NST];
     __shared__ __align__(16) float ex[4][32];   // blending weights of a survivor, one per pixel: two pairs in flight
     __shared__ __align__(16) uint32_t srows[NST][32];   // TMA: tensor-map row of the survivor in each slot
@@ -269,6 +273,8 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
     float T = T_final;
     float A = 0.0f, last_alpha = 0.0f, last_d = 0.0f;
     const size_t gbase = (size_t)v * in.P;
+    float* const colbase = dL_dcolor + (size_t)v * color_vs;
+    float* const geobase = grad_geo + gbase * 8;
 
     // Software pipeline, AHEAD = NST - 1 chunks deep: while chunk c is blended, chunks c+1 .. c+AHEAD are staged (rows in
     // flight), the records of chunk c+AHEAD+1 are in flight into a0/a1 and the ids of chunk c+AHEAD+2 into id_q[AHEAD+2].
@@ -420,14 +426,14 @@ render_backward_kernel(const Inputs in, const __grid_constant__ CUtensorMap fmap
                 const float col0 = cs0.x + cs0.y;
                 const float col1 = cs1.x + cs1.y;
 
-                const size_t gi0 = gbase + __shfl_sync(0xffffffffu, id_cur, jl0);
-                const size_t gi1 = gbase + __shfl_sync(0xffffffffu, id_cur, jl1);
+                const uint32_t gi0 = __shfl_sync(0xffffffffu, id_cur, jl0);
+                const uint32_t gi1 = __shfl_sync(0xffffffffu, id_cur, jl1);
                 // Lanes 0..27 add their partial of moment lane/4 to the packed record (word 7 is unused).
                 const bool geo_lane = lane < (INV ? 28 : 24);   // lanes 4k..4k+3: partials of moment k (7 is unused, 6 = invdepth)
-                if (any0) atomicAdd(dL_dcolor + gi0 * NUM_CHANNELS + lane, col0);
-                if (any1) atomicAdd(dL_dcolor + gi1 * NUM_CHANNELS + lane, col1);
-                if (any0 && geo_lane) atomicAdd(grad_geo + gi0 * 8 + (lane >> 2), mom0);
-                if (any1 && geo_lane) atomicAdd(grad_geo + gi1 * 8 + (lane >> 2), mom1);
+                if (any0) atomicAdd(colbase + (size_t)gi0 * color_rs + lane, col0);
+                if (any1) atomicAdd(colbase + (size_t)gi1 * color_rs + lane, col1);
+                if (any0 && geo_lane) atomicAdd(geobase + (size_t)gi0 * 8 + (lane >> 2), mom0);
+                if (any1 && geo_lane) atomicAdd(geobase + (size_t)gi1 * 8 + (lane >> 2), mom1);
             }
         }
 #pragma unroll
@@ -446,8 +452,10 @@ bool make_feature_tensor_map(const Inputs& in, CUtensorMap* out);   // render_fo
 
 void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs& img, const BinningPtrs& b,
                             const float* dL_dpix, const float* dL_dinvdepth_pix, float* dL_dcolor,
+                            size_t color_row_stride, size_t color_view_stride,
                             int taken_masks, int tma_staging, cudaStream_t s)
 {
+    const uint32_t crs = (uint32_t)color_row_stride;
     if (in.tiles == 0 || in.V == 0) return;
     CUtensorMap fmap;
     memset(&fmap, 0, sizeof(fmap));
@@ -462,18 +470,18 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
 #define GUAVA_LAUNCH_BWD2(MK, TM, IV, NS)                                                                                 \
     render_backward_kernel<MK, TM, IV, NS><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,  \
                                                                b.taken_marks, img.final_T, img.n_contrib, dL_dpix,        \
-                                                               dL_dinvdepth_pix, dL_dcolor, g.grad_geo, img.num_rendered)
+                                                               dL_dinvdepth_pix, dL_dcolor, crs, color_view_stride, g.grad_geo, img.num_rendered)
 #define GUAVA_LAUNCH_BWD(MK, TM) do { if (dL_dinvdepth_pix != nullptr) GUAVA_LAUNCH_BWD2(MK, TM, 1, 2); else GUAVA_LAUNCH_BWD2(MK, TM, 0, 2); } while (0)
 #define GUAVA_LAUNCH_BWD_MINB(MB)                                                                                          \
     do {                                                                                                                  \
         if (dL_dinvdepth_pix != nullptr)                                                                                  \
             render_backward_kernel<1, 0, 1, 2, MB><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order,       \
-                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo, \
-                img.num_rendered);                                                                                        \
+                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, crs, color_view_stride, \
+                g.grad_geo, img.num_rendered);                                                                                        \
         else                                                                                                              \
             render_backward_kernel<1, 0, 0, 2, MB><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order,       \
-                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, g.grad_geo, \
-                img.num_rendered);                                                                                        \
+                b.point_list, b.taken_marks, img.final_T, img.n_contrib, dL_dpix, dL_dinvdepth_pix, dL_dcolor, crs, color_view_stride, \
+                g.grad_geo, img.num_rendered);                                                                                        \
     } while (0)
     if (taken_masks && !tma_staging && stages == 2 && minb == 14) GUAVA_LAUNCH_BWD_MINB(14);
     else if (taken_masks && !tma_staging && stages == 2 && minb == 16) GUAVA_LAUNCH_BWD_MINB(16);

@@ -274,6 +274,41 @@ RasterizeGaussiansBatchBackwardCUDA(const torch::Tensor& background, const torch
     return std::make_tuple(part[1], part[0], part[2], part[3], part[4], part[5], part[6]);
 }
 
+// Backward of the batched entry with the sum over the views taken inside the kernels
+// (guava_rasterizer_backward_batch_summed): fills `packed` [P,43] = (means3D 3, scales 3, rotations 4, opacity 1,
+// features 32) -- the all-reduce payload of the training step -- which the caller has zero-filled.
+void RasterizeGaussiansBatchBackwardSummedCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                               const torch::Tensor& colors, const torch::Tensor& opacities, const torch::Tensor& scales,
+                                               const torch::Tensor& rotations, const float scale_modifier,
+                                               const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+                                               const torch::Tensor& tanfov, const torch::Tensor& dL_dout_color,
+                                               const c10::optional<torch::Tensor>& dL_dout_invdepth, const torch::Tensor& geomBuffer,
+                                               const int R, const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer,
+                                               const bool antialiasing, const bool debug, torch::Tensor& packed)
+{
+    TORCH_CHECK(means3D.is_cuda(), "guava_renderer_b200: tensors must live on a CUDA device (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int64_t V = viewmatrix.size(0);
+    const int64_t P = means3D.size(-2);
+    const int H = static_cast<int>(dL_dout_color.size(-2)), W = static_cast<int>(dL_dout_color.size(-1));
+    TORCH_CHECK(packed.is_cuda() && packed.scalar_type() == torch::kFloat32 && packed.is_contiguous() && packed.dim() == 2 &&
+                    packed.size(0) == P && packed.size(1) == 43,
+                "packed must be a contiguous float32 [P,43] CUDA tensor");
+    const bool has_inv = dL_dout_invdepth.has_value() && dL_dout_invdepth->defined();
+    if (V * P == 0) return;
+    const torch::Tensor bg = f32c(background), m = f32c(means3D), c = aligned16(colors), o = f32c(opacities), s = f32c(scales),
+                        r = f32c(rotations), vm = f32c(viewmatrix), pm = f32c(projmatrix), tf = f32c(tanfov),
+                        gc = f32c(dL_dout_color), gi = has_inv ? f32c(*dL_dout_invdepth) : torch::Tensor(), rad = radii.contiguous();
+    float* pk = packed.data_ptr<float>();
+    check(guava_rasterizer_backward_batch_summed(
+        static_cast<int>(V), static_cast<int>(P), R, fptr(bg), W, H, fptr(m), vstride(m, V, P * 3), fptr(c),
+        vstride(c, V, P * NUM_CHANNELS), fptr(o), vstride(o, V, P), fptr(s), vstride(s, V, P * 3), scale_modifier, fptr(r),
+        vstride(r, V, P * 4), fptr(vm), fptr(pm), fptr(tf), rad.data_ptr<int>(), reinterpret_cast<char*>(geomBuffer.data_ptr()),
+        reinterpret_cast<char*>(binningBuffer.data_ptr()), reinterpret_cast<char*>(imageBuffer.data_ptr()), fptr(gc),
+        has_inv ? fptr(gi) : nullptr, pk, pk + 3, pk + 6, pk + 10, pk + 11, 43, antialiasing ? 1 : 0, debug ? 1 : 0,
+        current_stream(means3D)));
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
@@ -285,4 +320,5 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m)
     // SURVEY.md 8(f) row 1
     m.def("rasterize_gaussians_batch", &RasterizeGaussiansBatchCUDA);
     m.def("rasterize_gaussians_batch_backward", &RasterizeGaussiansBatchBackwardCUDA);
+    m.def("rasterize_gaussians_batch_backward_summed", &RasterizeGaussiansBatchBackwardSummedCUDA);
 }

@@ -53,6 +53,9 @@ class GraphedRenderStep:
         .loss                            scalar tensor (training mode)
         .grads                           dict xyz / scaling / rotation / opacity / features (per view)
         .packed                          [P,43] sum over views, the all-reduce payload (sharding.py)
+    `summed=True`: the backward sums over the views inside its kernels, straight into `.packed`
+    (guava_rasterizer_backward_batch_summed: no [V,P,43] intermediates, no packing kernel); `.grads` and
+    `.viewspace_grad` are then not produced.  Not with a `producer` (its backward needs the per-view gradients).
     `producer` (instead of the five tensors, pass None for them): a callable that computes the rasterizer's inputs
     inside the captured step from its own static tensors -- e.g. `deform_gaussians` on a posed mesh (the step before
     the rasterizer in GUAVA, ubody_gaussian.py:245-289) -- and returns them as a dict xyz / features / opacity /
@@ -65,7 +68,10 @@ class GraphedRenderStep:
                  dL_dcolor: Optional[torch.Tensor] = None,
                  loss_fn: Optional[Callable[[torch.Tensor, torch.Tensor], torch.Tensor]] = None,
                  packed_out: Optional[torch.Tensor] = None, warmup: int = 2,
-                 producer: Optional[Callable[[], Dict[str, torch.Tensor]]] = None):
+                 producer: Optional[Callable[[], Dict[str, torch.Tensor]]] = None, summed: bool = False):
+        if summed and producer is not None:
+            raise ValueError("summed=True gives no per-view gradients for a producer's backward")
+        self.summed = bool(summed)
         self.producer = producer
         if producer is not None:
             means3D = settings.viewmatrix       # device only
@@ -120,10 +126,17 @@ class GraphedRenderStep:
             leaf = self.inputs
         P = int(leaf["xyz"].shape[-2])
         m2 = torch.empty((V, P, 3), device=self.device, requires_grad=self.training)
+        summed_out = None
+        if self.training and self.summed:
+            if self.packed is None:
+                self.packed = torch.empty(P, 43, dtype=torch.float32, device=self.device)
+            self.packed.zero_()          # the backward's kernels add into it
+            summed_out = self.packed
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
                                                            leaf["scaling"], leaf["rotation"], self.settings,
-                                                           status_words=self._status, no_host_wait=no_host_wait)
+                                                           status_words=self._status, no_host_wait=no_host_wait,
+                                                           summed_out=summed_out)
         self.color, self.radii, self.invdepth = color, radii, invd
         if not self.training:
             return
@@ -143,10 +156,13 @@ class GraphedRenderStep:
             with torch.cuda.stream(self._side):
                 self.loss = image_dot(color.detach(), self.dL_dcolor, self._loss_buf)
             color.backward(self.dL_dcolor)
-        self.grads = {k: v.grad for k, v in leaf.items()}
-        self.viewspace_grad = m2.grad
-        order = ("xyz", "scaling", "rotation", "opacity", "features")
-        self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
+        if self.summed:
+            self.grads, self.viewspace_grad = {}, None
+        else:
+            self.grads = {k: v.grad for k, v in leaf.items()}
+            self.viewspace_grad = m2.grad
+            order = ("xyz", "scaling", "rotation", "opacity", "features")
+            self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
         if self.loss_fn is None:
             cur.wait_stream(self._side)
 

@@ -402,6 +402,9 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         aux = call.get("refiner_output")
         status = call.get("status_words")
         no_wait = bool(call.get("no_host_wait", False))
+        # the training step's packed [P,43] buffer: the backward then sums over the views inside its kernels
+        # (guava_rasterizer_backward_batch_summed) and hands autograd no per-view gradients
+        ctx.summed_out = call.get("summed_out")
         fwd_only = not any(ctx.needs_input_grad)      # no gradient can be asked for: inference
         m, c, o = _f32c(means3D), _f32c(colors_precomp), _f32c(opacities)
         s, r = _f32c(scales), _f32c(rotations)
@@ -466,6 +469,28 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         has_inv = grad_invdepth is not None
         if grad_color is None:
             grad_color = torch.zeros(V, NUM_CHANNELS, H, W, dtype=torch.float32, device=dev)
+        if ctx.summed_out is not None:
+            pk = ctx.summed_out
+            if pk.dtype != torch.float32 or tuple(pk.shape) != (P, 43) or not pk.is_contiguous() or pk.device != dev:
+                raise ValueError("summed_out must be a contiguous float32 [P,43] tensor on the inputs' device")
+            if BINDING == "compiled":
+                _C.rasterize_gaussians_batch_backward_summed(
+                    bg, m, radii, c, o, s, r, float(st.scale_modifier), vm, pm, tf, grad_color,
+                    grad_invdepth if has_inv else None, geom, int(ctx.num_rendered), binning, img,
+                    bool(st.antialiasing), bool(st.debug), pk)
+            elif V * P:
+                with _device_of(m):
+                    gc = _f32c(grad_color)
+                    gi = _f32c(grad_invdepth) if has_inv else None
+                    b0 = pk.data_ptr()
+                    _check(_lib.load().guava_rasterizer_backward_batch_summed(
+                        V, P, int(ctx.num_rendered), _ptr(bg), W, H,
+                        _ptr(m), ctx.strides[0], _ptr(c), ctx.strides[1], _ptr(o), ctx.strides[2],
+                        _ptr(s), ctx.strides[3], float(st.scale_modifier), _ptr(r), ctx.strides[4],
+                        _ptr(vm), _ptr(pm), _ptr(tf), _ptr(radii), _ptr(geom), _ptr(binning), _ptr(img),
+                        _ptr(gc), _ptr(gi), b0, b0 + 12, b0 + 24, b0 + 40, b0 + 44, 43,
+                        int(bool(st.antialiasing)), int(bool(st.debug)), _stream_ptr(dev)))
+            return (None,) * 8
         if BINDING == "compiled":
             g_mean2D, g_color, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot = _C.rasterize_gaussians_batch_backward(
                 bg, m, radii, c, o, s, r, float(st.scale_modifier), vm, pm, tf, grad_color,
@@ -511,16 +536,21 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
 
 def rasterize_gaussians_batch(means3D, means2D, colors_precomp, opacities, scales, rotations,
                               settings: BatchRasterizationSettings, refiner_output: Optional[torch.Tensor] = None,
-                              status_words: Optional[torch.Tensor] = None, no_host_wait: bool = False):
+                              status_words: Optional[torch.Tensor] = None, no_host_wait: bool = False,
+                              summed_out: Optional[torch.Tensor] = None):
     """means3D [V,P,3] or [P,3]; means2D [V,P,3] (gradient sink only); colors_precomp [V,P,32] or [P,32];
     opacities [V,P,1] or [P,1]; scales [V,P,3] or [P,3]; rotations [V,P,4] or [P,4].
     Per-call options (guava_call_options): `refiner_output` bf16 [V,H,W,32] written by the compositing
     kernel's epilogue; `status_words` pinned int32[2] receiving (num_rendered, longest list | overflow << 31);
     `no_host_wait` enqueues the chain without waiting for num_rendered (CUDA-graph capture).
+    `summed_out`: a ZERO-FILLED float32 [P,43] tensor; the backward then adds into it, inside its kernels, the sum over
+    the views of the parameter gradients (means3D 3, scales 3, rotations 4, opacity 1, features 32 -- the training
+    step's all-reduce payload, sharding.py) and the input tensors receive NO `.grad`.
     Returns (color [V,32,H,W], radii [V,P] int32, invdepth [V,1,H,W])."""
     call = None
-    if refiner_output is not None or status_words is not None or no_host_wait:
-        call = dict(refiner_output=refiner_output, status_words=status_words, no_host_wait=no_host_wait)
+    if refiner_output is not None or status_words is not None or no_host_wait or summed_out is not None:
+        call = dict(refiner_output=refiner_output, status_words=status_words, no_host_wait=no_host_wait,
+                    summed_out=summed_out)
     return _RasterizeGaussiansBatch.apply(means3D, means2D, colors_precomp, opacities, scales, rotations, settings, call)
 
 

@@ -234,6 +234,45 @@ int guava_rasterizer_backward_batch(
     int debug,
     void *stream);
 
+/* Backward of the batched entry with the sum over the views taken inside the kernels ("one
+ * all-reduce over the concatenated per-Gaussian parameter gradients [P,43] ... written directly by the
+ * backward-preprocess kernel"; mirrors what the reference trainer's DDP step sums, main/trainer.py:40-43,95).
+ * Each output row i receives  sum over v of  dL/d(parameter i of view v)  -- for tensors shared by all views
+ * (view stride 0) that IS the gradient of the shared tensor, what the per-view entry leaves to the caller.  The two
+ * kernels add with atomics into the caller's ZERO-FILLED outputs; the per-view outputs the reference's binding keeps
+ * (mean2D, conic, cov3D, inverse depth: rasterize_points.cu:163-172) are not produced.
+ * out_row_stride = 0: five dense tensors [P,3] [P,3] [P,4] [P,1] [P,32].  out_row_stride = s >= 43: the five
+ * pointers address columns of rows s floats apart -- one packed [P,43] buffer is (buf, buf+3, buf+6, buf+10,
+ * buf+11, 43), the layout of guava_pack_view_gradients, without that kernel and without the [V,P,43] intermediates. */
+int guava_rasterizer_backward_batch_summed(
+    int V, int P, int R,
+    const float *background,
+    int width, int height,
+    const float *means3D, size_t means3D_view_stride,
+    const float *colors_precomp, size_t colors_view_stride,
+    const float *opacities, size_t opacities_view_stride,
+    const float *scales, size_t scales_view_stride,
+    float scale_modifier,
+    const float *rotations, size_t rotations_view_stride,
+    const float *viewmatrix,
+    const float *projmatrix,
+    const float *tan_fov,
+    const int *radii,
+    char *geom_buffer,
+    char *binning_buffer,
+    char *image_buffer,
+    const float *dL_dpix,               /* [V,32,H,W] */
+    const float *dL_invdepths,          /* [V,1,H,W] or NULL */
+    float *dL_dmean3D,                  /* rows of 3, zero-filled */
+    float *dL_dscale,                   /* rows of 3, zero-filled */
+    float *dL_drot,                     /* rows of 4, zero-filled */
+    float *dL_dopacity,                 /* rows of 1, zero-filled */
+    float *dL_dcolor,                   /* rows of 32, zero-filled */
+    size_t out_row_stride,              /* 0 = dense, else floats between rows (>= 43) */
+    int antialiasing,
+    int debug,
+    void *stream);
+
 /* Training-side helper: sum the per-view per-Gaussian parameter gradients over the
  * V local views and pack them as one [P,43] fp32 row per Gaussian = (means3D 3, scales 3, rotations 4,
  * opacity 1, features 32) -- the payload of the one all-reduce that mirrors the reference trainer's DDP

@@ -25,7 +25,9 @@ def test_bench_line_carries_the_contract_keys():
     assert line["e2e"]["value"] <= line["value"] * 1.02
     assert line["e2e"]["h2d_bytes_per_step"] == 2 * 20000 * 43 * 4 + 2 * 32 * 4
     assert line["e2e"]["d2h_bytes_per_step"] > 0
-    assert line["gpu_launches"] >= 4 * 9          # at least the nine library kernels of a step, every step
+    # the eight library kernels of a step, every step: preprocess, tile scan, scatter, tile sort, the two compositors,
+    # the loss reduction and the backward preprocess (the packing kernel went when the backward began to sum the views)
+    assert line["gpu_launches"] >= 4 * 8
     r = line["roofline"]
     assert r["bound"] == "hbm" and 0 < r["frac"] < 1 and r["achieved"] > 0 and r["peak"] > 0
     assert "workload" in line["config"] and "model" not in line["config"]

@@ -172,6 +172,22 @@ def test_c3_headline_config_batched_and_graphed_vs_reference_build(ref, P):
     want_loss = sum(float((torch.from_numpy(refs[v][1]).double() * dL[v].cpu().double()).sum()) for v in range(V))
     assert abs(float(step.loss) - want_loss) <= 1e-4 * abs(want_loss) + 1e-3
 
+    # the same step with the sum over the views taken inside the backward's kernels (what bench.py replays)
+    del step
+    step = grb.GraphedRenderStep(stack("xyz"), stack("features"), stack("opacity"), stack("scaling"), stack("rotation"),
+                                 st, dL_dcolor=dL, summed=True)
+    for _ in range(3):       # every replay zero-fills the packed buffer before its backward adds into it
+        step.replay()
+    step.check()
+    for v in range(V):
+        assert np.abs(step.color[v].detach().cpu().numpy() - refs[v][1]).max() <= 1e-5
+    got = step.packed.detach().cpu().numpy()
+    for name, sl in (("xyz", slice(0, 3)), ("scaling", slice(3, 6)), ("rotation", slice(6, 10)), ("opacity", slice(10, 11)),
+                     ("features", slice(11, 43))):
+        st_ = util.grad_gate("summed " + name, got[:, sl], want[:, sl])
+        _record(f"C3 P={P} graphed summed {name}", st_)
+    assert abs(float(step.loss) - want_loss) <= 1e-4 * abs(want_loss) + 1e-3
+
 
 def test_c2_eight_views_batched_forward_vs_reference_build(ref):
     """BASELINE.json config 2: 8 views x 100 k Gaussians, 512x512, forward only, one launch chain -- eager and as a

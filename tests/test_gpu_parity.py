@@ -958,3 +958,83 @@ def test_inference_calls_of_the_batched_entry_record_no_taken_marks():
     assert out[False][1] == 0 and out[True][1] == 1
     assert out[False][2] < out[True][2]
     assert torch.equal(out[False][0], out[True][0])
+
+
+@pytest.mark.parametrize("binding", ["compiled", "ctypes"])
+@pytest.mark.parametrize("shared", [False, True], ids=["per_view_clouds", "shared_cloud"])
+@pytest.mark.parametrize("antialiasing", [False, True], ids=["plain", "antialiasing"])
+def test_summed_backward_equals_the_sum_of_the_per_view_gradients(binding, shared, antialiasing, monkeypatch):
+    """guava_rasterizer_backward_batch_summed (sum over the views inside the two backward kernels, straight into the
+    packed [P,43] rows) against the per-view entry followed by pack_gradients, with an inverse-depth gradient, for
+    per-view clouds and for one cloud shared by all views (view strides 0: the sum is that tensor's gradient), through
+    both bindings; then the dense form (out_row_stride = 0) through the C ABI."""
+    import ctypes
+    from guava_renderer_b200 import rasterizer as rz
+    if binding == "compiled" and rz.BINDING != "compiled":
+        pytest.skip("this process runs with GUAVA_BINDING=ctypes")
+    monkeypatch.setattr(rz, "BINDING", binding)      # the batched entry picks its binding per call
+    V, P, H, W = 3, 5000, 80, 112
+    views = [util.inputs_for(P, H, W, seed=700 + (0 if shared else v), view=v, num_views=V, scale_mult=1.3) for v in range(V)]
+    stack = lambda k: torch.stack([x[k] for x in views], 0).to(DEV)
+    cloud = (lambda k: views[0][k].to(DEV)) if shared else stack
+    g = torch.Generator().manual_seed(4)
+    dL = torch.randn(V, 32, H, W, generator=g).to(DEV)
+    dLi = torch.randn(V, 1, H, W, generator=g).to(DEV)
+    tanfov = torch.tensor([[x["tanfovx"], x["tanfovy"]] for x in views], device=DEV)
+    st = grb.BatchRasterizationSettings(H, W, tanfov, torch.linspace(-1, 1, 32, device=DEV).repeat(V, 1).contiguous(), 1.0,
+                                        stack("viewmatrix"), stack("projmatrix"), antialiasing=antialiasing)
+    grb.set_option("capacity_hint", 0)
+    keys = ("xyz", "scaling", "rotation", "opacity", "features")
+
+    def run(summed_out):
+        leaf = {k: cloud(k).clone().requires_grad_(True) for k in keys}
+        m2 = torch.zeros(V, P, 3, device=DEV, requires_grad=True)
+        color, radii, invd = grb.rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
+                                                           leaf["scaling"], leaf["rotation"], st, summed_out=summed_out)
+        ((color * dL).sum() + (invd * dLi).sum()).backward()
+        torch.cuda.synchronize()
+        return leaf, color.detach()
+
+    leaf, color0 = run(None)
+    grads = [leaf[k].grad for k in keys]
+    want = torch.cat([x if x.dim() == 2 else x.sum(0) for x in grads], dim=1).cpu().numpy()
+    packed = torch.zeros(P, 43, device=DEV)
+    leaf1, color1 = run(packed)
+    assert torch.equal(color0, color1)
+    assert all(leaf1[k].grad is None for k in keys)          # the sum is the only output of that backward
+    got = packed.cpu().numpy()
+    assert np.abs(want[:, 3:10]).max() > 0 and np.abs(want[:, 10]).max() > 0
+    for name, sl in (("xyz", slice(0, 3)), ("scaling", slice(3, 6)), ("rotation", slice(6, 10)), ("opacity", slice(10, 11)),
+                     ("features", slice(11, 43))):
+        assert util.rel_err(got[:, sl], want[:, sl]) <= 5e-5, name
+        util.grad_gate("summed " + name, got[:, sl], want[:, sl])
+    if binding != "ctypes" or antialiasing:
+        return
+    # dense outputs: five [P,w] tensors, same call with out_row_stride = 0 on the buffers of one more forward
+    lib = grb._lib_mod.load()
+    leaf2 = {k: cloud(k).clone().requires_grad_(True) for k in keys}
+    m2 = torch.zeros(V, P, 3, device=DEV, requires_grad=True)
+    color, radii, invd = grb.rasterize_gaussians_batch(leaf2["xyz"], m2, leaf2["features"], leaf2["opacity"],
+                                                       leaf2["scaling"], leaf2["rotation"], st)
+    geom, binning, img = rz._tls.last_buffers
+    outs = {k: torch.zeros(P, w, device=DEV) for k, w in zip(keys, (3, 3, 4, 1, 32))}
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    vs = lambda k, w: 0 if shared else P * w
+    x = {k: leaf2[k].detach().contiguous() for k in keys}
+    rc = lib.guava_rasterizer_backward_batch_summed(
+        V, P, 0, p(st.bg), W, H, p(x["xyz"]), vs("xyz", 3), p(x["features"]), vs("features", 32), p(x["opacity"]),
+        vs("opacity", 1), p(x["scaling"]), vs("scaling", 3), 1.0, p(x["rotation"]), vs("rotation", 4),
+        p(st.viewmatrix), p(st.projmatrix), p(tanfov), p(radii), p(geom), p(binning), p(img), p(dL), p(dLi),
+        p(outs["xyz"]), p(outs["scaling"]), p(outs["rotation"]), p(outs["opacity"]), p(outs["features"]), 0, 0, 0,
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, grb._lib_mod.last_error()
+    torch.cuda.synchronize()
+    dense = torch.cat([outs[k] for k in keys], dim=1).cpu().numpy()
+    assert util.rel_err(dense, want) <= 5e-5
+    rc = lib.guava_rasterizer_backward_batch_summed(
+        V, P, 0, p(st.bg), W, H, p(x["xyz"]), vs("xyz", 3), p(x["features"]), vs("features", 32), p(x["opacity"]),
+        vs("opacity", 1), p(x["scaling"]), vs("scaling", 3), 1.0, p(x["rotation"]), vs("rotation", 4),
+        p(st.viewmatrix), p(st.projmatrix), p(tanfov), p(radii), p(geom), p(binning), p(img), p(dL), p(dLi),
+        p(outs["xyz"]), p(outs["scaling"]), p(outs["rotation"]), p(outs["opacity"]), p(outs["features"]), 17, 0, 0,
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == grb._lib_mod.GUAVA_ERR_INVALID_ARGUMENT and "out_row_stride" in grb._lib_mod.last_error()
