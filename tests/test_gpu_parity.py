@@ -1038,3 +1038,76 @@ def test_summed_backward_equals_the_sum_of_the_per_view_gradients(binding, share
         p(outs["xyz"]), p(outs["scaling"]), p(outs["rotation"]), p(outs["opacity"]), p(outs["features"]), 17, 0, 0,
         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == grb._lib_mod.GUAVA_ERR_INVALID_ARGUMENT and "out_row_stride" in grb._lib_mod.last_error()
+
+
+def _autograd_on(device, inp, dL, stream=None, delayed_fill=False):
+    """One forward + backward through GaussianRasterizer_32 with every tensor on `device`.  delayed_fill: the inputs
+    are written by a copy that sits on `stream` behind a ~20 ms spin kernel -- only work ordered on that stream sees them."""
+    keys = ("xyz", "features", "opacity", "scaling", "rotation")
+    with torch.cuda.device(device):
+        ctx = torch.cuda.stream(stream) if stream is not None else torch.cuda.stream(torch.cuda.current_stream(device))
+        src = {k: inp[k].to(device) for k in keys}
+        torch.cuda.synchronize(device)
+        with ctx:
+            leaf = {k: torch.zeros_like(src[k]) for k in keys}
+            if delayed_fill:
+                torch.cuda._sleep(40_000_000)
+            for k in keys:
+                leaf[k].copy_(src[k], non_blocking=True)
+                leaf[k].requires_grad_(True)
+            m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+            rast = ours.GaussianRasterizer_32(raster_settings=util.settings_for(ours, inp, device))
+            color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                                      opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"],
+                                      cov3D_precomp=None)
+            (color * dL.to(device)).sum().backward()
+        torch.cuda.synchronize(device)
+    return color.detach().cpu(), radii.cpu(), {k: v.grad.cpu().numpy() for k, v in leaf.items()}
+
+
+def test_calls_are_ordered_on_the_callers_current_stream():
+    """The reference launches on the legacy default stream (no stream argument anywhere in rasterize_points.cu); the
+    C ABI takes the stream and the bindings pass torch's current one.  Inputs that only exist on a side stream --
+    written behind a spin kernel, no synchronisation before the call -- must be what the forward AND the backward see."""
+    inp = util.inputs_for(P=4000, H=96, W=96, seed=70, scale_mult=1.0)
+    dL = torch.randn(32, 96, 96, generator=torch.Generator().manual_seed(1))
+    c0, r0, g0 = _autograd_on(DEV, inp, dL)
+    side = torch.cuda.Stream(device=DEV)
+    c1, r1, g1 = _autograd_on(DEV, inp, dL, stream=side, delayed_fill=True)
+    assert int((r0 > 0).sum()) > 1000
+    assert torch.equal(c0, c1) and torch.equal(r0, r1)
+    for k in g0:
+        assert util.rel_err(g1[k], g0[k]) <= 5e-5, k
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_calls_on_a_device_that_is_not_the_current_one():
+    """Tensors on cuda:1 while cuda:0 is the current device (the reference has no device guard): same image, same
+    radii, same gradients as on cuda:0 -- through the default binding and through the ctypes binding of the batched
+    entry (its allocator callbacks, pinned status words and per-device state)."""
+    inp = util.inputs_for(P=4000, H=96, W=96, seed=71, scale_mult=1.0)
+    dL = torch.randn(32, 96, 96, generator=torch.Generator().manual_seed(1))
+    torch.cuda.set_device(0)
+    c0, r0, g0 = _autograd_on("cuda:0", inp, dL)
+    # not inside `with torch.cuda.device(1)`: the call itself has to find the tensors' device
+    keys = ("xyz", "features", "opacity", "scaling", "rotation")
+    leaf = {k: inp[k].to("cuda:1").requires_grad_(True) for k in keys}
+    m2 = torch.zeros_like(leaf["xyz"], requires_grad=True)
+    rast = ours.GaussianRasterizer_32(raster_settings=util.settings_for(ours, inp, "cuda:1"))
+    color, radii, invd = rast(means3D=leaf["xyz"], means2D=m2, shs=None, colors_precomp=leaf["features"],
+                              opacities=leaf["opacity"], scales=leaf["scaling"], rotations=leaf["rotation"], cov3D_precomp=None)
+    (color * dL.to("cuda:1")).sum().backward()
+    torch.cuda.synchronize("cuda:1")
+    assert torch.cuda.current_device() == 0
+    assert torch.equal(color.detach().cpu(), c0) and torch.equal(radii.cpu(), r0)
+    for k in g0:
+        assert util.rel_err(leaf[k].grad.cpu().numpy(), g0[k]) <= 5e-5, k
+    # the batched entry on cuda:1
+    st = grb.BatchRasterizationSettings(96, 96, torch.tensor([[inp["tanfovx"], inp["tanfovy"]]], device="cuda:1"),
+                                        inp["bg"][None].to("cuda:1"), 1.0, inp["viewmatrix"][None].to("cuda:1"),
+                                        inp["projmatrix"][None].to("cuda:1"))
+    x = {k: inp[k].to("cuda:1") for k in keys}
+    cb, rb, _ = grb.rasterize_gaussians_batch(x["xyz"], torch.zeros(1, 4000, 3, device="cuda:1"), x["features"], x["opacity"],
+                                              x["scaling"], x["rotation"], st)
+    torch.cuda.synchronize("cuda:1")
+    assert torch.equal(cb[0].cpu(), c0) and torch.equal(rb[0].cpu(), r0)
