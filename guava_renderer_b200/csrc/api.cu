@@ -773,7 +773,7 @@ int guava_rasterizer_backward_batch_summed(
     in.tan_fov_dev = tan_fov;
     in.background = background; in.antialiasing = antialiasing; in.prefiltered = 0;
     const uint32_t rs = (uint32_t)out_row_stride;
-    const SummedRows sum = rs ? SummedRows{rs, rs, rs, rs, rs} : SummedRows{3u, 3u, 4u, 1u, (uint32_t)NUM_CHANNELS};
+    const SummedRows sum = rs ? SummedRows{rs, rs, rs, rs, rs, -1} : SummedRows{3u, 3u, 4u, 1u, (uint32_t)NUM_CHANNELS, -1};
     return backward_impl(in, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_invdepths, nullptr, nullptr,
                          dL_dopacity, dL_dcolor, nullptr, dL_dmean3D, nullptr, dL_dscale, dL_drot, debug,
                          (cudaStream_t)stream, &sum);

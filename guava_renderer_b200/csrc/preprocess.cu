@@ -289,9 +289,20 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
                            float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
                            float* __restrict__ dL_dscale, float* __restrict__ dL_drot, const SummedRows sum)
 {
-    const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (gid >= (size_t)in.V * in.P) return;
-    if (num_rendered[1]) return;   // the forward's binning overflowed: no lists, no gradients (see render_backward.cu)
+    // SUM with a power-of-two view count (sum.vshift >= 0): the V views of a Gaussian sit in adjacent lanes, their
+    // eleven values are added with shuffles and lane v = 0 stores the sums -- plain stores instead of 11 V scattered
+    // reductions per Gaussian (at V = 2, P = 100 k the atomics cost 7 us of a 12 us kernel).  Every lane then stays to
+    // the end: what used to be early returns are predicates.
+    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
+    const size_t n_total = (size_t)in.V * in.P;
+    const bool lanes = SUM && sum.vshift >= 0;
+    if (!lanes && t >= n_total) return;
+    if (num_rendered[1]) return;   // the forward's binning overflowed: no lists, no gradients (see render_backward.cu); grid-uniform
+    const bool in_range = t < n_total;
+    const size_t gid = !lanes ? t : (in_range ? (t & (size_t)(in.V - 1)) * in.P + (t >> sum.vshift) : 0);
+    float acc[11];
+#pragma unroll
+    for (int k = 0; k < 11; k++) acc[k] = 0.0f;
     // Per-Gaussian sums written by the backward compositing kernel: moments of s = dL/dG * G about
     // the pixel offset d = mean2D - pixel, (sum s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2), then
     // sum G*dL/dalpha and sum w*dL/dinvdepth.  backward.cu:612-635 in terms of them.
@@ -313,7 +324,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         sr[0] = sp[0]; sr[1] = sp[1]; sr[2] = sp[2];
         sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
     }
-    if (!(rad > 0)) return;
+    if (in_range && rad > 0) {
     float4 gg0, gg1;
     gg0.x = -(rc0.z * mo0.x + rc0.w * mo0.y) * (0.5f * in.W);   // dL/dmean2D.x (NDC units, :626)
     gg0.y = -(rc1.x * mo0.y + rc0.w * mo0.x) * (0.5f * in.H);   // dL/dmean2D.y
@@ -388,12 +399,12 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         const float h_scale = sqrtf(fmaxf(0.000025f, det_cov / det_cov_plus_h_cov));
         const float dL_dop_v = gg1.y;
         const float d_h_scale = dL_dop_v * in.opacities[(size_t)v * in.opacities_vs + i];
-        if (SUM) atomicAdd(dL_dopacity + (size_t)i * sum.rs_opacity, dL_dop_v * h_scale);
+        if (SUM) acc[10] = dL_dop_v * h_scale;
         else dL_dopacity[gid] = dL_dop_v * h_scale;
         d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f ? 0.0f : d_h_scale / (2 * h_scale);
     } else {
         c_xx += h_var; c_yy += h_var;
-        if (SUM) atomicAdd(dL_dopacity + (size_t)i * sum.rs_opacity, gg1.y);
+        if (SUM) acc[10] = gg1.y;
         else dL_dopacity[gid] = gg1.y;
     }
     float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
@@ -457,8 +468,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
     gmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
     gmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
     if (SUM) {
-        float* q = dL_dmean3D + (size_t)i * sum.rs_mean3D;
-        atomicAdd(q, gmx); atomicAdd(q + 1, gmy); atomicAdd(q + 2, gmz);
+        acc[0] = gmx; acc[1] = gmy; acc[2] = gmz;
     } else {
         dL_dmean3D[3 * gid] = gmx; dL_dmean3D[3 * gid + 1] = gmy; dL_dmean3D[3 * gid + 2] = gmz;
     }
@@ -487,7 +497,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             const float ds = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
-            if (SUM) atomicAdd(dL_dscale + (size_t)i * sum.rs_scale + k, ds);
+            if (SUM) acc[3 + k] = ds;
             else dL_dscale[3 * gid + k] = ds;
         }
 #pragma unroll
@@ -500,11 +510,32 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
         dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
         if (SUM) {
-            float* q = dL_drot + (size_t)i * sum.rs_rot;
-            atomicAdd(q, dq.x); atomicAdd(q + 1, dq.y); atomicAdd(q + 2, dq.z); atomicAdd(q + 3, dq.w);
+            acc[6] = dq.x; acc[7] = dq.y; acc[8] = dq.z; acc[9] = dq.w;
         } else {
             reinterpret_cast<float4*>(dL_drot)[gid] = dq;
         }
+    }
+    }   // visible
+    if (!SUM) return;
+    if (lanes) {
+        // lanes 0 .. V-1 of every aligned group hold the views of one Gaussian: butterfly over the group
+        for (int o = 1; o < in.V; o <<= 1) {
+#pragma unroll
+            for (int k = 0; k < 11; k++) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+        }
+        if (!in_range || v != 0) return;
+        float* q;
+        q = dL_dmean3D + (size_t)i * sum.rs_mean3D;  q[0] = acc[0]; q[1] = acc[1]; q[2] = acc[2];
+        q = dL_dscale + (size_t)i * sum.rs_scale;    q[0] = acc[3]; q[1] = acc[4]; q[2] = acc[5];
+        q = dL_drot + (size_t)i * sum.rs_rot;        q[0] = acc[6]; q[1] = acc[7]; q[2] = acc[8]; q[3] = acc[9];
+        dL_dopacity[(size_t)i * sum.rs_opacity] = acc[10];
+    } else if (rad > 0) {   // any view count: the views add up in the zero-filled rows
+        float* q;
+        q = dL_dmean3D + (size_t)i * sum.rs_mean3D;  atomicAdd(q, acc[0]); atomicAdd(q + 1, acc[1]); atomicAdd(q + 2, acc[2]);
+        q = dL_dscale + (size_t)i * sum.rs_scale;    atomicAdd(q, acc[3]); atomicAdd(q + 1, acc[4]); atomicAdd(q + 2, acc[5]);
+        q = dL_drot + (size_t)i * sum.rs_rot;
+        atomicAdd(q, acc[6]); atomicAdd(q + 1, acc[7]); atomicAdd(q + 2, acc[8]); atomicAdd(q + 3, acc[9]);
+        atomicAdd(dL_dopacity + (size_t)i * sum.rs_opacity, acc[10]);
     }
 }
 
@@ -516,10 +547,16 @@ void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const uint3
     const size_t n = (size_t)in.V * in.P;
     if (n == 0) return;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    if (sum != nullptr)
+    if (sum != nullptr) {
+        SummedRows sr = *sum;
+        sr.vshift = -1;
+        if (in.V <= 32 && (in.V & (in.V - 1)) == 0)
+            for (int k = 0; k < 6; k++)
+                if ((1 << k) == in.V) sr.vshift = k;
         preprocess_backward_kernel<1><<<grid, 256, 0, s>>>(
             in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D,
-            dL_dcov3D, dL_dscale, dL_drot, *sum);
+            dL_dcov3D, dL_dscale, dL_drot, sr);
+    }
     else
         preprocess_backward_kernel<0><<<grid, 256, 0, s>>>(
             in, num_rendered, radii, g.rec, g.grad_geo, has_invdepth, dL_dmean2D, dL_dconic, dL_dinvdepth, dL_dopacity, dL_dmean3D,
