@@ -577,7 +577,8 @@ def run_own_pose(args, rank, world, device):
         buf.copy_(poses_host[i % POSE_SETS])
         prod = Producer(buf)
         stage.append(dict(buf=buf, prod=prod, ev=torch.cuda.Event(), done=torch.cuda.Event(), fin=torch.cuda.Event(),
-                          step=grb.GraphedRenderStep(None, None, None, None, None, st, dL_dcolor=dL, producer=prod)))
+                          step=grb.GraphedRenderStep(None, None, None, None, None, st, dL_dcolor=dL, producer=prod,
+                                                     pack=False)))      # the step ends in the avatar attributes' gradients
     copy_stream = torch.cuda.Stream(device=device)
     result_stream = torch.cuda.Stream(device=device)     # the step's result is reduced and read back beside the next step
     result_host = torch.empty(3, dtype=torch.float32).pin_memory()
@@ -599,12 +600,13 @@ def run_own_pose(args, rank, world, device):
         if host_inputs:
             compute.wait_event(b["fin"])      # the result of the step that last used these buffers has been read
         g.replay()
-        if host_inputs:   # the step's result: loss, |d/d(rasterizer inputs)|_1, |d/d(uv_local_xyz)|_1 -> pinned host memory
+        if host_inputs:   # the step's result: loss, |d/d(avatar attributes)|_1, |d/d(uv_local_xyz)|_1 -> pinned host memory
             b["done"].record(compute)
             with torch.cuda.stream(result_stream):
                 result_stream.wait_event(b["done"])
-                res = torch.stack([g.loss, torch.linalg.vector_norm(g.packed.view(-1), 1),
-                                   torch.linalg.vector_norm(b["prod"].leaves["uv_local_xyz"].grad.view(-1), 1)])
+                lv = b["prod"].leaves      # the reference arm's recipe: loss, |d/d(all attributes)|_1, |d/d(uv_local_xyz)|_1
+                res = torch.stack([g.loss, sum(torch.linalg.vector_norm(lv[k].grad.view(-1), 1) for k in ATTR_KEYS),
+                                   torch.linalg.vector_norm(lv["uv_local_xyz"].grad.view(-1), 1)])
                 result_host.copy_(res, non_blocking=True)
                 b["fin"].record(result_stream)
 

@@ -27,6 +27,7 @@ EXPORTS = (
     "guava_selftest_cull",
     "guava_deform_gaussians_forward",
     "guava_deform_gaussians_backward",
+    "guava_deform_split_gradients",
     "guava_deform_gaussians_forward_static",
     "guava_buffer_layout",
     "guava_buffer_layout_of_call",
@@ -129,6 +130,8 @@ def load() -> ctypes.CDLL:
     lib.guava_deform_gaussians_forward_static.argtypes = [c_int] * 4 + [P] * 20
     lib.guava_deform_gaussians_backward.restype = c_int
     lib.guava_deform_gaussians_backward.argtypes = [c_int] * 4 + [P] * 12
+    lib.guava_deform_split_gradients.restype = c_int
+    lib.guava_deform_split_gradients.argtypes = [c_int] * 3 + [P] * 9
     lib.guava_buffer_layout.restype = c_int
     lib.guava_buffer_layout.argtypes = [c_int, c_int, c_int, c_int, c_size_t, POINTER(Layout)]
     lib.guava_selftest_cull.restype = c_int

@@ -264,6 +264,43 @@ concat_features_kernel(int B, int Nv, int N, const float4* __restrict__ a, const
     }
 }
 
+// The backward of that concatenation (and of the opacity / SMPLX-scaling pass-through): the rasterizer's gradients
+// [B,Nv+N,w] split into the contiguous per-attribute tensors autograd hands to the leaves.  As slices of the
+// [B,Nv+N,w] tensors they would each be cloned by torch's gradient accumulation (four copy kernels, 29 us at the
+// GUAVA size); this is one pass, 16 bytes per thread for the features.
+__global__ void __launch_bounds__(256)
+split_gradients_kernel(int B, int Nv, int N, const float* __restrict__ g_scale, const float* __restrict__ g_op,
+                       const float4* __restrict__ g_feat, float* __restrict__ d_smplx_scale, float* __restrict__ d_smplx_op,
+                       float4* __restrict__ d_smplx_feat, float* __restrict__ d_uv_op, float4* __restrict__ d_uv_feat)
+{
+    const size_t rowq = NUM_CHANNELS / 4;
+    const size_t P = (size_t)Nv + N;
+    const size_t first = (size_t)blockIdx.x * 256 + threadIdx.x, step = (size_t)gridDim.x * 256;
+    if (g_feat != nullptr) {
+        const size_t total = (size_t)B * P * rowq;
+        for (size_t t = first; t < total; t += step) {
+            const size_t row = t / rowq, c = t - row * rowq;
+            const size_t b = row / P, i = row - b * P;
+            const float4 v = g_feat[t];
+            if (i < (size_t)Nv) { if (d_smplx_feat != nullptr) d_smplx_feat[(b * Nv + i) * rowq + c] = v; }
+            else if (d_uv_feat != nullptr) d_uv_feat[(b * N + (i - Nv)) * rowq + c] = v;
+        }
+    }
+    if (g_op != nullptr) {
+        for (size_t t = first; t < (size_t)B * P; t += step) {
+            const size_t b = t / P, i = t - b * P;
+            if (i < (size_t)Nv) { if (d_smplx_op != nullptr) d_smplx_op[b * Nv + i] = g_op[t]; }
+            else if (d_uv_op != nullptr) d_uv_op[b * N + (i - Nv)] = g_op[t];
+        }
+    }
+    if (g_scale != nullptr && d_smplx_scale != nullptr) {
+        for (size_t t = first; t < (size_t)B * Nv * 3; t += step) {
+            const size_t b = t / ((size_t)Nv * 3), k = t - b * (size_t)Nv * 3;
+            d_smplx_scale[t] = g_scale[b * P * 3 + k];
+        }
+    }
+}
+
 void launch_deform_forward(const DeformArgs& a, const float* smplx_features, const float* uv_features,
                            float* out_xyz, float* out_rot, float* out_scale, float* out_opacity, float* out_features,
                            cudaStream_t s)
@@ -406,6 +443,21 @@ int guava_deform_gaussians_backward(int B, int Nv, int N, int F, const float* ve
     launch_deform_backward(a, dL_dxyz, dL_drotation, dL_dscaling, dL_dsmplx_rotation, dL_duv_local_xyz, dL_duv_rotation,
                            dL_duv_scaling, (cudaStream_t)stream);
     return cudaGetLastError() == cudaSuccess ? 0 : 2;
+}
+
+int guava_deform_split_gradients(int B, int Nv, int N, const float* dL_dscaling, const float* dL_dopacity,
+                                 const float* dL_dfeatures, float* dL_dsmplx_scaling, float* dL_dsmplx_opacity,
+                                 float* dL_dsmplx_features, float* dL_duv_opacity, float* dL_duv_features, void* stream)
+{
+    if (B < 0 || Nv < 0 || N < 0) return report_error(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
+    if ((size_t)B * ((size_t)Nv + N) == 0) return GUAVA_OK;
+    if (((uintptr_t)dL_dfeatures | (uintptr_t)dL_dsmplx_features | (uintptr_t)dL_duv_features) & 15)
+        return report_error(GUAVA_ERR_INVALID_ARGUMENT, "feature gradients must be 16-byte aligned");
+    split_gradients_kernel<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(
+        B, Nv, N, dL_dscaling, dL_dopacity, (const float4*)dL_dfeatures, dL_dsmplx_scaling, dL_dsmplx_opacity,
+        (float4*)dL_dsmplx_features, dL_duv_opacity, (float4*)dL_duv_features);
+    count_launch();
+    return cudaGetLastError() == cudaSuccess ? GUAVA_OK : report_error(GUAVA_ERR_CUDA, "split_gradients_kernel launch failed");
 }
 
 }  // extern "C"

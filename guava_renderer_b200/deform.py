@@ -97,10 +97,23 @@ class _DeformGaussians(torch.autograd.Function):
                 _ptr(g_xyz), _ptr(g_rot), _ptr(g_sc), _ptr(d_srot), _ptr(d_loc), _ptr(d_urot), _ptr(d_usc), stream)
         if rc != _lib.GUAVA_OK:
             raise _lib.GuavaLibraryError(f"guava_deform_gaussians_backward failed ({rc}): {_lib.last_error()}")
-        sl = lambda g, a, b: None if g is None else g[:, a:b]
-        return (None, None, None, None, None,
-                d_srot, sl(g_sc, 0, Nv), sl(g_op, 0, Nv), sl(g_feat, 0, Nv),
-                d_loc, d_urot, d_usc, sl(g_op, Nv, Nv + N), sl(g_feat, Nv, Nv + N))
+        # the pass-through gradients as contiguous tensors of their own, one kernel (as slices of [B,Nv+N,w] each would be
+        # cloned by autograd's accumulation into the leaf)
+        want = ctx.needs_input_grad
+        g_op = None if g_op is None else g_op.contiguous()
+        g_feat = None if g_feat is None else g_feat.contiguous()
+        new = lambda cond, n, w: torch.empty(B, n, w, device=dev) if cond else None
+        d_ssc = new(want[6], Nv, 3)
+        d_sop, d_uop = new(want[7] and g_op is not None, Nv, 1), new(want[12] and g_op is not None, N, 1)
+        d_sft, d_uft = new(want[8] and g_feat is not None, Nv, 32), new(want[13] and g_feat is not None, N, 32)
+        if any(t is not None for t in (d_ssc, d_sop, d_uop, d_sft, d_uft)):
+            with torch.cuda.device(dev):
+                rc = _lib.load().guava_deform_split_gradients(
+                    B, Nv, N, _ptr(g_sc), _ptr(g_op), _ptr(g_feat), _ptr(d_ssc), _ptr(d_sop), _ptr(d_sft), _ptr(d_uop),
+                    _ptr(d_uft), stream)
+            if rc != _lib.GUAVA_OK:
+                raise _lib.GuavaLibraryError(f"guava_deform_split_gradients failed ({rc}): {_lib.last_error()}")
+        return (None, None, None, None, None, d_srot, d_ssc, d_sop, d_sft, d_loc, d_urot, d_usc, d_uop, d_uft)
 
 
 def deform_gaussians(vertices: torch.Tensor, ver_transform_mat: torch.Tensor, faces: torch.Tensor,

@@ -56,6 +56,7 @@ class GraphedRenderStep:
     `summed=True`: the backward sums over the views inside its kernels, straight into `.packed`
     (guava_rasterizer_backward_batch_summed: no [V,P,43] intermediates, no packing kernel); `.grads` and
     `.viewspace_grad` are then not produced.  Not with a `producer` (its backward needs the per-view gradients).
+    `pack=False`: `.packed` is not produced at all (e.g. with a `producer`, whose own leaves' gradients are the result).
     `producer` (instead of the five tensors, pass None for them): a callable that computes the rasterizer's inputs
     inside the captured step from its own static tensors -- e.g. `deform_gaussians` on a posed mesh (the step before
     the rasterizer in GUAVA, ubody_gaussian.py:245-289) -- and returns them as a dict xyz / features / opacity /
@@ -68,10 +69,12 @@ class GraphedRenderStep:
                  dL_dcolor: Optional[torch.Tensor] = None,
                  loss_fn: Optional[Callable[[torch.Tensor, torch.Tensor], torch.Tensor]] = None,
                  packed_out: Optional[torch.Tensor] = None, warmup: int = 2,
-                 producer: Optional[Callable[[], Dict[str, torch.Tensor]]] = None, summed: bool = False):
+                 producer: Optional[Callable[[], Dict[str, torch.Tensor]]] = None, summed: bool = False,
+                 pack: bool = True):
         if summed and producer is not None:
             raise ValueError("summed=True gives no per-view gradients for a producer's backward")
         self.summed = bool(summed)
+        self.pack = bool(pack)      # False: `.packed` is not produced (a producer's step ends in ITS leaves' gradients)
         self.producer = producer
         if producer is not None:
             means3D = settings.viewmatrix       # device only
@@ -161,8 +164,9 @@ class GraphedRenderStep:
         else:
             self.grads = {k: v.grad for k, v in leaf.items()}
             self.viewspace_grad = m2.grad
-            order = ("xyz", "scaling", "rotation", "opacity", "features")
-            self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
+            if self.pack:
+                order = ("xyz", "scaling", "rotation", "opacity", "features")
+                self.packed = pack_gradients([self.grads[k] for k in order], out=self.packed)
         if self.loss_fn is None:
             cur.wait_stream(self._side)
 

@@ -418,6 +418,17 @@ int guava_deform_gaussians_backward(
     float *dL_dsmplx_rotation /* [B,Nv,4] */, float *dL_duv_local_xyz /* [B,N,3] */,
     float *dL_duv_rotation /* [B,N,4] */, float *dL_duv_scaling /* [B,N,3] */, void *stream);
 
+/* The backward of the forward's pass-through outputs (features = smplx ++ uv, opacity likewise, scaling's SMPLX part):
+ * the rasterizer's gradients [B,Nv+N,w] split into contiguous per-attribute tensors in one pass.  Any input / output
+ * pointer may be NULL (that gradient is not wanted).  No reference counterpart: there autograd slices the tensors. */
+int guava_deform_split_gradients(
+    int B, int Nv, int N,
+    const float *dL_dscaling /* [B,Nv+N,3] */, const float *dL_dopacity /* [B,Nv+N,1] */,
+    const float *dL_dfeatures /* [B,Nv+N,32] */,
+    float *dL_dsmplx_scaling /* [B,Nv,3] */, float *dL_dsmplx_opacity /* [B,Nv,1] */,
+    float *dL_dsmplx_features /* [B,Nv,32] */, float *dL_duv_opacity /* [B,N,1] */,
+    float *dL_duv_features /* [B,N,32] */, void *stream);
+
 /* No-allocation variant of guava_deform_gaussians_forward.  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
  * serving loops, harnesses that forbid allocation).  Same inputs, same outputs, same arithmetic as
