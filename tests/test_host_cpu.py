@@ -81,6 +81,19 @@ def test_no_cpu_fallback_and_argument_validation():
           rotations=torch.zeros(4, 4))
 
 
+def test_graphed_step_rejects_a_summed_backward_for_a_producer_and_host_tensors():
+    """Argument errors of GraphedRenderStep that need no GPU: the view-summed backward hands a producer no per-view
+    gradients to continue with, and host tensors are refused (there is no CPU path to capture)."""
+    import guava_renderer_b200 as grb
+    st = grb.BatchRasterizationSettings(16, 16, torch.zeros(1, 2), torch.zeros(1, 32), 1.0, torch.eye(4)[None], torch.eye(4)[None])
+    with pytest.raises(ValueError, match="summed"):
+        grb.GraphedRenderStep(None, None, None, None, None, st, dL_dcolor=torch.zeros(1, 32, 16, 16),
+                              producer=lambda: {}, summed=True)
+    x = torch.zeros(1, 4, 3)
+    with pytest.raises(RuntimeError, match="no CPU path|CUDA"):
+        grb.GraphedRenderStep(x, torch.zeros(1, 4, 32), torch.zeros(1, 4, 1), x, torch.zeros(1, 4, 4), st)
+
+
 def test_product_never_imports_the_oracle():
     for d in ("guava_renderer_b200", "diff_gaussian_rasterization_32", "diff_gaussian_rasterization"):
         for root, _dirs, files in os.walk(os.path.join(ROOT, d)):
@@ -179,7 +192,8 @@ def test_compiled_torch_binding_is_built_and_exports_the_reference_entry_points(
     assert os.path.isfile(rasterizer.TORCH_SO_PATH)
     if rasterizer.BINDING == "compiled":
         for name in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible",
-                     "rasterize_gaussians_batch", "rasterize_gaussians_batch_backward"):
+                     "rasterize_gaussians_batch", "rasterize_gaussians_batch_backward",
+                     "rasterize_gaussians_batch_backward_summed"):
             assert callable(getattr(grb._C, name)), name
     import diff_gaussian_rasterization_32 as dgr
     assert dgr._C is grb._C
