@@ -281,7 +281,6 @@ def run_own(args, rank, world, device):
             color.backward(dL)
             sharding.pack_gradients([leaves[0].grad, leaves[1].grad, leaves[2].grad, leaves[3].grad, leaves[4].grad], out=gbuf)
         else:       # the same work as the replayed step: the backward sums the views into the all-reduce buffer
-            gbuf.zero_()
             color, radii, invd = grb.rasterize_gaussians_batch(leaves[0], m2, leaves[4], leaves[3], leaves[1], leaves[2], st,
                                                                summed_out=gbuf)
             color.backward(dL)

@@ -58,11 +58,12 @@ class Layout(Structure):
 class CallOptions(Structure):
     """guava_call_options (include/guava_rasterizer.h): per-call options of the batched entry."""
     _fields_ = [("struct_size", c_size_t), ("refiner_output_nhwc_bf16", c_void_p), ("status_words", c_void_p),
-                ("no_host_wait", c_int), ("forward_only", c_int)]
+                ("no_host_wait", c_int), ("forward_only", c_int), ("zero_fill", c_void_p), ("zero_fill_bytes", c_size_t)]
 
-    def __init__(self, refiner_output=0, status_words=0, no_host_wait=False, forward_only=False):
+    def __init__(self, refiner_output=0, status_words=0, no_host_wait=False, forward_only=False, zero_fill=0,
+                 zero_fill_bytes=0):
         super().__init__(ctypes.sizeof(CallOptions), refiner_output or None, status_words or None, int(bool(no_host_wait)),
-                         int(bool(forward_only)))
+                         int(bool(forward_only)), zero_fill or None, int(zero_fill_bytes))
 
 
 class GuavaLibraryError(RuntimeError):

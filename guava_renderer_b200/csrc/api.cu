@@ -370,9 +370,15 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "status words must be 8-byte aligned");
     if (((uintptr_t)in.aux_nhwc_bf16 & 15) != 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "refiner output must be 16-byte aligned");
+    if (co != nullptr && co->zero_fill != nullptr && ((((uintptr_t)co->zero_fill) | co->zero_fill_bytes) & 3) != 0)
+        return fail(GUAVA_ERR_INVALID_ARGUMENT, "zero_fill must be 4-byte aligned and a multiple of 4 bytes long");
     if (in.V < 0 || in.P < 0 || in.W <= 0 || in.H <= 0)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "negative size");
-    if ((size_t)in.V * in.P == 0) return GUAVA_OK;   // rasterize_points.cu:88: outputs stay as allocated
+    if ((size_t)in.V * in.P == 0) {   // rasterize_points.cu:88: outputs stay as allocated
+        if (co != nullptr && co->zero_fill != nullptr && co->zero_fill_bytes)
+            GUAVA_CUDA(cudaMemsetAsync(co->zero_fill, 0, co->zero_fill_bytes, stream));
+        return GUAVA_OK;
+    }
     if (in.colors == nullptr)
         return fail(GUAVA_ERR_INVALID_ARGUMENT, "For non-RGB, provide precomputed Gaussian colors!");
     if (in.means3D == nullptr || in.opacities == nullptr || in.viewmatrix == nullptr || in.projmatrix == nullptr ||
@@ -461,7 +467,8 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     }
     launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap,
                      with_large ? 0xFFFFFFFFu : tile_sort_small_limit(),
-                     (uint32_t)sort_mode | ((uint32_t)block_masks << 8) | ((uint32_t)emit_keys << 16), stream);
+                     (uint32_t)sort_mode | ((uint32_t)block_masks << 8) | ((uint32_t)emit_keys << 16),
+                     co ? co->zero_fill : nullptr, co && co->zero_fill ? co->zero_fill_bytes : 0, stream);
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 

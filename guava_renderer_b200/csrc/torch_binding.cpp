@@ -184,7 +184,7 @@ RasterizeGaussiansBatchCUDA(const torch::Tensor& background, const torch::Tensor
                             const float scale_modifier, const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
                             const torch::Tensor& tanfov, const int image_height, const int image_width, const bool antialiasing,
                             const bool debug, const c10::optional<torch::Tensor>& refiner_output, const int64_t status_words,
-                            const bool no_host_wait, const bool forward_only)
+                            const bool no_host_wait, const bool forward_only, const c10::optional<torch::Tensor>& zero_fill)
 {
     TORCH_CHECK(means3D.is_cuda(), "guava_renderer_b200: tensors must live on a CUDA device (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
@@ -210,6 +210,13 @@ RasterizeGaussiansBatchCUDA(const torch::Tensor& background, const torch::Tensor
     co.status_words = reinterpret_cast<void*>(status_words);
     co.no_host_wait = no_host_wait ? 1 : 0;
     co.forward_only = forward_only ? 1 : 0;
+    if (zero_fill.has_value() && zero_fill->defined()) {   // e.g. the summed backward's [P,43] output: zeroed under the tile scan
+        TORCH_CHECK(zero_fill->is_cuda() && zero_fill->is_contiguous() && zero_fill->device() == means3D.device(),
+                    "zero_fill must be a contiguous tensor on the inputs' device");
+        if (V * P == 0) zero_fill->zero_();
+        co.zero_fill = zero_fill->data_ptr();
+        co.zero_fill_bytes = static_cast<size_t>(zero_fill->numel()) * zero_fill->element_size();
+    }
     if (V * P == 0) {
         out_color.zero_();
         out_invdepth.zero_();
@@ -236,7 +243,8 @@ RasterizeGaussiansBatchBackwardCUDA(const torch::Tensor& background, const torch
                                     const torch::Tensor& projmatrix, const torch::Tensor& tanfov,
                                     const torch::Tensor& dL_dout_color, const c10::optional<torch::Tensor>& dL_dout_invdepth,
                                     const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
-                                    const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug)
+                                    const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug,
+                                    const c10::optional<torch::Tensor>& zeroed_block)
 {
     TORCH_CHECK(means3D.is_cuda(), "guava_renderer_b200: tensors must live on a CUDA device (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
@@ -249,7 +257,10 @@ RasterizeGaussiansBatchBackwardCUDA(const torch::Tensor& background, const torch
     const int64_t n = V * P;
     int64_t total = 0;
     for (int i = 0; i < (has_inv ? 9 : 8); i++) total += widths[i];
-    torch::Tensor flat = torch::zeros({n * total}, fopts);
+    // zeroed_block: n * 57 floats the forward of this call zero-filled under its tile scan (guava_call_options::zero_fill)
+    const bool given = zeroed_block.has_value() && zeroed_block->defined() && zeroed_block->numel() >= n * total &&
+                       zeroed_block->is_contiguous() && zeroed_block->scalar_type() == torch::kFloat32;
+    torch::Tensor flat = given ? zeroed_block->view({-1}) : torch::zeros({n * total}, fopts);
     torch::Tensor part[9];
     int64_t off = 0;
     for (int i = 0; i < (has_inv ? 9 : 8); i++) {

@@ -133,8 +133,7 @@ class GraphedRenderStep:
         if self.training and self.summed:
             if self.packed is None:
                 self.packed = torch.empty(P, 43, dtype=torch.float32, device=self.device)
-            self.packed.zero_()          # the backward's kernels add into it
-            summed_out = self.packed
+            summed_out = self.packed     # zero-filled by the forward (under its tile scan); the backward's kernels add into it
         with torch.set_grad_enabled(self.training):
             color, radii, invd = rasterize_gaussians_batch(leaf["xyz"], m2, leaf["features"], leaf["opacity"],
                                                            leaf["scaling"], leaf["rotation"], self.settings,

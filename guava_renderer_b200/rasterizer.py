@@ -406,6 +406,12 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         # (guava_rasterizer_backward_batch_summed) and hands autograd no per-view gradients
         ctx.summed_out = call.get("summed_out")
         fwd_only = not any(ctx.needs_input_grad)      # no gradient can be asked for: inference
+        # the backward's [V,P,.] gradients must start at zero: the block is allocated here and zero-filled by the forward
+        # under its tile scan (guava_call_options::zero_fill) instead of by a 9 us fill kernel in front of the backward
+        ctx.grad_block = None
+        zero_fill = ctx.summed_out
+        if zero_fill is None and not fwd_only and V * P:
+            ctx.grad_block = zero_fill = torch.empty(V * P * sum(_GRAD_WIDTHS), dtype=torch.float32, device=dev)
         m, c, o = _f32c(means3D), _f32c(colors_precomp), _f32c(opacities)
         s, r = _f32c(scales), _f32c(rotations)
         bg, vm, pm, tf = _f32c(st.bg), _f32c(st.viewmatrix), _f32c(st.projmatrix), _f32c(st.tanfov)
@@ -414,7 +420,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
         if BINDING == "compiled":
             rendered, out_color, radii, geom, binning, img, out_invdepth = _C.rasterize_gaussians_batch(
                 bg, m, c, o, s, r, float(st.scale_modifier), vm, pm, tf, H, W, bool(st.antialiasing), bool(st.debug),
-                aux, status.data_ptr() if status is not None else 0, no_wait, fwd_only)
+                aux, status.data_ptr() if status is not None else 0, no_wait, fwd_only, zero_fill)
             bufs = [geom, binning, img]
         else:
             lib = _lib.load()
@@ -434,9 +440,15 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                         raise ValueError("refiner output must be a contiguous bfloat16 [V,H,W,32] tensor")
                     if V * P == 0:
                         aux.zero_()
+                zf = zero_fill
+                if zf is not None and (not zf.is_contiguous() or zf.device != dev):
+                    raise ValueError("summed_out must be a contiguous tensor on the inputs' device")
+                if zf is not None and V * P == 0:
+                    zf.zero_()
                 copts = _lib.CallOptions(refiner_output=_ptr(aux) if aux is not None else 0,
                                          status_words=status.data_ptr() if status is not None else 0, no_host_wait=no_wait,
-                                         forward_only=fwd_only)
+                                         forward_only=fwd_only, zero_fill=zf.data_ptr() if zf is not None else 0,
+                                         zero_fill_bytes=zf.numel() * zf.element_size() if zf is not None else 0)
                 rc = lib.guava_rasterizer_forward_batch(
                     _ALLOC, _USER[0], _ALLOC, _USER[1], _ALLOC, _USER[2],
                     V, P, _ptr(bg), W, H,
@@ -491,11 +503,12 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                         _ptr(gc), _ptr(gi), b0, b0 + 12, b0 + 24, b0 + 40, b0 + 44, 43,
                         int(bool(st.antialiasing)), int(bool(st.debug)), _stream_ptr(dev)))
             return (None,) * 8
+        block, ctx.grad_block = ctx.grad_block, None      # zero-filled by the forward; a repeated backward gets a fresh one
         if BINDING == "compiled":
             g_mean2D, g_color, g_opacity, g_mean3D, g_cov3D, g_scale, g_rot = _C.rasterize_gaussians_batch_backward(
                 bg, m, radii, c, o, s, r, float(st.scale_modifier), vm, pm, tf, grad_color,
                 grad_invdepth if has_inv else None, geom, int(ctx.num_rendered), binning, img,
-                bool(st.antialiasing), bool(st.debug))
+                bool(st.antialiasing), bool(st.debug), block)
         else:
             lib = _lib.load()
             with _device_of(m):
@@ -503,7 +516,7 @@ class _RasterizeGaussiansBatch(torch.autograd.Function):
                 n = V * P
                 # one fill for all gradient tensors.  (Issuing it during the forward on a side stream was
                 # measured slower inside the captured step: the fork/join costs more than the 9 us fill.)
-                flat = torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
+                flat = block if block is not None else torch.zeros(n * sum(widths), dtype=torch.float32, device=dev)
                 parts, off = [], 0
                 for w in widths:
                     parts.append(flat[off:off + n * w].view(V, P, w))
@@ -543,7 +556,8 @@ def rasterize_gaussians_batch(means3D, means2D, colors_precomp, opacities, scale
     Per-call options (guava_call_options): `refiner_output` bf16 [V,H,W,32] written by the compositing
     kernel's epilogue; `status_words` pinned int32[2] receiving (num_rendered, longest list | overflow << 31);
     `no_host_wait` enqueues the chain without waiting for num_rendered (CUDA-graph capture).
-    `summed_out`: a ZERO-FILLED float32 [P,43] tensor; the backward then adds into it, inside its kernels, the sum over
+    `summed_out`: a float32 [P,43] tensor, zero-filled BY THE FORWARD (guava_call_options::zero_fill: on the SMs the
+    one-block tile scan leaves idle); the backward then adds into it, inside its kernels, the sum over
     the views of the parameter gradients (means3D 3, scales 3, rotations 4, opacity 1, features 32 -- the training
     step's all-reduce payload, sharding.py) and the input tensors receive NO `.grad`.
     Returns (color [V,32,H,W], radii [V,P] int32, invdepth [V,1,H,W])."""

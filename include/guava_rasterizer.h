@@ -166,6 +166,12 @@ typedef struct guava_call_options {
      * "taken" marks (option "taken_masks") and the binning buffer does not hold them -- 2 % of the forward and
      * 8 bytes per instance saved.  A backward call after such a forward is still correct, only slower. */
     int forward_only;
+    /* When non-NULL: a device buffer of `zero_fill_bytes` bytes (both multiples of 4) that the forward zero-fills on
+     * its stream -- meant for the output of guava_rasterizer_backward_batch_summed, which must start at zero.  For
+     * frames of up to 8192 tiles the fill costs no time: it runs on the SMs the one-block tile scan leaves idle (same
+     * launch); larger frames get a cudaMemsetAsync. */
+    void *zero_fill;
+    size_t zero_fill_bytes;
 } guava_call_options;
 
 /* Batched multi-view entry (replaces the per-view Python
