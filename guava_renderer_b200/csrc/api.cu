@@ -468,7 +468,8 @@ static int forward_impl(guava_alloc_fn geometryBuffer, void* geometry_user,
     launch_tile_scan(total_tiles, im, hslot_dev, exact ? (size_t)-1 : cap,
                      with_large ? 0xFFFFFFFFu : tile_sort_small_limit(),
                      (uint32_t)sort_mode | ((uint32_t)block_masks << 8) | ((uint32_t)emit_keys << 16),
-                     co ? co->zero_fill : nullptr, co && co->zero_fill ? co->zero_fill_bytes : 0, stream);
+                     co ? co->zero_fill : nullptr, co && co->zero_fill ? co->zero_fill_bytes : 0,
+                     g.grad_geo, (size_t)in.V * in.P * 32, stream);   // grad_geo: see backward_impl
     timer.end();
     GUAVA_STAGE("tile_scan", debug);
 
@@ -604,7 +605,8 @@ static int backward_impl(Inputs in, const int* radii, char* geom, char* bin, cha
 
     StageTimer timer(stream);
     timer.begin(5);
-    GUAVA_CUDA(cudaMemsetAsync(g.grad_geo, 0, (size_t)in.V * in.P * 32, stream));
+    // GeomPtrs::grad_geo is all zeros here: the forward zero-filled it under its tile scan and every backward's
+    // preprocess kernel re-zeroes the records it has consumed (a memset node per backward until round 2).
     launch_render_backward(in, g, im, b, dL_dpix, dL_invdepths, dL_dcolor, sum ? sum->rs_color : (size_t)NUM_CHANNELS,
                            sum ? 0 : (size_t)in.P * NUM_CHANNELS, block_masks, g_opt_tma_staging.load() != 0, stream);
     timer.end();

@@ -169,19 +169,25 @@ __global__ void __launch_bounds__(1024)
 tile_scan_single_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges,
                         uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
                         uint32_t list_limit, uint32_t call_flags, uint4* __restrict__ tile_order,
-                        uint32_t* __restrict__ zero_fill, size_t zero_words)
+                        uint32_t* __restrict__ zero_fill, size_t zero_words, uint32_t* __restrict__ zero_fill2,
+                        size_t zero_words2)
 {
     // Blocks 1 .. gridDim.x-1 (guava_call_options::zero_fill): the scan is one block of latency on one SM; the other
     // SMs zero-fill a caller's buffer meanwhile -- the summed backward's [P,43] output, 17 MB that were a 5 us fill
     // kernel of their own in front of the step.
     if (blockIdx.x != 0) {
         const size_t nthreads = (size_t)(gridDim.x - 1) * 1024, first = (size_t)(blockIdx.x - 1) * 1024 + threadIdx.x;
-        const size_t head = min(zero_words, (size_t)((16u - ((uintptr_t)zero_fill & 15u)) & 15u) / 4);   // words up to 16-byte alignment
-        const size_t nvec = (zero_words - head) / 4;
-        uint4* const vec = reinterpret_cast<uint4*>(zero_fill + head);
-        for (size_t k = first; k < nvec; k += nthreads) vec[k] = make_uint4(0u, 0u, 0u, 0u);
-        for (size_t k = first; k < head; k += nthreads) zero_fill[k] = 0u;
-        for (size_t k = head + 4 * nvec + first; k < zero_words; k += nthreads) zero_fill[k] = 0u;
+        auto fill = [&](uint32_t* p, size_t words) {
+            if (p == nullptr) return;
+            const size_t head = min(words, (size_t)((16u - ((uintptr_t)p & 15u)) & 15u) / 4);   // words up to 16-byte alignment
+            const size_t nvec = (words - head) / 4;
+            uint4* const vec = reinterpret_cast<uint4*>(p + head);
+            for (size_t k = first; k < nvec; k += nthreads) vec[k] = make_uint4(0u, 0u, 0u, 0u);
+            for (size_t k = first; k < head; k += nthreads) p[k] = 0u;
+            for (size_t k = head + 4 * nvec + first; k < words; k += nthreads) p[k] = 0u;
+        };
+        fill(zero_fill, zero_words);     // the caller's buffer (guava_call_options::zero_fill)
+        fill(zero_fill2, zero_words2);   // the backward's per-Gaussian scratch (GeomPtrs::grad_geo)
         return;
     }
     __shared__ uint32_t warp_sums[32];
@@ -258,28 +264,33 @@ tile_scan_single_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict_
 }
 
 void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapped_R, size_t capacity,
-                      uint32_t list_limit, uint32_t call_flags, void* zero_fill, size_t zero_bytes, cudaStream_t s)
+                      uint32_t list_limit, uint32_t call_flags, void* zero_fill, size_t zero_bytes, void* zero_fill2,
+                      size_t zero_bytes2, cudaStream_t s)
 {
     uint32_t* const zf = zero_bytes ? static_cast<uint32_t*>(zero_fill) : nullptr;
     const size_t zw = zero_bytes / 4;
+    uint32_t* const zf2 = zero_bytes2 ? static_cast<uint32_t*>(zero_fill2) : nullptr;
+    const size_t zw2 = zero_bytes2 / 4;
     static const int single = [] { const char* e = getenv("GUAVA_SCAN_SINGLE"); return e ? atoi(e) : 1; }();   // tuning knob
     if (single && total_tiles <= 8192) {
         // + fill blocks on the SMs the scan leaves idle, 16 KB of zeros per block and pass
-        const unsigned fill_blocks = zf ? (unsigned)std::min<size_t>((size_t)sm_count() - 1, (zero_bytes + 16383) / 16384) : 0u;
+        const size_t fill_bytes = (zf ? zero_bytes : 0) + (zf2 ? zero_bytes2 : 0);
+        const unsigned fill_blocks = (unsigned)std::min<size_t>((size_t)sm_count() - 1, (fill_bytes + 16383) / 16384);
         if (total_tiles <= 2048)
             tile_scan_single_kernel<2><<<1 + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges,
                                                                         img.num_rendered, host_mapped_R,
                                                                         (unsigned long long)capacity, list_limit,
-                                                                        call_flags, img.tile_order, zf, zw);
+                                                                        call_flags, img.tile_order, zf, zw, zf2, zw2);
         else
             tile_scan_single_kernel<8><<<1 + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges,
                                                                         img.num_rendered, host_mapped_R,
                                                                         (unsigned long long)capacity, list_limit,
-                                                                        call_flags, img.tile_order, zf, zw);
+                                                                        call_flags, img.tile_order, zf, zw, zf2, zw2);
         count_launch();
         return;
     }
-    if (zf) cudaMemsetAsync(zf, 0, zero_bytes, s);   // frames of more than 8192 tiles: a fill of its own
+    if (zf) cudaMemsetAsync(zf, 0, zero_bytes, s);   // frames of more than 8192 tiles: fills of their own
+    if (zf2) cudaMemsetAsync(zf2, 0, zero_bytes2, s);
     const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
     tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,

@@ -281,9 +281,9 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
 // the per-view outputs the reference's binding keeps (mean2D, conic, cov3D, inverse depth) are not written.
 template <int SUM>
 __global__ void __launch_bounds__(256)
-preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_rendered, const int* __restrict__ radii,
+preprocess_backward_kernel(const Inputs in, uint32_t* __restrict__ num_rendered, const int* __restrict__ radii,
                            const SplatRec* __restrict__ recs,
-                           const float* __restrict__ grad_geo,
+                           float* __restrict__ grad_geo,
                            int has_invdepth, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
                            float* __restrict__ dL_dinvdepth, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
@@ -298,6 +298,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
     const bool lanes = SUM && sum.vshift >= 0;
     if (!lanes && t >= n_total) return;
     if (num_rendered[1]) return;   // the forward's binning overflowed: no lists, no gradients (see render_backward.cu); grid-uniform
+    if (t == 0) num_rendered[3] = 0u;   // the backward compositor's work counter, re-armed for a repeated backward (it ran before this kernel)
     const bool in_range = t < n_total;
     const size_t gid = !lanes ? t : (in_range ? (t & (size_t)(in.V - 1)) * in.P + (t >> sum.vshift) : 0);
     float acc[11];
@@ -325,6 +326,9 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
         sr[3] = qp[0]; sr[4] = qp[1]; sr[5] = qp[2]; sr[6] = qp[3];
     }
     if (in_range && rad > 0) {
+    // consumed: the record is zero again for the next backward of this forward (the forward's scan zero-filled it first)
+    reinterpret_cast<float4*>(grad_geo)[2 * gid] = make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4*>(grad_geo)[2 * gid + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     float4 gg0, gg1;
     gg0.x = -(rc0.z * mo0.x + rc0.w * mo0.y) * (0.5f * in.W);   // dL/dmean2D.x (NDC units, :626)
     gg0.y = -(rc1.x * mo0.y + rc0.w * mo0.x) * (0.5f * in.H);   // dL/dmean2D.y
@@ -539,7 +543,7 @@ preprocess_backward_kernel(const Inputs in, const uint32_t* __restrict__ num_ren
     }
 }
 
-void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, const uint32_t* num_rendered, const int* radii, int has_invdepth,
+void launch_preprocess_backward(const Inputs& in, const GeomPtrs& g, uint32_t* num_rendered, const int* radii, int has_invdepth,
                                 float* dL_dmean2D, float* dL_dconic, float* dL_dinvdepth,
                                 float* dL_dopacity, float* dL_dmean3D, float* dL_dcov3D,
                                 float* dL_dscale, float* dL_drot, const SummedRows* sum, cudaStream_t s)

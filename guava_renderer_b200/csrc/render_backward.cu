@@ -465,7 +465,7 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
     static const int ctas_per_sm = [] { const char* e = getenv("GUAVA_BWD_CTAS"); return e ? atoi(e) : minb; }();   // tuning knob
     const long long full = (long long)sm_count() * ctas_per_sm;
     const unsigned grid = (unsigned)(total < full ? total : full);
-    // the counter was zeroed by the forward's tile scan and is re-armed below for a repeated backward
+    // the counter was zeroed by the forward's tile scan; preprocess_backward_kernel, which follows, re-arms it for a repeated backward
     static const int stages = [] { const char* e = getenv("GUAVA_BWD_STAGES"); return e ? atoi(e) : 2; }();   // tuning knob
 #define GUAVA_LAUNCH_BWD2(MK, TM, IV, NS)                                                                                 \
     render_backward_kernel<MK, TM, IV, NS><<<grid, 32, 0, s>>>(in, fmap, g.rec, img.ranges, img.tile_order, b.point_list,  \
@@ -492,7 +492,6 @@ void launch_render_backward(const Inputs& in, const GeomPtrs& g, const ImagePtrs
 #undef GUAVA_LAUNCH_BWD
 #undef GUAVA_LAUNCH_BWD2
 #undef GUAVA_LAUNCH_BWD_MINB
-    cudaMemsetAsync(img.num_rendered + 3, 0, sizeof(uint32_t), s);
     count_launch();
 }
 

@@ -301,7 +301,8 @@ typedef struct guava_layout {
     size_t depths;         /* float per g (view-space z) */
     size_t rects;          /* uint16[4] per g: tile rect min.x, min.y, max.x, max.y */
     size_t tiles_touched;  /* uint32 per g */
-    size_t grad_geo;       /* float[8] per g, backward scratch (zeroed and filled by backward): sums over
+    size_t grad_geo;       /* float[8] per g, backward scratch (all zeros between calls: zero-filled by the forward
+                              under its tile scan, re-zeroed by each backward once consumed): sums over
                               contributing pixels of s*dx, s*dy, s*dx^2, s*dx*dy, s*dy^2 (s = dL/dG * G,
                               d = mean2D - pixel), G*dL/dalpha, w*dL/dinvdepth, 0 */
     /* image buffer */
