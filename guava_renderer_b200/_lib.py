@@ -11,7 +11,8 @@ from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_float, c_int, c_l
                     c_size_t, c_ulonglong, c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "lib", "libguava_rasterizer_b200.so")
+# GUAVA_LIB_DIR: a directory holding another build of the two libraries (A/B runs of kernel variants, tools/gpu_ab_lib.sh)
+SO_PATH = os.path.join(os.environ.get("GUAVA_LIB_DIR") or os.path.join(_HERE, "lib"), "libguava_rasterizer_b200.so")
 
 ALLOC_FN = CFUNCTYPE(c_void_p, c_void_p, c_size_t)
 
