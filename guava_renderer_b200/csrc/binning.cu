@@ -163,7 +163,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
 // The same results from ONE block when the frame has few tiles (up to 1024 * ITEMS: every GUAVA training shape --
 // 2 views of 512 x 512 are 2048 tiles): thread t owns ITEMS consecutive tiles, so the scan is a serial sum per thread
 // plus one block scan, and the work order is written from registers.  No ticket, no look-back, no "last block" election,
-// no second read of the ranges: one global round trip (the counters) instead of seven, 12 us -> 5 us per step.
+// no second read of the ranges: one global round trip (the counters) instead of seven (13.3 -> 9.6 us under ncu).
 template <int ITEMS>
 __global__ void __launch_bounds__(1024)
 tile_scan_single_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges,
@@ -333,46 +333,30 @@ scatter_kernel(const Inputs in, const GeomPtrs g, const uint32_t* __restrict__ n
     }
     const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t excl = incl - cnt;
-    // UNROLL rounds of 32 instances per iteration: their atomics are independent and in flight together (a warp has
-    // ~100 instances at the GUAVA shapes; one round at a time, each round waited out its own L2 round trip)
-    constexpr int UNROLL = 4;
-    for (uint32_t base = 0; base < total; base += 32 * UNROLL) {
-        uint32_t pos[UNROLL];
-        uint64_t key[UNROLL];
-        bool live[UNROLL];
+    // (Four rounds per iteration, their atomics in flight together, measured the same 19 us: profiles/r02_v16_scan_single.txt.)
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t t = base + lane;
+        // owner = last lane whose exclusive offset is <= t (binary search over the warp)
+        int owner = 0;
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) { live[u] = false; pos[u] = 0u; key[u] = 0ull; }
-#pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const uint32_t t = base + 32u * u + lane;
-            // owner = last lane whose exclusive offset is <= t (binary search over the warp)
-            int owner = 0;
-#pragma unroll
-            for (int step = 16; step >= 1; step >>= 1) {
-                const uint32_t e = __shfl_sync(0xffffffffu, excl, owner + step);
-                if (e <= t) owner += step;
-            }
-            const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, owner);
-            const uint32_t o_w = __shfl_sync(0xffffffffu, w, owner);
-            const uint32_t o_rx = __shfl_sync(0xffffffffu, rx, owner);
-            const uint32_t o_ry = __shfl_sync(0xffffffffu, ry, owner);
-            const uint32_t o_v = __shfl_sync(0xffffffffu, v, owner);
-            const uint32_t o_klo = __shfl_sync(0xffffffffu, klo, owner);
-            const uint32_t o_khi = __shfl_sync(0xffffffffu, khi, owner);
-            live[u] = t < total;
-            pos[u] = 0u;
-            key[u] = ((uint64_t)o_khi << 32) | o_klo;
-            if (live[u]) {
-                const uint32_t local = t - o_excl;
-                const uint32_t yy = local / o_w, xx = local - yy * o_w;
-                const size_t tile = (size_t)o_v * in.tiles + (size_t)(o_ry + yy) * in.gx + (o_rx + xx);
-                pos[u] = atomicAdd(cursor + tile * CURSOR_STRIDE, 1u);
-            }
-            if (base + 32u * (u + 1) >= total) break;   // warp-uniform
+        for (int step = 16; step >= 1; step >>= 1) {
+            const uint32_t e = __shfl_sync(0xffffffffu, excl, owner + step);
+            if (e <= t) owner += step;
         }
-#pragma unroll
-        for (int u = 0; u < UNROLL; u++)
-            if (live[u] && pos[u] < capacity) keys[pos[u]] = key[u];
+        const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, owner);
+        const uint32_t o_w = __shfl_sync(0xffffffffu, w, owner);
+        const uint32_t o_rx = __shfl_sync(0xffffffffu, rx, owner);
+        const uint32_t o_ry = __shfl_sync(0xffffffffu, ry, owner);
+        const uint32_t o_v = __shfl_sync(0xffffffffu, v, owner);
+        const uint32_t o_klo = __shfl_sync(0xffffffffu, klo, owner);
+        const uint32_t o_khi = __shfl_sync(0xffffffffu, khi, owner);
+        if (t < total) {
+            const uint32_t local = t - o_excl;
+            const uint32_t yy = local / o_w, xx = local - yy * o_w;
+            const size_t tile = (size_t)o_v * in.tiles + (size_t)(o_ry + yy) * in.gx + (o_rx + xx);
+            const uint32_t pos = atomicAdd(cursor + tile * CURSOR_STRIDE, 1u);
+            if (pos < capacity) keys[pos] = ((uint64_t)o_khi << 32) | o_klo;
+        }
     }
 }
 
