@@ -60,6 +60,19 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_1024(uint32_t x, uint32
 constexpr int SCAN_TICKET = 0, SCAN_LONGEST = 1, SCAN_DONE = 2, SCAN_BINS = 32, SCAN_BINCUR = 288, SCAN_STATE = 544;
 size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (total_tiles + 1023) / 1024 + 1); }
 
+// Zero-fill duty of the scan launches' spare blocks (guava_call_options::zero_fill and the backward's grad_geo scratch):
+// `nthreads` threads, this one is number `first`; 16-byte vectors with a scalar head and tail.
+__device__ __forceinline__ void zero_fill_slice(uint32_t* p, size_t words, size_t first, size_t nthreads)
+{
+    if (p == nullptr) return;
+    const size_t head = min(words, (size_t)((16u - ((uintptr_t)p & 15u)) & 15u) / 4);   // words up to 16-byte alignment
+    const size_t nvec = (words - head) / 4;
+    uint4* const vec = reinterpret_cast<uint4*>(p + head);
+    for (size_t k = first; k < nvec; k += nthreads) vec[k] = make_uint4(0u, 0u, 0u, 0u);
+    for (size_t k = first; k < head; k += nthreads) p[k] = 0u;
+    for (size_t k = head + 4 * nvec + first; k < words; k += nthreads) p[k] = 0u;
+}
+
 // One block per 1024 tiles, chained by a decoupled look-back (blocks ordered by ticket): exclusive scan of the
 // per-tile counts = tile ranges (identifyTileRanges) and bucket cursors, the histogram of list lengths, the longest
 // list, and -- by the last block of the chain -- R and the overflow flag.  The block that FINISHES last then writes
@@ -69,8 +82,16 @@ size_t tile_scan_scratch_bytes(size_t total_tiles) { return 4 * (SCAN_STATE + (t
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ ranges, uint32_t* __restrict__ scratch,
                  uint32_t* __restrict__ num_rendered, uint32_t* __restrict__ host_R, unsigned long long capacity,
-                 uint32_t list_limit, uint32_t call_flags, uint4* __restrict__ tile_order)
+                 uint32_t list_limit, uint32_t call_flags, uint4* __restrict__ tile_order, int scan_blocks,
+                 uint32_t* __restrict__ zero_fill, size_t zero_words, uint32_t* __restrict__ zero_fill2, size_t zero_words2)
 {
+    if ((int)blockIdx.x >= scan_blocks) {   // spare blocks: zero-fill duty (see tile_scan_single_kernel)
+        const size_t nthreads = (size_t)(gridDim.x - scan_blocks) * 1024;
+        const size_t first = (size_t)(blockIdx.x - scan_blocks) * 1024 + threadIdx.x;
+        zero_fill_slice(zero_fill, zero_words, first, nthreads);
+        zero_fill_slice(zero_fill2, zero_words2, first, nthreads);
+        return;
+    }
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t bins[256];
     __shared__ uint32_t bin_base[256];
@@ -80,7 +101,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     if (tid == 0) s_bid = atomicAdd(scratch + SCAN_TICKET, 1u);
     __syncthreads();
     const int bid = (int)s_bid;
-    const int nblocks = (n + 1023) / 1024;
+    const int nblocks = scan_blocks;
     const int k = bid * 1024 + tid;
     const uint32_t c = k < n ? cursor[(size_t)k * CURSOR_STRIDE] : 0u;
     // length bins (255 - len/8) and the longest list; warp-aggregated: most tiles of a frame are empty
@@ -160,7 +181,7 @@ tile_scan_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict__ range
     }
 }
 
-// The same results from ONE block when the frame has few tiles (up to 1024 * ITEMS: every GUAVA training shape --
+// The same results from ONE block when the frame has few tiles (up to 1024 * ITEMS = 2048: every GUAVA training shape --
 // 2 views of 512 x 512 are 2048 tiles): thread t owns ITEMS consecutive tiles, so the scan is a serial sum per thread
 // plus one block scan, and the work order is written from registers.  No ticket, no look-back, no "last block" election,
 // no second read of the ranges: one global round trip (the counters) instead of seven (13.3 -> 9.6 us under ncu).
@@ -177,17 +198,8 @@ tile_scan_single_kernel(int n, uint32_t* __restrict__ cursor, uint2* __restrict_
     // kernel of their own in front of the step.
     if (blockIdx.x != 0) {
         const size_t nthreads = (size_t)(gridDim.x - 1) * 1024, first = (size_t)(blockIdx.x - 1) * 1024 + threadIdx.x;
-        auto fill = [&](uint32_t* p, size_t words) {
-            if (p == nullptr) return;
-            const size_t head = min(words, (size_t)((16u - ((uintptr_t)p & 15u)) & 15u) / 4);   // words up to 16-byte alignment
-            const size_t nvec = (words - head) / 4;
-            uint4* const vec = reinterpret_cast<uint4*>(p + head);
-            for (size_t k = first; k < nvec; k += nthreads) vec[k] = make_uint4(0u, 0u, 0u, 0u);
-            for (size_t k = first; k < head; k += nthreads) p[k] = 0u;
-            for (size_t k = head + 4 * nvec + first; k < words; k += nthreads) p[k] = 0u;
-        };
-        fill(zero_fill, zero_words);     // the caller's buffer (guava_call_options::zero_fill)
-        fill(zero_fill2, zero_words2);   // the backward's per-Gaussian scratch (GeomPtrs::grad_geo)
+        zero_fill_slice(zero_fill, zero_words, first, nthreads);     // the caller's buffer (guava_call_options::zero_fill)
+        zero_fill_slice(zero_fill2, zero_words2, first, nthreads);   // the backward's per-Gaussian scratch (GeomPtrs::grad_geo)
         return;
     }
     __shared__ uint32_t warp_sums[32];
@@ -272,30 +284,30 @@ void launch_tile_scan(int total_tiles, const ImagePtrs& img, uint32_t* host_mapp
     uint32_t* const zf2 = zero_bytes2 ? static_cast<uint32_t*>(zero_fill2) : nullptr;
     const size_t zw2 = zero_bytes2 / 4;
     static const int single = [] { const char* e = getenv("GUAVA_SCAN_SINGLE"); return e ? atoi(e) : 1; }();   // tuning knob
-    if (single && total_tiles <= 8192) {
-        // + fill blocks on the SMs the scan leaves idle, 16 KB of zeros per block and pass
-        const size_t fill_bytes = (zf ? zero_bytes : 0) + (zf2 ? zero_bytes2 : 0);
+    // + fill blocks on the SMs the scan leaves idle, 16 KB of zeros per block and pass
+    const size_t fill_bytes = (zf ? zero_bytes : 0) + (zf2 ? zero_bytes2 : 0);
+    const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
+    if (single && total_tiles <= 2048) {   // (eight tiles per thread for frames of up to 8192 tiles measured slower than the chain: 32 against 19 us at C2)
         const unsigned fill_blocks = (unsigned)std::min<size_t>((size_t)sm_count() - 1, (fill_bytes + 16383) / 16384);
-        if (total_tiles <= 2048)
-            tile_scan_single_kernel<2><<<1 + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges,
-                                                                        img.num_rendered, host_mapped_R,
-                                                                        (unsigned long long)capacity, list_limit,
-                                                                        call_flags, img.tile_order, zf, zw, zf2, zw2);
-        else
-            tile_scan_single_kernel<8><<<1 + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges,
-                                                                        img.num_rendered, host_mapped_R,
-                                                                        (unsigned long long)capacity, list_limit,
-                                                                        call_flags, img.tile_order, zf, zw, zf2, zw2);
+        tile_scan_single_kernel<2><<<1 + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, img.num_rendered,
+                                                                    host_mapped_R, (unsigned long long)capacity, list_limit,
+                                                                    call_flags, img.tile_order, zf, zw, zf2, zw2);
         count_launch();
         return;
     }
-    if (zf) cudaMemsetAsync(zf, 0, zero_bytes, s);   // frames of more than 8192 tiles: fills of their own
-    if (zf2) cudaMemsetAsync(zf2, 0, zero_bytes2, s);
-    const unsigned nblocks = (unsigned)((total_tiles + 1023) / 1024);
+    // larger frames: one scan block per 1024 tiles (they start first: blocks are dispatched in index order, and the
+    // look-back is ordered by ticket, not by block index), the rest of the machine fills
+    const unsigned spare = (unsigned)sm_count() > nblocks ? (unsigned)sm_count() - nblocks : 0u;
+    unsigned fill_blocks = (unsigned)std::min<size_t>(spare, (fill_bytes + 16383) / 16384);
+    if (fill_bytes && spare < 32u) {   // frames of > 100 k tiles: the scan fills the machine itself, plain memsets
+        if (zf) cudaMemsetAsync(zf, 0, zero_bytes, s);
+        if (zf2) cudaMemsetAsync(zf2, 0, zero_bytes2, s);
+        fill_blocks = 0;
+    }
     uint32_t* scratch = img.tile_cursor + (size_t)total_tiles * CURSOR_STRIDE;
-    tile_scan_kernel<<<nblocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
-                                              host_mapped_R, (unsigned long long)capacity, list_limit, call_flags,
-                                              img.tile_order);
+    tile_scan_kernel<<<nblocks + fill_blocks, 1024, 0, s>>>(total_tiles, img.tile_cursor, img.ranges, scratch, img.num_rendered,
+                                                            host_mapped_R, (unsigned long long)capacity, list_limit, call_flags,
+                                                            img.tile_order, (int)nblocks, zf, zw, zf2, zw2);
     count_launch();
 }
 

@@ -167,9 +167,9 @@ typedef struct guava_call_options {
      * 8 bytes per instance saved.  A backward call after such a forward is still correct, only slower. */
     int forward_only;
     /* When non-NULL: a device buffer of `zero_fill_bytes` bytes (both multiples of 4) that the forward zero-fills on
-     * its stream -- meant for the output of guava_rasterizer_backward_batch_summed, which must start at zero.  For
-     * frames of up to 8192 tiles the fill costs no time: it runs on the SMs the one-block tile scan leaves idle (same
-     * launch); larger frames get a cudaMemsetAsync. */
+     * its stream -- meant for the output of guava_rasterizer_backward_batch_summed, which must start at zero.  The
+     * fill costs little or no time: it runs, in the tile scan's launch, on the SMs the scan leaves idle (frames of more
+     * than ~100 k tiles get a cudaMemsetAsync). */
     void *zero_fill;
     size_t zero_fill_bytes;
 } guava_call_options;
