@@ -94,6 +94,45 @@ def test_graphed_step_rejects_a_summed_backward_for_a_producer_and_host_tensors(
         grb.GraphedRenderStep(x, torch.zeros(1, 4, 32), torch.zeros(1, 4, 1), x, torch.zeros(1, 4, 4), st)
 
 
+def test_c_abi_rejects_bad_arguments_before_touching_the_device():
+    """Argument errors of the entry points added in round 2, through ctypes; each returns before any CUDA call (the
+    pointers are never dereferenced), so this runs without a GPU."""
+    import ctypes
+    import guava_renderer_b200 as grb
+    lib = grb._lib_mod.load()
+    L = grb._lib_mod
+    p = ctypes.c_void_p
+    fake = p(0x1000)
+    # guava_call_options::zero_fill must be 4-byte aligned and a multiple of 4 bytes long
+    for ptr, nbytes in ((0x1002, 16), (0x1000, 18)):
+        co = L.CallOptions(zero_fill=ptr, zero_fill_bytes=nbytes)
+        n = ctypes.c_int(7)
+        rc = lib.guava_rasterizer_forward_batch(L.ALLOC_FN(lambda u, s: 0), None, L.ALLOC_FN(lambda u, s: 0), None,
+                                                L.ALLOC_FN(lambda u, s: 0), None, 0, 0, fake, 16, 16, fake, 0, fake, 0, fake, 0,
+                                                fake, 0, 1.0, fake, 0, fake, fake, fake, fake, fake, 0, fake, 0, None,
+                                                ctypes.byref(n), ctypes.byref(co))
+        assert rc == L.GUAVA_ERR_INVALID_ARGUMENT and "zero_fill" in L.last_error()
+    # a struct of another size (another version of the header) is refused
+    co = L.CallOptions()
+    co.struct_size = 8
+    rc = lib.guava_rasterizer_forward_batch(L.ALLOC_FN(lambda u, s: 0), None, L.ALLOC_FN(lambda u, s: 0), None,
+                                            L.ALLOC_FN(lambda u, s: 0), None, 0, 0, fake, 16, 16, fake, 0, fake, 0, fake, 0,
+                                            fake, 0, 1.0, fake, 0, fake, fake, fake, fake, fake, 0, fake, 0, None, None,
+                                            ctypes.byref(co))
+    assert rc == L.GUAVA_ERR_INVALID_ARGUMENT and "struct_size" in L.last_error()
+    # the summed backward: out_row_stride is 0 or at least 43 floats
+    rc = lib.guava_rasterizer_backward_batch_summed(1, 4, 0, fake, 16, 16, fake, 0, fake, 0, fake, 0, fake, 0, 1.0, fake, 0,
+                                                    fake, fake, fake, fake, fake, fake, fake, fake, None,
+                                                    fake, fake, fake, fake, fake, 17, 0, 0, None)
+    assert rc == L.GUAVA_ERR_INVALID_ARGUMENT and "out_row_stride" in L.last_error()
+    # the deformation's gradient split: sizes, and 16-byte alignment of the feature tensors
+    assert lib.guava_deform_split_gradients(-1, 4, 4, None, None, None, None, None, None, None, None, None) == \
+        L.GUAVA_ERR_INVALID_ARGUMENT
+    assert lib.guava_deform_split_gradients(1, 0, 0, None, None, None, None, None, None, None, None, None) == L.GUAVA_OK
+    rc = lib.guava_deform_split_gradients(1, 4, 4, None, None, p(0x1004), None, None, fake, None, fake, None)
+    assert rc == L.GUAVA_ERR_INVALID_ARGUMENT and "16-byte" in L.last_error()
+
+
 def test_product_never_imports_the_oracle():
     for d in ("guava_renderer_b200", "diff_gaussian_rasterization_32", "diff_gaussian_rasterization"):
         for root, _dirs, files in os.walk(os.path.join(ROOT, d)):
