@@ -4,8 +4,10 @@ tools/ timing scripts; the product path is csrc/deform.cu and never touches this
 Follows models/UbodyAvatar/ubody_gaussian.py:245-289 line by line with plain torch ops, so that
 `torch.autograd` provides the reference gradients.  `compute_face_orientation`, `safe_normalize`,
 `length`, `dot` follow utils/graphics_utils.py:52-80.  The quaternion helpers restate roma 1.5.3
-(requirements.txt:6; not vendored in /root/reference, not installed here => parity for them is pinned
-only by the algebraic checks in tests/test_deform_cpu.py: "parity unpinned" against roma itself):
+(requirements.txt:6; not vendored in /root/reference, not installed here => "parity unpinned" against roma itself;
+pinned against SciPy instead, whose Rotation.from_matrix is the algorithm roma's rotmat_to_unitquat adapts -- component
+for component, sign included, in every decision branch -- and against SciPy's composition of rotations for the
+product, plus the algebraic checks, tests/test_deform_cpu.py):
   rotmat_to_unitquat  SciPy's Rotation.from_matrix decision (argmax over diag and trace), XYZW
   quat_product        Hamilton product, XYZW
   quat_xyzw_to_wxyz / quat_wxyz_to_xyzw

@@ -22,6 +22,29 @@ def test_rotmat_to_unitquat_roundtrip_all_branches():
     assert torch.allclose(do.unitquat_to_rotmat(q2), R, atol=1e-12)
 
 
+def test_restated_roma_helpers_against_scipy():
+    """roma is not installed, but the algorithm its `rotmat_to_unitquat` uses is SciPy's
+    (`scipy.spatial.transform.Rotation.from_matrix`: decision matrix of the diagonal and the trace, XYZW, no sign
+    canonicalisation) and SciPy is: the restatement must reproduce it component for component, sign included, in every
+    decision branch; the quaternion product against SciPy's composition of rotations (up to the sign of q)."""
+    from scipy.spatial.transform import Rotation as Rot
+    g = torch.Generator().manual_seed(4)
+    q = torch.nn.functional.normalize(torch.randn(4000, 4, generator=g, dtype=torch.float64), dim=-1)
+    for k in range(4):
+        q[k * 500:(k + 1) * 500, k] += 3.0
+    q = torch.nn.functional.normalize(q, dim=-1)
+    R = do.unitquat_to_rotmat(q)
+    mine = do.rotmat_to_unitquat(R).numpy()
+    theirs = Rot.from_matrix(R.numpy()).as_quat()          # XYZW
+    assert np.abs(mine - theirs).max() <= 1e-15
+    assert np.abs(do.unitquat_to_rotmat(q).numpy() - Rot.from_quat(q.numpy()).as_matrix()).max() <= 1e-14
+    p = torch.nn.functional.normalize(torch.randn(4000, 4, generator=g, dtype=torch.float64), dim=-1)
+    prod = do.quat_product(p, q).numpy()
+    comp = (Rot.from_quat(p.numpy()) * Rot.from_quat(q.numpy())).as_quat()
+    sign = np.sign((prod * comp).sum(-1, keepdims=True))
+    assert np.abs(prod * sign - comp).max() <= 1e-14
+
+
 def test_quat_product_is_rotation_composition():
     g = torch.Generator().manual_seed(1)
     p = torch.nn.functional.normalize(torch.randn(100, 4, generator=g, dtype=torch.float64), dim=-1)
